@@ -1,0 +1,102 @@
+/* qfedx_b200 C ABI - hand-written sm_100a kernels behind the Python package.
+ *
+ * Every entry point returns 0 on success, a positive cudaError_t value if a CUDA call
+ * failed, or a negative QFX_ERR_* code for a rejected argument; qfx_last_error() gives the
+ * message.  All pointers are device pointers unless a comment says otherwise.  Kernels are
+ * enqueued on `stream` and do not synchronise.  The library is built by
+ * `python -m qfedx_b200.build` into qfedx_b200/lib/libqfedx_b200.so.
+ *
+ * Citations name the part of the reference (/root/reference) or of its ROADMAP that the
+ * entry point provides; the reference itself contains no native code.
+ */
+#ifndef QFEDX_B200_H
+#define QFEDX_B200_H
+
+#include <cuda_runtime_api.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QFX_ERR_BAD_ARG (-1)
+#define QFX_ERR_UNSUPPORTED (-2)
+#define QFX_ERR_TOO_LARGE (-3)
+
+/* basis: 0 rx, 1 ry, 2 rz (feature-map rotation, /root/reference/src/QFed/qAngle.py:43-50)
+ * entangler: 0 CNOT ring, 1 CZ ring, 2 none (/root/reference/ROADMAP.md:127) */
+
+const char* qfx_last_error(void);
+int qfx_version(void);
+
+/* K1+K3: feature map (angles [B,n]) or amplitude-encoded real state (init_state [B,2^n]),
+ * L ansatz layers theta [G,L,n,2] (gid [B] picks the group, NULL = group 0), <Z_q> for every
+ * qubit -> expvals [B,n] (nullable).  state_out [B,2^n] complex64 interleaved (nullable).
+ * n <= 10.  Ansatz: /root/reference/ROADMAP.md:126-128; encoders: src/QFed/qAngle.py:27-51,
+ * src/QFed/qAmplitude.py:25-46. */
+int qfx_sv_forward(int n_qubits, int n_layers, int basis, int entangler, const float* angles,
+                   const float* init_state, const float* theta, const int* gid, int batch,
+                   float* expvals, float* state_out, cudaStream_t stream);
+
+/* K4a: adjoint differentiation of sum_q cot[b,q] <Z_q>; ACCUMULATES into grad_theta [G,L,n,2]
+ * (zero it first); grad_angles [B,n] nullable.  /root/reference/ROADMAP.md:23,27. */
+int qfx_sv_adjoint_backward(int n_qubits, int n_layers, int basis, int entangler, const float* angles,
+                            const float* init_state, const float* theta, const int* gid, int batch,
+                            const float* cot, float* grad_theta, float* grad_angles, cudaStream_t stream);
+
+/* K4b: the same gradient by the two-term parameter-shift rule, 2P shifted circuits per sample
+ * as an extra batch axis; ACCUMULATES into grad_theta.  /root/reference/ROADMAP.md:130-135. */
+int qfx_sv_param_shift(int n_qubits, int n_layers, int basis, int entangler, const float* angles,
+                       const float* init_state, const float* theta, const int* gid, int batch,
+                       const float* cot, float* grad_theta, cudaStream_t stream);
+
+/* Whole-client local training in one launch: one thread-block cluster (cluster_size 1..8 CTAs)
+ * per selected client walks `epochs` x ceil(n_k/batch_size) minibatches with forward, loss,
+ * adjoint (grad_mode 0) or parameter-shift (grad_mode 1) gradients and the optimizer
+ * (0 SGD-momentum: beta1 = momentum; 1 Adam) on-chip.  Parameters are the flat vector
+ * [theta (2nL) | a (C) | b (C)], logits_j = a_j <Z_j> + b_j, C = 1 -> BCE, C > 1 -> softmax CE.
+ * angles [N,n], labels [N], offsets [K+1], perm [epochs,N] (nullable), client_ids [n_selected],
+ * params_out [n_selected, D], stats_out [n_selected, 2] (mean loss, accuracy of the last epoch).
+ * Counterpart of client_update, /root/reference/src/CFed/Classical_FL.py:40-64, for the VQC of
+ * /root/reference/ROADMAP.md:29-43. */
+int qfx_vqc_local_train(int n_qubits, int n_layers, int basis, int entangler, int n_classes,
+                        const float* angles, const int* labels, const int* offsets, const int* perm,
+                        int n_total, const float* params_in, const int* client_ids, int n_selected,
+                        float* params_out, float* stats_out, int epochs, int batch_size, int optimizer,
+                        float lr, float beta1, float beta2, float eps, int grad_mode, int cluster_size,
+                        cudaStream_t stream);
+
+/* Evaluation in one launch: out2[0] = sum of losses, out2[1] = number correct.
+ * Counterpart of evaluate_model, /root/reference/src/CFed/Classical_FL.py:83-102. */
+int qfx_vqc_eval(int n_qubits, int n_layers, int basis, int entangler, int n_classes, const float* angles,
+                 const int* labels, const float* params, int n_samples, float* out2, cudaStream_t stream);
+
+/* K7: fused FedAvg + per-client L2 clip + Gaussian noise + pairwise-mask secure aggregation +
+ * server update, one cooperative launch.  client_params [K,D]; weights [K] sample counts;
+ * participate [K] 0/1 (nullable); mode 0 = average weights (the reference's federated_averaging,
+ * /root/reference/src/CFed/Classical_FL.py:66-81), 1 = average deltas theta_k - theta_g with the
+ * first n_wrap entries wrapped to [-pi,pi) (/root/reference/ROADMAP.md:37); clip <= 0 disables
+ * clipping; sigma is the noise multiplier (std = sigma*clip per client, ROADMAP.md:50-51);
+ * secagg != 0 sums fixed-point messages carrying pairwise masks (ROADMAP.md:52-55).
+ * norms_out [K] and masked_out [K,D] are nullable; scratch is K floats of workspace. */
+int qfx_fedavg_fused(const float* client_params, const float* global_in, float* global_out,
+                     const float* weights, const int* participate, int n_clients, int dim, int mode,
+                     int n_wrap, float clip, float sigma, float server_lr, unsigned long long seed, int round,
+                     int secagg, float* norms_out, long long* masked_out, float* scratch, cudaStream_t stream);
+
+/* K7 across GPUs: this rank's k_local clients (global ids client_gids) are reduced locally,
+ * the partial sum is pushed into slot [rank] of every rank's receive buffer with peer stores over
+ * NVLink, flags are released/acquired at system scope, and every rank applies the same update.
+ * recv_slots[r] / flags[r] are device-visible pointers to rank r's buffers ([world][dim] int64 and
+ * [world] u32).  epoch must increase every call; alternate two slot sets between calls. */
+int qfx_fedavg_fused_multi(const float* client_params, const float* global_in, float* global_out,
+                           const float* weights, const int* participate, const int* client_gids, int k_local,
+                           int k_global, int dim, int mode, int n_wrap, float clip, float sigma, float server_lr,
+                           unsigned long long seed, int round, int secagg, float* norms_out, float* scratch,
+                           int rank, int world, long long* const* recv_slots, unsigned int* const* flags,
+                           unsigned int epoch, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QFEDX_B200_H */

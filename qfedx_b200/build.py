@@ -1,0 +1,97 @@
+"""Build the in-tree CUDA library: ``python -m qfedx_b200.build [--force] [--verbose]``.
+
+Every ``csrc/*.cu`` is compiled with nvcc for sm_100a only
+(``-gencode arch=compute_100a,code=sm_100a -lineinfo``) into an object under ``build/`` and
+the objects are linked into ``qfedx_b200/lib/libqfedx_b200.so``.  The library has a C ABI
+(include/qfedx_b200.h) and is loaded with ctypes (qfedx_b200/ops/_lib.py); it lives in-tree
+so that it travels to the GPU box with the repository snapshot.  Compilation is incremental
+(content hash of the source, its headers and the flags) and parallel across files.
+"""
+from __future__ import annotations
+
+import argparse
+import hashlib
+import os
+import shutil
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+from pathlib import Path
+
+PKG = Path(__file__).resolve().parent
+ROOT = PKG.parent
+CSRC = PKG / "csrc"
+OBJ_DIR = ROOT / "build" / "obj"
+LIB_DIR = PKG / "lib"
+LIB_PATH = LIB_DIR / "libqfedx_b200.so"
+
+ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]
+NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr",
+              "-diag-suppress", "128", "-I", str(ROOT / "include"), "-I", str(CSRC)]
+
+
+def nvcc_path() -> str:
+    cand = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(cand):
+        raise RuntimeError("nvcc not found; the qfedx_b200 CUDA library cannot be built")
+    return cand
+
+
+def _digest(src: Path, extra: str) -> str:
+    h = hashlib.sha256()
+    h.update(extra.encode())
+    h.update(src.read_bytes())
+    for hdr in sorted(list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.h")) + list((ROOT / "include").glob("*.h"))):
+        h.update(hdr.read_bytes())
+    return h.hexdigest()
+
+
+def sources():
+    return sorted(CSRC.glob("*.cu"))
+
+
+def compile_one(src: Path, force: bool, verbose: bool) -> Path:
+    OBJ_DIR.mkdir(parents=True, exist_ok=True)
+    obj = OBJ_DIR / (src.stem + ".o")
+    stamp = OBJ_DIR / (src.stem + ".sha")
+    flags = ARCH_FLAGS + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else [])
+    dig = _digest(src, " ".join(flags))
+    if not force and obj.exists() and stamp.exists() and stamp.read_text() == dig:
+        return obj
+    cmd = [nvcc_path()] + flags + ["-c", str(src), "-o", str(obj)]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError(f"nvcc failed for {src.name}:\n{res.stdout}\n{res.stderr}")
+    if verbose:
+        print(res.stderr)
+    stamp.write_text(dig)
+    return obj
+
+
+def build(force: bool = False, verbose: bool = False, jobs: int | None = None) -> Path:
+    srcs = sources()
+    jobs = jobs or min(len(srcs), os.cpu_count() or 4)
+    with ThreadPoolExecutor(max_workers=jobs) as pool:
+        objs = list(pool.map(lambda s: compile_one(s, force, verbose), srcs))
+    LIB_DIR.mkdir(parents=True, exist_ok=True)
+    newest = max(o.stat().st_mtime for o in objs)
+    if force or not LIB_PATH.exists() or LIB_PATH.stat().st_mtime < newest:
+        cmd = [nvcc_path()] + ARCH_FLAGS + ["-shared", "-o", str(LIB_PATH)] + [str(o) for o in objs] + \
+              ["-Xcompiler", "-fPIC", "-lcudart_static", "-ldl", "-lrt", "-lpthread"]
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError(f"link failed:\n{res.stdout}\n{res.stderr}")
+    return LIB_PATH
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser(description=__doc__)
+    ap.add_argument("--force", action="store_true")
+    ap.add_argument("--verbose", action="store_true")
+    ap.add_argument("-j", "--jobs", type=int, default=None)
+    args = ap.parse_args(argv)
+    print(build(args.force, args.verbose, args.jobs))
+
+
+if __name__ == "__main__":
+    sys.exit(main())

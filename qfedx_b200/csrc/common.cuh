@@ -1,0 +1,84 @@
+// Shared device/host helpers for the qfedx_b200 sm_100a kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+namespace qfx {
+
+// ---- error plumbing for the C ABI -------------------------------------------------
+// Every extern "C" entry point returns 0 on success or a cudaError_t / negative
+// argument-error code; qfx_last_error() returns the text of the last failure.
+void set_last_error(const char* fmt, ...);
+inline int check_launch(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        set_last_error("%s: %s", what, cudaGetErrorString(e));
+        return (int)e;
+    }
+    return 0;
+}
+#define QFX_CUDA_TRY(expr)                                                     \
+    do {                                                                       \
+        cudaError_t _e = (expr);                                               \
+        if (_e != cudaSuccess) {                                               \
+            ::qfx::set_last_error("%s: %s", #expr, cudaGetErrorString(_e));    \
+            return (int)_e;                                                    \
+        }                                                                      \
+    } while (0)
+#define QFX_ARG_CHECK(cond, code, ...)                                         \
+    do {                                                                       \
+        if (!(cond)) {                                                         \
+            ::qfx::set_last_error(__VA_ARGS__);                                \
+            return (code);                                                     \
+        }                                                                      \
+    } while (0)
+
+enum : int { QFX_ERR_BAD_ARG = -1, QFX_ERR_UNSUPPORTED = -2, QFX_ERR_TOO_LARGE = -3 };
+
+// ---- counter-based RNG (shared bit-for-bit with qfedx_b200/fl/prng.py) --------------
+// splitmix64 finaliser as a stateless hash; streams are keyed by mixing words in.
+__host__ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+__host__ __device__ __forceinline__ uint64_t key3(uint64_t seed, uint64_t a, uint64_t b) {
+    return mix64(mix64(mix64(seed) ^ a) ^ (b * 0xD1342543DE82EF95ull));
+}
+__host__ __device__ __forceinline__ uint64_t stream_at(uint64_t key, uint64_t idx) {
+    return mix64(key ^ (idx * 0x9E3779B97F4A7C15ull));
+}
+// two uniforms in (0,1] from one 64-bit word -> one standard normal (Box-Muller)
+__device__ __forceinline__ float normal_from_bits(uint64_t r) {
+    float u1 = ((uint32_t)(r >> 40) + 1u) * (1.0f / 16777216.0f);          // (0,1]
+    float u2 = ((uint32_t)(r & 0xFFFFFFu)) * (1.0f / 16777216.0f);          // [0,1)
+    float rad = sqrtf(-2.0f * __logf(u1));
+    float s, c;
+    __sincosf(6.283185307179586f * u2, &s, &c);
+    return rad * c;
+}
+__device__ __forceinline__ float uniform_from_bits(uint64_t r) {
+    return ((uint32_t)(r >> 40)) * (1.0f / 16777216.0f);                     // [0,1)
+}
+
+// ---- warp helpers -----------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+template <int WIDTH>
+__device__ __forceinline__ float group_sum(float v) {  // butterfly over WIDTH consecutive lanes
+#pragma unroll
+    for (int o = WIDTH / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__device__ __forceinline__ float wrap_pi(float x) {  // to [-pi, pi)
+    const float two_pi = 6.283185307179586f;
+    return x - two_pi * floorf((x + 3.14159265358979323846f) / two_pi);
+}
+
+}  // namespace qfx

@@ -1,0 +1,395 @@
+// Register-tiled statevector for n <= 10 qubits (kernels K1/K3/K4a/K4b of SURVEY.md 2.5).
+//
+// A circuit's 2^n complex amplitudes live entirely in registers, spread over a group of
+// LANES = 2^LB consecutive lanes of one warp with A = 2^NL amplitudes per lane:
+//   n <= 4      : LB = 0, one thread owns the whole state (16 amplitudes = 32 registers)
+//   5 <= n <= 9 : LB = n-4, 16 amplitudes per lane, 2..32 lanes per circuit
+//   n == 10     : LB = 5, 32 amplitudes per lane
+// Amplitude index = (lane_in_group << NL) | local, so qubits [0, NL) are "local" (gates are
+// pure register arithmetic, CNOTs between local qubits are compile-time register renames)
+// and qubits [NL, n) are "lane" qubits (gates exchange amplitudes with __shfl_xor_sync).
+// Every loop over amplitudes and qubits is fully unrolled so that all indexing is static
+// and nothing spills to local memory (checked with -Xptxas -v).
+//
+// Gate conventions: qfedx_b200/oracle/statevector.py (little-endian, exp(-i a P/2)).
+// No reference counterpart: /root/reference has no simulator; the ansatz is the one planned
+// in /root/reference/ROADMAP.md:126-128.
+#pragma once
+#include "common.cuh"
+
+namespace qfx {
+
+constexpr unsigned FULL_MASK = 0xffffffffu;
+
+template <int NQ>
+struct SvCfg {
+    static_assert(NQ >= 1 && NQ <= 10, "register-tiled statevector supports 1..10 qubits");
+    static constexpr int LB = (NQ <= 4) ? 0 : ((NQ <= 9) ? NQ - 4 : 5);
+    static constexpr int NL = NQ - LB;
+    static constexpr int A = 1 << NL;
+    static constexpr int LANES = 1 << LB;
+    static constexpr int DIM = 1 << NQ;
+};
+
+enum : int { BASIS_RX = 0, BASIS_RY = 1, BASIS_RZ = 2 };
+enum : int { ENT_CNOT = 0, ENT_CZ = 1, ENT_NONE = 2 };
+
+template <int NQ>
+struct Sv {
+    using C = SvCfg<NQ>;
+    float re[C::A], im[C::A];
+
+    // ---- initial states ------------------------------------------------------------
+    __device__ __forceinline__ void set_basis(int b, int lg) {
+#pragma unroll
+        for (int i = 0; i < C::A; ++i) {
+            re[i] = (((lg << C::NL) | i) == b) ? 1.0f : 0.0f;
+            im[i] = 0.0f;
+        }
+    }
+    // product state of one rotation per qubit on |0..0>; ang points at NQ floats
+    __device__ __forceinline__ void set_product(const float* __restrict__ ang, int basis, int lg) {
+#pragma unroll
+        for (int i = 0; i < C::A; ++i) { re[i] = 1.0f; im[i] = 0.0f; }
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+            float s, c;
+            sincosf(0.5f * ang[q], &s, &c);
+            // factor for bit 0: f0, for bit 1: f1 (complex)
+            float f0r, f0i, f1r, f1i;
+            if (basis == BASIS_RY)      { f0r = c; f0i = 0.f; f1r = s;   f1i = 0.f; }
+            else if (basis == BASIS_RX) { f0r = c; f0i = 0.f; f1r = 0.f; f1i = -s; }
+            else                        { f0r = c; f0i = -s;  f1r = 0.f; f1i = 0.f; }
+#pragma unroll
+            for (int i = 0; i < C::A; ++i) {
+                const bool bit = (q < C::NL) ? ((i >> q) & 1) : ((lg >> (q - C::NL)) & 1);
+                const float fr = bit ? f1r : f0r, fi = bit ? f1i : f0i;
+                const float r = re[i], m = im[i];
+                re[i] = r * fr - m * fi;
+                im[i] = r * fi + m * fr;
+            }
+        }
+    }
+    // real amplitude vector (amplitude encoding); src points at DIM floats, already normalised
+    __device__ __forceinline__ void set_real(const float* __restrict__ src, int lg) {
+#pragma unroll
+        for (int i = 0; i < C::A; ++i) { re[i] = src[(lg << C::NL) | i]; im[i] = 0.0f; }
+    }
+
+    // ---- single-qubit rotations (q is a compile-time constant after unrolling) -------
+    __device__ __forceinline__ void rx(int q, float c, float s, int lg) {
+        if (q < C::NL) {
+#pragma unroll
+            for (int i = 0; i < C::A; ++i) {
+                if (!((i >> q) & 1)) {
+                    const int j = i | (1 << q);
+                    const float r0 = re[i], i0 = im[i], r1 = re[j], i1 = im[j];
+                    re[i] = c * r0 + s * i1;  im[i] = c * i0 - s * r1;
+                    re[j] = c * r1 + s * i0;  im[j] = c * i1 - s * r0;
+                }
+            }
+        } else {
+            const int m = 1 << (q - C::NL);
+#pragma unroll
+            for (int i = 0; i < C::A; ++i) {
+                const float pr = __shfl_xor_sync(FULL_MASK, re[i], m);
+                const float pi = __shfl_xor_sync(FULL_MASK, im[i], m);
+                const float r0 = re[i], i0 = im[i];
+                re[i] = c * r0 + s * pi;
+                im[i] = c * i0 - s * pr;
+            }
+        }
+    }
+    __device__ __forceinline__ void ry(int q, float c, float s, int lg) {
+        if (q < C::NL) {
+#pragma unroll
+            for (int i = 0; i < C::A; ++i) {
+                if (!((i >> q) & 1)) {
+                    const int j = i | (1 << q);
+                    const float r0 = re[i], i0 = im[i], r1 = re[j], i1 = im[j];
+                    re[i] = c * r0 - s * r1;  im[i] = c * i0 - s * i1;
+                    re[j] = s * r0 + c * r1;  im[j] = s * i0 + c * i1;
+                }
+            }
+        } else {
+            const int m = 1 << (q - C::NL);
+            const float sg = ((lg >> (q - C::NL)) & 1) ? s : -s;
+#pragma unroll
+            for (int i = 0; i < C::A; ++i) {
+                const float pr = __shfl_xor_sync(FULL_MASK, re[i], m);
+                const float pi = __shfl_xor_sync(FULL_MASK, im[i], m);
+                re[i] = c * re[i] + sg * pr;
+                im[i] = c * im[i] + sg * pi;
+            }
+        }
+    }
+    __device__ __forceinline__ void rz(int q, float c, float s, int lg) {
+        // bit 0: *(c - i s); bit 1: *(c + i s)
+        const float s_lane = (q >= C::NL && ((lg >> (q - C::NL)) & 1)) ? -s : s;
+#pragma unroll
+        for (int i = 0; i < C::A; ++i) {
+            const float sg = (q < C::NL) ? (((i >> q) & 1) ? -s : s) : s_lane;
+            const float r = re[i], m = im[i];
+            re[i] = c * r + sg * m;
+            im[i] = c * m - sg * r;
+        }
+    }
+
+    // ---- entanglers -------------------------------------------------------------------
+    __device__ __forceinline__ void cnot(int ctl, int tgt, int lg) {
+        if (tgt < C::NL) {
+            const bool lane_ctl_on = (ctl >= C::NL) ? ((lg >> (ctl - C::NL)) & 1) : true;
+#pragma unroll
+            for (int i = 0; i < C::A; ++i) {
+                const bool ctl_local_on = (ctl < C::NL) ? ((i >> ctl) & 1) : true;
+                if (ctl_local_on && !((i >> tgt) & 1)) {
+                    const int j = i | (1 << tgt);
+                    if (ctl < C::NL) {  // static register rename
+                        float t = re[i]; re[i] = re[j]; re[j] = t;
+                        t = im[i]; im[i] = im[j]; im[j] = t;
+                    } else {
+                        const float ri = re[i], rj = re[j], ii = im[i], ij = im[j];
+                        re[i] = lane_ctl_on ? rj : ri;  re[j] = lane_ctl_on ? ri : rj;
+                        im[i] = lane_ctl_on ? ij : ii;  im[j] = lane_ctl_on ? ii : ij;
+                    }
+                }
+            }
+        } else {
+            const int m = 1 << (tgt - C::NL);
+            if (ctl < C::NL) {
+#pragma unroll
+                for (int i = 0; i < C::A; ++i) {
+                    if ((i >> ctl) & 1) {
+                        re[i] = __shfl_xor_sync(FULL_MASK, re[i], m);
+                        im[i] = __shfl_xor_sync(FULL_MASK, im[i], m);
+                    }
+                }
+            } else {
+                const bool on = (lg >> (ctl - C::NL)) & 1;
+#pragma unroll
+                for (int i = 0; i < C::A; ++i) {
+                    const float pr = __shfl_xor_sync(FULL_MASK, re[i], m);
+                    const float pi = __shfl_xor_sync(FULL_MASK, im[i], m);
+                    re[i] = on ? pr : re[i];
+                    im[i] = on ? pi : im[i];
+                }
+            }
+        }
+    }
+    __device__ __forceinline__ void cz(int a, int b, int lg) {
+        const bool lane_a = (a >= C::NL) ? ((lg >> (a - C::NL)) & 1) : true;
+        const bool lane_b = (b >= C::NL) ? ((lg >> (b - C::NL)) & 1) : true;
+#pragma unroll
+        for (int i = 0; i < C::A; ++i) {
+            const bool on_a = (a < C::NL) ? ((i >> a) & 1) : lane_a;
+            const bool on_b = (b < C::NL) ? ((i >> b) & 1) : lane_b;
+            if (on_a && on_b) { re[i] = -re[i]; im[i] = -im[i]; }
+        }
+    }
+    __device__ __forceinline__ void entangle(int ent, bool reverse, int lg) {
+        if (ent == ENT_NONE || NQ < 2) return;
+        if (NQ == 2) {
+            if (ent == ENT_CNOT) cnot(0, 1, lg); else cz(0, 1, lg);
+            return;
+        }
+#pragma unroll
+        for (int k = 0; k < NQ; ++k) {
+            const int q = reverse ? (NQ - 1 - k) : k;
+            const int t = (q + 1) % NQ;
+            if (ent == ENT_CNOT) cnot(q, t, lg); else cz(q, t, lg);
+        }
+    }
+
+    // ---- reductions --------------------------------------------------------------------
+    // <Z_q> for all qubits, reduced over the circuit's lanes; every lane gets the result
+    __device__ __forceinline__ void expval_z_all(float* __restrict__ ez /*[NQ]*/, int lg) const {
+        float p[C::A];
+        float tot = 0.f;
+#pragma unroll
+        for (int i = 0; i < C::A; ++i) { p[i] = re[i] * re[i] + im[i] * im[i]; tot += p[i]; }
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+            float v;
+            if (q < C::NL) {
+                v = 0.f;
+#pragma unroll
+                for (int i = 0; i < C::A; ++i) v += ((i >> q) & 1) ? -p[i] : p[i];
+            } else {
+                v = ((lg >> (q - C::NL)) & 1) ? -tot : tot;
+            }
+            ez[q] = group_sum<C::LANES>(v);
+        }
+    }
+    // lam = diag(sum_q cot[q] Z_q) * psi
+    __device__ __forceinline__ void set_obs_times(const Sv& psi, const float* __restrict__ cot, int lg) {
+        float lane_part = 0.f;
+#pragma unroll
+        for (int q = C::NL; q < NQ; ++q) lane_part += ((lg >> (q - C::NL)) & 1) ? -cot[q] : cot[q];
+#pragma unroll
+        for (int i = 0; i < C::A; ++i) {
+            float d = lane_part;
+#pragma unroll
+            for (int q = 0; q < C::NL; ++q) d += ((i >> q) & 1) ? -cot[q] : cot[q];
+            re[i] = d * psi.re[i];
+            im[i] = d * psi.im[i];
+        }
+    }
+};
+
+// Im <lam| Z_q |psi>, this lane's share
+template <int NQ>
+__device__ __forceinline__ float im_lam_z_psi(const Sv<NQ>& lam, const Sv<NQ>& psi, int q, int lg) {
+    using C = SvCfg<NQ>;
+    float acc = 0.f;
+#pragma unroll
+    for (int i = 0; i < C::A; ++i) {
+        const float t = lam.re[i] * psi.im[i] - lam.im[i] * psi.re[i];
+        const bool bit = (q < C::NL) ? ((i >> q) & 1) : ((lg >> (q - C::NL)) & 1);
+        acc += bit ? -t : t;
+    }
+    return acc;
+}
+
+// One reverse step through RX(theta) on qubit q: returns this lane's share of
+// Im <lam| X_q |psi> (evaluated after the gate) and replaces psi, lam by RX^dagger applied
+// to them.  For lane qubits the partner amplitudes are fetched once and used for both.
+template <int NQ>
+__device__ __forceinline__ float grad_and_undo_rx(Sv<NQ>& psi, Sv<NQ>& lam, int q, float c, float s, int lg) {
+    using C = SvCfg<NQ>;
+    float acc = 0.f;
+    if (q < C::NL) {
+#pragma unroll
+        for (int i = 0; i < C::A; ++i) {
+            if (!((i >> q) & 1)) {
+                const int j = i | (1 << q);
+                acc += lam.re[i] * psi.im[j] - lam.im[i] * psi.re[j];
+                acc += lam.re[j] * psi.im[i] - lam.im[j] * psi.re[i];
+            }
+        }
+        psi.rx(q, c, -s, lg);
+        lam.rx(q, c, -s, lg);
+    } else {
+        const int m = 1 << (q - C::NL);
+#pragma unroll
+        for (int i = 0; i < C::A; ++i) {
+            const float pr = __shfl_xor_sync(FULL_MASK, psi.re[i], m);
+            const float pi = __shfl_xor_sync(FULL_MASK, psi.im[i], m);
+            const float qr = __shfl_xor_sync(FULL_MASK, lam.re[i], m);
+            const float qi = __shfl_xor_sync(FULL_MASK, lam.im[i], m);
+            acc += lam.re[i] * pi - lam.im[i] * pr;
+            const float r0 = psi.re[i], i0 = psi.im[i];
+            psi.re[i] = c * r0 - s * pi;  psi.im[i] = c * i0 + s * pr;
+            const float l0 = lam.re[i], m0 = lam.im[i];
+            lam.re[i] = c * l0 - s * qi;  lam.im[i] = c * m0 + s * qr;
+        }
+    }
+    return acc;
+}
+
+// Im <lam| P_q |psi> for the feature-map generator (no undo needed: it is the first layer)
+template <int NQ>
+__device__ __forceinline__ float im_lam_p_psi(const Sv<NQ>& lam, const Sv<NQ>& psi, int basis, int q, int lg) {
+    using C = SvCfg<NQ>;
+    if (basis == BASIS_RZ) return im_lam_z_psi<NQ>(lam, psi, q, lg);
+    float acc = 0.f;
+    if (q < C::NL) {
+#pragma unroll
+        for (int i = 0; i < C::A; ++i) {
+            if (!((i >> q) & 1)) {
+                const int j = i | (1 << q);
+                if (basis == BASIS_RX) {
+                    acc += lam.re[i] * psi.im[j] - lam.im[i] * psi.re[j];
+                    acc += lam.re[j] * psi.im[i] - lam.im[j] * psi.re[i];
+                } else {  // Y
+                    acc -= lam.re[i] * psi.re[j] + lam.im[i] * psi.im[j];
+                    acc += lam.re[j] * psi.re[i] + lam.im[j] * psi.im[i];
+                }
+            }
+        }
+    } else {
+        const int m = 1 << (q - C::NL);
+        const bool bit = (lg >> (q - C::NL)) & 1;
+#pragma unroll
+        for (int i = 0; i < C::A; ++i) {
+            const float pr = __shfl_xor_sync(FULL_MASK, psi.re[i], m);
+            const float pi = __shfl_xor_sync(FULL_MASK, psi.im[i], m);
+            if (basis == BASIS_RX) {
+                acc += lam.re[i] * pi - lam.im[i] * pr;
+            } else {
+                const float t = lam.re[i] * pr + lam.im[i] * pi;
+                acc += bit ? t : -t;
+            }
+        }
+    }
+    return acc;
+}
+
+// ---- trig sources: where cos/sin(theta/2) come from ------------------------------------
+// Table in shared memory (one parameter group per CTA), with an optional +-pi/2 shift of one
+// parameter for the parameter-shift rule: theta/2 +- pi/4.
+struct TrigTable {
+    const float2* __restrict__ t;
+    int shift_p;       // -1: none
+    float shift_sign;  // +1 / -1
+    __device__ __forceinline__ float2 get(int p) const {
+        float2 v = t[p];
+        if (p == shift_p) {
+            const float k = 0.70710678118654752f;
+            const float c = (v.x - shift_sign * v.y) * k;
+            const float s = (v.y + shift_sign * v.x) * k;
+            v = make_float2(c, s);
+        }
+        return v;
+    }
+};
+// Straight from a parameter vector in global memory (circuits of mixed groups in one warp).
+struct TrigDirect {
+    const float* __restrict__ theta;
+    int shift_p;
+    float shift_sign;
+    __device__ __forceinline__ float2 get(int p) const {
+        float a = 0.5f * theta[p];
+        if (p == shift_p) a += shift_sign * 0.78539816339744831f;
+        float s, c;
+        sincosf(a, &s, &c);
+        return make_float2(c, s);
+    }
+};
+
+// ---- ansatz sweeps ---------------------------------------------------------------------
+template <int NQ, class Trig>
+__device__ __forceinline__ void ansatz_forward(Sv<NQ>& psi, const Trig& trig, int n_layers, int ent, int lg) {
+    for (int l = 0; l < n_layers; ++l) {
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+            const float2 a = trig.get((l * NQ + q) * 2 + 0);
+            psi.rx(q, a.x, a.y, lg);
+            const float2 b = trig.get((l * NQ + q) * 2 + 1);
+            psi.rz(q, b.x, b.y, lg);
+        }
+        psi.entangle(ent, false, lg);
+    }
+}
+
+// Reverse sweep.  sink(p, v) receives this lane's share of d<O>/d theta_p.
+template <int NQ, class Trig, class Sink>
+__device__ __forceinline__ void ansatz_backward(Sv<NQ>& psi, Sv<NQ>& lam, const Trig& trig, int n_layers, int ent,
+                                                int lg, Sink& sink) {
+    for (int l = n_layers - 1; l >= 0; --l) {
+        psi.entangle(ent, true, lg);
+        lam.entangle(ent, true, lg);
+#pragma unroll
+        for (int k = 0; k < NQ; ++k) {
+            const int q = NQ - 1 - k;
+            const int p = (l * NQ + q) * 2;
+            const float2 b = trig.get(p + 1);
+            sink(p + 1, im_lam_z_psi<NQ>(lam, psi, q, lg));
+            psi.rz(q, b.x, -b.y, lg);
+            lam.rz(q, b.x, -b.y, lg);
+            const float2 a = trig.get(p);
+            sink(p, grad_and_undo_rx<NQ>(psi, lam, q, a.x, a.y, lg));
+        }
+    }
+}
+
+}  // namespace qfx

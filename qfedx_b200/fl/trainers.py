@@ -1,0 +1,192 @@
+"""Local-training engines.  A trainer turns (global flat parameters, selected clients, round) into
+the matrix of client parameters [K_sel, D] that the aggregation consumes.
+
+* ``TorchLocalTrainer``  - any ``nn.Module``; sequential clients, fresh optimizer per round,
+  full passes over shuffled minibatches: the semantics of the reference's client_update
+  (/root/reference/src/CFed/Classical_FL.py:40-64).  CPU path, numerics reference, and baseline.
+* ``VQCFusedTrainer``    - all selected clients in ONE launch of csrc/vqc_train.cu on CUDA
+  (one thread-block cluster per client); on CPU it defers to ``TorchLocalTrainer``.
+"""
+from __future__ import annotations
+
+import copy
+from typing import Callable, Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from ..models.tinycnn import flatten_state, unflatten_state
+from ..models.vqc import VQC
+from ..ops import _lib
+from ..ops.statevector import BASIS, ENTANGLER
+from .dataset import FederatedDataset
+from .spsa import spsa_gradient
+
+OPTIMIZERS = {"sgd": 0, "adam": 1}
+
+
+def make_optimizer(params, name: str, lr: float, momentum: float = 0.9, betas=(0.9, 0.999), eps: float = 1e-8):
+    if name == "sgd":
+        return torch.optim.SGD(params, lr=lr, momentum=momentum)
+    if name == "adam":
+        return torch.optim.Adam(params, lr=lr, betas=betas, eps=eps)
+    raise ValueError(f"unknown optimizer {name!r}")
+
+
+class TorchLocalTrainer:
+    def __init__(self, model: nn.Module, data: FederatedDataset, loss_fn: Optional[Callable] = None,
+                 epochs: int = 5, batch_size: int = 32, lr: float = 0.01, optimizer: str = "sgd",
+                 momentum: float = 0.9, n_wrap: int = 0, grad_estimator: str = "backprop", spsa_c: float = 0.1,
+                 generator=None):
+        self.model, self.data = model, data
+        self.loss_fn = loss_fn or (model.loss if hasattr(model, "loss") else nn.CrossEntropyLoss())
+        self.epochs, self.batch_size, self.lr = epochs, batch_size, lr
+        self.optimizer, self.momentum = optimizer, momentum
+        self.n_wrap = n_wrap
+        self.grad_estimator, self.spsa_c = grad_estimator, spsa_c
+        self.generator = generator
+        self._template = copy.deepcopy(model.state_dict())
+        self.launches = 0
+
+    @property
+    def dim(self) -> int:
+        return sum(v.numel() for v in self._template.values())
+
+    @property
+    def weights(self) -> torch.Tensor:
+        return torch.as_tensor(self.data.sizes, dtype=torch.float32)
+
+    def global_flat(self) -> torch.Tensor:
+        return flatten_state(self.model.state_dict())
+
+    def load_flat(self, flat: torch.Tensor) -> None:
+        self.model.load_state_dict(unflatten_state(flat, self._template))
+
+    def _train_one(self, flat: torch.Tensor, k: int) -> tuple:
+        self.load_flat(flat)
+        self.model.train()
+        Xk, yk = self.data.client(k)
+        opt = make_optimizer(self.model.parameters(), self.optimizer, self.lr, self.momentum)
+        last_loss, n = 0.0, len(Xk)
+        for _ in range(self.epochs):
+            order = torch.randperm(n, device=Xk.device, generator=self.generator)
+            tot = 0.0
+            for lo in range(0, n, self.batch_size):
+                idx = order[lo:lo + self.batch_size]
+                xb, yb = Xk[idx], yk[idx]
+                opt.zero_grad(set_to_none=True)
+                if self.grad_estimator == "spsa":
+                    loss = spsa_gradient(self.model, lambda: self.loss_fn(self.model(xb), yb), self.spsa_c)
+                else:
+                    loss = self.loss_fn(self.model(xb), yb)
+                    loss.backward()
+                opt.step()
+                tot += float(loss.detach()) * len(idx)
+            last_loss = tot / max(n, 1)
+        return flatten_state(self.model.state_dict()).clone(), last_loss
+
+    def train(self, global_flat: torch.Tensor, selected, rnd: int):
+        rows, losses = [], []
+        for k in selected:
+            f, l = self._train_one(global_flat, int(k))
+            rows.append(f)
+            losses.append(l)
+        self.load_flat(global_flat)
+        return torch.stack(rows), {"train_loss": float(np.mean(losses)) if losses else 0.0}
+
+    @torch.no_grad()
+    def evaluate(self, global_flat: torch.Tensor, X: torch.Tensor, y: torch.Tensor, batch_size: int = 256):
+        self.load_flat(global_flat)
+        self.model.eval()
+        tot_loss, correct = 0.0, 0
+        for lo in range(0, len(X), batch_size):
+            xb, yb = X[lo:lo + batch_size], y[lo:lo + batch_size]
+            z = self.model(xb)
+            tot_loss += float(self.loss_fn(z, yb)) * len(xb)
+            pred = (z[:, 0] > 0).long() if z.shape[1] == 1 else z.argmax(1)
+            correct += int((pred == yb).sum())
+        return tot_loss / len(X), correct / len(X)
+
+
+class VQCFusedTrainer:
+    """All selected clients train in one kernel launch (CUDA); see csrc/vqc_train.cu."""
+
+    def __init__(self, model: VQC, data: FederatedDataset, epochs: int = 5, batch_size: int = 32,
+                 lr: float = 0.05, optimizer: str = "adam", momentum: float = 0.9, betas=(0.9, 0.999),
+                 eps: float = 1e-8, grad_method: str = "adjoint", cluster_size: int = 0, shuffle: bool = True,
+                 generator=None):
+        if model.encoding != "angle":
+            raise ValueError("the fused trainer takes angle-encoded features")
+        self.model, self.data = model, data
+        self.epochs, self.batch_size, self.lr = epochs, batch_size, lr
+        self.optimizer, self.momentum, self.betas, self.eps = optimizer, momentum, betas, eps
+        self.grad_method, self.shuffle, self.generator = grad_method, shuffle, generator
+        self.n_wrap = model.n_angle_params
+        self.cuda = data.device.type == "cuda"
+        self.launches = 0
+        if self.cuda:
+            self.angles = data.X.contiguous().float()
+            self.labels = data.y.to(torch.int32).contiguous()
+            lanes = 1 << max(0, min(model.n_qubits - 4, 5)) if model.n_qubits <= 9 else 32
+            slots = 256 // lanes
+            if cluster_size <= 0:  # enough CTAs to cover one minibatch in a single pass, at most 8
+                cluster_size = 1
+                while cluster_size < 8 and slots * cluster_size < batch_size:
+                    cluster_size *= 2
+            self.cluster_size = cluster_size
+            self._out = None
+        else:
+            self._fallback = TorchLocalTrainer(model, data, None, epochs, batch_size, lr, optimizer, momentum,
+                                               n_wrap=self.n_wrap, generator=generator)
+
+    @property
+    def dim(self) -> int:
+        return self.model.n_angle_params + 2 * self.model.n_logits
+
+    @property
+    def weights(self) -> torch.Tensor:
+        return torch.as_tensor(self.data.sizes, dtype=torch.float32)
+
+    def global_flat(self) -> torch.Tensor:
+        return self.model.flat_params().to(self.data.device)
+
+    def load_flat(self, flat):
+        self.model.load_flat_params(flat)
+
+    def train(self, global_flat: torch.Tensor, selected, rnd: int):
+        if not self.cuda:
+            return self._fallback.train(global_flat, selected, rnd)
+        m = self.model
+        sel = torch.as_tensor(np.asarray(selected), dtype=torch.int32, device=self.angles.device)
+        K = sel.numel()
+        out = torch.empty(K, self.dim, device=self.angles.device, dtype=torch.float32)
+        stats = torch.empty(K, 2, device=self.angles.device, dtype=torch.float32)
+        perm = self.data.epoch_permutations(self.epochs, self.generator) if self.shuffle else None
+        beta1 = self.momentum if self.optimizer == "sgd" else self.betas[0]
+        g = global_flat.contiguous().float()
+        _lib.call("qfx_vqc_local_train", _lib.c_int(m.n_qubits), _lib.c_int(m.n_layers), _lib.c_int(BASIS[m.basis]),
+                  _lib.c_int(ENTANGLER[m.entangler]), _lib.c_int(m.n_logits), _lib.ptr(self.angles),
+                  _lib.ptr(self.labels), _lib.ptr(self.data.offsets), _lib.ptr(perm),
+                  _lib.c_int(self.angles.shape[0]), _lib.ptr(g), _lib.ptr(sel), _lib.c_int(K), _lib.ptr(out),
+                  _lib.ptr(stats), _lib.c_int(self.epochs), _lib.c_int(self.batch_size),
+                  _lib.c_int(OPTIMIZERS[self.optimizer]), _lib.c_float(self.lr), _lib.c_float(beta1),
+                  _lib.c_float(self.betas[1]), _lib.c_float(self.eps),
+                  _lib.c_int(0 if self.grad_method == "adjoint" else 1), _lib.c_int(self.cluster_size),
+                  _lib.stream_ptr())
+        self.launches += 1
+        self._last_stats = stats
+        return out, {"train_stats": stats}
+
+    def evaluate(self, global_flat: torch.Tensor, X: torch.Tensor, y: torch.Tensor, batch_size: int = 0):
+        if not self.cuda:
+            return self._fallback.evaluate(global_flat, X, y)
+        m = self.model
+        out2 = torch.empty(2, device=X.device, dtype=torch.float32)
+        _lib.call("qfx_vqc_eval", _lib.c_int(m.n_qubits), _lib.c_int(m.n_layers), _lib.c_int(BASIS[m.basis]),
+                  _lib.c_int(ENTANGLER[m.entangler]), _lib.c_int(m.n_logits), _lib.ptr(X.contiguous().float()),
+                  _lib.ptr(y.to(torch.int32).contiguous()), _lib.ptr(global_flat.contiguous().float()),
+                  _lib.c_int(X.shape[0]), _lib.ptr(out2), _lib.stream_ptr())
+        self.launches += 1
+        res = out2.cpu()  # the round's single host sync
+        return float(res[0]) / X.shape[0], float(res[1]) / X.shape[0]

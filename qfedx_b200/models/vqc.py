@@ -1,0 +1,73 @@
+"""Variational quantum classifier as an ``nn.Module`` with an ordinary ``state_dict``.
+
+Feature map RY(x_i) (x already scaled to angles, e.g. pi * minmax(features), the mapping of
+/root/reference/src/QFed/qAngle.py:35-41) or an amplitude-encoded input state
+(/root/reference/src/QFed/qAmplitude.py:25-41); hardware-efficient ansatz of L layers
+[RX(theta) RZ(phi) per qubit + CNOT/CZ ring]; readout <Z_j> on qubit j for j < C;
+``logit_j = a_j <Z_j> + b_j`` (/root/reference/ROADMAP.md:126-128).  C = 1 is the binary
+classifier (BCE-with-logits), C > 1 uses softmax cross-entropy.
+
+On CUDA the forward/backward run on the register-tiled sm_100a kernels through
+``qfedx_b200.ops.statevector``; ``grad_method`` selects adjoint (K4a) or parameter shift (K4b).
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from ..ops import statevector as _sv
+
+
+class VQC(nn.Module):
+    def __init__(self, n_qubits: int = 4, n_layers: int = 2, num_classes: int = 2, basis: str = "ry",
+                 entangler: str = "cnot", encoding: str = "angle", grad_method: str = "adjoint",
+                 init_scale: float = 0.1):
+        super().__init__()
+        self.n_qubits, self.n_layers = n_qubits, n_layers
+        self.n_logits = 1 if num_classes <= 2 else num_classes
+        if self.n_logits > n_qubits:
+            raise ValueError(f"{num_classes} classes need at least {self.n_logits} readout qubits")
+        self.num_classes = num_classes
+        self.basis, self.entangler, self.encoding, self.grad_method = basis, entangler, encoding, grad_method
+        self.theta = nn.Parameter(init_scale * torch.randn(n_layers, n_qubits, 2))
+        self.readout_scale = nn.Parameter(torch.ones(self.n_logits))
+        self.readout_bias = nn.Parameter(torch.zeros(self.n_logits))
+
+    # flat layout used by the fused kernels: [theta | a | b]
+    @property
+    def n_angle_params(self) -> int:
+        return self.theta.numel()
+
+    def flat_params(self) -> torch.Tensor:
+        return torch.cat([self.theta.detach().reshape(-1), self.readout_scale.detach(), self.readout_bias.detach()])
+
+    def load_flat_params(self, flat: torch.Tensor) -> None:
+        p, c = self.theta.numel(), self.n_logits
+        with torch.no_grad():
+            self.theta.copy_(flat[:p].reshape(self.theta.shape))
+            self.readout_scale.copy_(flat[p:p + c])
+            self.readout_bias.copy_(flat[p + c:p + 2 * c])
+
+    def expvals(self, x: torch.Tensor) -> torch.Tensor:
+        if self.encoding == "amplitude":
+            return _sv.vqc_expvals(None, self.theta, None, self.basis, self.entangler, init_state=x,
+                                   method=self.grad_method)
+        return _sv.vqc_expvals(x, self.theta, None, self.basis, self.entangler, method=self.grad_method)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        """x: [B, n] feature-map angles (or [B, 2^n] unit-norm amplitudes) -> logits [B, n_logits]."""
+        E = self.expvals(x)
+        return self.readout_scale * E[:, : self.n_logits] + self.readout_bias
+
+    def loss(self, logits: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        if self.n_logits == 1:
+            return F.binary_cross_entropy_with_logits(logits[:, 0], y.float())
+        return F.cross_entropy(logits, y)
+
+    @torch.no_grad()
+    def predict(self, x: torch.Tensor) -> torch.Tensor:
+        z = self.forward(x)
+        return (z[:, 0] > 0).long() if self.n_logits == 1 else z.argmax(1)
