@@ -1,0 +1,356 @@
+#!/usr/bin/env python
+"""Benchmark driver contract: ``python bench.py --gpus N --steps K --warmup W [--impl reference]``.
+
+One "step" is one federated round (all clients train locally, the server aggregates, the global
+model is evaluated).  The headline metric is FL rounds/sec (BASELINE.json: "FL rounds/sec +
+statevector gates/sec"), strong scaling: the job (number of clients, samples, epochs) is fixed
+and spread over N GPUs, clients mapped to ranks.
+
+Configs (``--config``):
+  cfed  (default) classical TinyCNN FedAvg, 8 clients x 4,190 MNIST-shape samples, 5 local epochs,
+        batch 32, SGD(0.01, momentum 0.9) - the reference's only runnable training benchmark
+        (/root/reference/src/CFed/Classical_FL.py:161-173; BASELINE.json config 2); ours adds DP
+        clip + Gaussian noise inside the fused aggregation.
+  vqc8  8-qubit 6-layer VQC, 64 clients, Dirichlet non-IID split (BASELINE.json config 3).
+  vqc4  4-qubit 2-layer binary VQC, 4 clients (BASELINE.json config 1).
+The line's ``aux`` carries the secondary numbers measured in the same run.
+
+``--impl reference`` runs the UNMODIFIED reference from baseline/_ref through its own
+``federated_learning`` on the same job.  The reference is single-process and single-device
+(/root/reference/src/CFed/Classical_FL.py:19), so under torchrun rank 0 runs the whole job and
+the other ranks only take part in the barriers.  Two adapters, neither touching its math
+(SURVEY.md 0.2): client arrays are handed over as torch tensors with int64 labels (as shipped it
+crashes on NumPy input), and ``matplotlib`` (not installed; imported by its Preprocess module for
+plots that are never drawn here) is satisfied by an empty stand-in module.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+import types
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CFED = dict(clients=8, samples_per_client=4190, classes=3, epochs=5, batch=32, lr=0.01, test_n=3147,
+            clip=5.0, sigma=0.01)
+VQC8 = dict(clients=64, n_train=16760, classes=3, n_qubits=8, n_layers=6, epochs=5, batch=32, lr=0.05,
+            alpha=0.5, test_n=3147)
+VQC4 = dict(clients=4, n_train=11183, classes=2, n_qubits=4, n_layers=2, epochs=5, batch=32, lr=0.05, test_n=1991)
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    return rank, world, local
+
+
+def init_dist(world, local):
+    import torch.distributed as dist
+    if torch.cuda.is_available():
+        torch.cuda.set_device(local)
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        dist.init_process_group("nccl" if torch.cuda.is_available() else "gloo",
+                                device_id=torch.device("cuda", local) if torch.cuda.is_available() else None)
+    return dist
+
+
+def barrier(world):
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    if torch.cuda.is_available():
+        torch.cuda.synchronize()
+
+
+def timed_rounds(step_fn, steps, warmup, world, flush=True):
+    """W untimed steps, then exactly K steps between CUDA events, max over ranks; returns ms/step."""
+    from qfedx_b200.utils.timing import ClockSampler, flush_l2, max_over_ranks
+    for _ in range(warmup):
+        step_fn()
+    barrier(world)
+    cuda = torch.cuda.is_available()
+    sampler = ClockSampler(torch.cuda.current_device() if cuda else 0)
+    with sampler:
+        if cuda:
+            evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+            for s, e in evs:
+                if flush:
+                    flush_l2()
+                s.record()
+                step_fn()
+                e.record()
+            barrier(world)
+            total_ms = sum(s.elapsed_time(e) for s, e in evs)
+        else:
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                step_fn()
+            total_ms = (time.perf_counter() - t0) * 1e3
+    total_ms = max_over_ranks(total_ms)
+    return total_ms / steps, sampler.summary()
+
+
+def split_clients(n_clients, rank, world):
+    per = (n_clients + world - 1) // world
+    return list(range(rank * per, min(n_clients, (rank + 1) * per)))
+
+
+# --------------------------------------------------------------------------------------------
+# data
+def cfed_data(cfg, seed=0):
+    from qfedx_b200.data import synthetic_mnist
+    n = cfg["clients"] * cfg["samples_per_client"]
+    X, y = synthetic_mnist(n, cfg["classes"], seed=seed)
+    Xt, yt = synthetic_mnist(cfg["test_n"], cfg["classes"], seed=seed + 1)
+    per = cfg["samples_per_client"]
+    clients = [(X[k * per:(k + 1) * per], y[k * per:(k + 1) * per]) for k in range(cfg["clients"])]
+    return clients, (Xt, yt)
+
+
+def vqc_data(cfg, seed=0, non_iid=True):
+    import random
+    from qfedx_b200.data import images_to_angles, partition, synthetic_mnist
+    random.seed(seed); np.random.seed(seed)
+    X, y = synthetic_mnist(cfg["n_train"], cfg["classes"], seed=seed)
+    Xt, yt = synthetic_mnist(cfg["test_n"], cfg["classes"], seed=seed + 1)
+    A, At = images_to_angles(X, cfg["n_qubits"]), images_to_angles(Xt, cfg["n_qubits"])
+    clients = partition(A, y, cfg["clients"], "non_iid" if non_iid else "iid", cfg.get("alpha", 0.5))
+    clients = [(a, b) if len(a) else (A[:1], y[:1]) for a, b in clients]  # Dirichlet can leave a client empty
+    return clients, (At, yt)
+
+
+# --------------------------------------------------------------------------------------------
+# our arm
+def run_vqc(cfg, name, args, rank, world, local):
+    from qfedx_b200.fl import FederatedDataset, FederatedRunner, FLConfig, VQCFusedTrainer
+    from qfedx_b200.models import VQC
+    from qfedx_b200.ops import _lib
+    from qfedx_b200.parallel.runtime import make_aggregator
+    dev = torch.device("cuda", local) if torch.cuda.is_available() else torch.device("cpu")
+    clients, test = vqc_data(cfg, non_iid=(name == "vqc8"))
+    mine = split_clients(len(clients), rank, world)
+    host = [(clients[k][0].float().contiguous(), clients[k][1].long().contiguous()) for k in mine]
+    data = FederatedDataset.from_clients(host, dev)
+    torch.manual_seed(0)
+    model = VQC(cfg["n_qubits"], cfg["n_layers"], cfg["classes"]).to(dev)
+    trainer = VQCFusedTrainer(model, data, cfg["epochs"], cfg["batch"], cfg["lr"], "adam",
+                              lane_mode=os.environ.get("QFX_LANE_MODE", "latency"),
+                              cluster_size=int(os.environ.get("QFX_CLUSTER", "0")))
+    all_sizes = torch.tensor([len(c[0]) for c in clients], dtype=torch.float32)
+    flc = FLConfig(num_rounds=10 ** 9, mode="delta", quiet=True)
+    agg = make_aggregator(rank, world, mine, all_sizes, trainer.dim, dev)
+    runner = FederatedRunner(trainer, flc, (test[0].to(dev), test[1].to(dev)), aggregator=agg,
+                             client_gids=mine if agg is not None else None,
+                             global_weights=all_sizes if agg is not None else None)
+    result = {}
+
+    def step():
+        runner.run_round()
+        result["eval"] = runner.evaluate()
+
+    l0 = _lib.LAUNCH_COUNT
+    ms, clocks = timed_rounds(step, args.steps, args.warmup, world)
+    launches = (_lib.LAUNCH_COUNT - l0) // max(1, args.steps + args.warmup) * args.steps
+
+    # end to end: the round's client data goes pinned host -> device every round, the metric comes back
+    pin = dev.type == "cuda"
+    hX = torch.cat([h[0] for h in host]); hy = torch.cat([h[1] for h in host]).to(torch.int32)
+    if pin:
+        hX, hy = hX.pin_memory(), hy.pin_memory()
+
+    def step_e2e():
+        trainer.angles.copy_(hX, non_blocking=True)
+        trainer.labels.copy_(hy, non_blocking=True)
+        runner.run_round()
+        result["eval"] = runner.evaluate()  # .cpu() inside: the device -> host read of the result
+
+    if dev.type == "cuda":
+        e2e_ms, _ = timed_rounds(step_e2e, args.steps, 1, world)
+    else:
+        e2e_ms = ms
+    h2d = (hX.numel() * 4 + hy.numel() * 4) * world
+    return dict(ms=ms, e2e_ms=e2e_ms, clocks=clocks, launches=launches, h2d=h2d, d2h=8,
+                model=f"VQC {cfg['n_qubits']}q x {cfg['n_layers']} layers, {cfg['classes']} classes",
+                clients=len(clients), samples=int(all_sizes.sum()), eval=result.get("eval"),
+                extra={"local_epochs": cfg["epochs"], "batch": cfg["batch"], "optimizer": "adam",
+                       "partition": "dirichlet(0.5)" if name == "vqc8" else "iid"})
+
+
+def run_cfed(cfg, args, rank, world, local):
+    from qfedx_b200.fl import FederatedDataset, FederatedRunner, FLConfig
+    from qfedx_b200.fl.trainers_cnn import TinyCNNBatchedTrainer
+    from qfedx_b200.models import TinyCNN
+    from qfedx_b200.ops import _lib
+    from qfedx_b200.parallel.runtime import make_aggregator
+    dev = torch.device("cuda", local)
+    clients, test = cfed_data(cfg)
+    mine = split_clients(len(clients), rank, world)
+    host = [(clients[k][0].contiguous(), clients[k][1].long().contiguous()) for k in mine]
+    data = FederatedDataset.from_clients(host, dev)
+    torch.manual_seed(0)
+    model = TinyCNN(cfg["classes"]).to(dev)
+    trainer = TinyCNNBatchedTrainer(model, data, cfg["epochs"], cfg["batch"], cfg["lr"])
+    all_sizes = torch.tensor([len(c[0]) for c in clients], dtype=torch.float32)
+    flc = FLConfig(num_rounds=10 ** 9, mode="delta", clip=cfg["clip"], sigma=cfg["sigma"], quiet=True)
+    agg = make_aggregator(rank, world, mine, all_sizes, trainer.dim, dev)
+    runner = FederatedRunner(trainer, flc, (test[0].to(dev), test[1].to(dev)), aggregator=agg,
+                             client_gids=mine if agg is not None else None,
+                             global_weights=all_sizes if agg is not None else None)
+    result = {}
+
+    def step():
+        runner.run_round()
+        result["eval"] = runner.evaluate()
+
+    l0 = _lib.LAUNCH_COUNT
+    ms, clocks = timed_rounds(step, args.steps, args.warmup, world)
+    launches = (_lib.LAUNCH_COUNT - l0) // max(1, args.steps + args.warmup) * args.steps
+    hX = torch.cat([h[0] for h in host]).pin_memory()
+    hy = torch.cat([h[1] for h in host]).to(torch.int32).pin_memory()
+
+    def step_e2e():
+        trainer.upload(hX, hy)
+        runner.run_round()
+        result["eval"] = runner.evaluate()
+
+    e2e_ms, _ = timed_rounds(step_e2e, args.steps, 1, world)
+    return dict(ms=ms, e2e_ms=e2e_ms, clocks=clocks, launches=launches,
+                h2d=(hX.numel() * 4 + hy.numel() * 4) * world, d2h=8,
+                model="TinyCNN (113,859 params) FedAvg + DP clip/noise", clients=len(clients),
+                samples=int(all_sizes.sum()), eval=result.get("eval"),
+                extra={"local_epochs": cfg["epochs"], "batch": cfg["batch"], "optimizer": "sgd(0.01, m=0.9)",
+                       "dp": {"clip": cfg["clip"], "sigma": cfg["sigma"]}})
+
+
+# --------------------------------------------------------------------------------------------
+# reference arm
+def run_reference(cfg, args, rank, world, local):
+    ref_dir = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.exists(os.path.join(ref_dir, "Classical_FL.py")):
+        return {"impl": "reference", "unavailable": "baseline/_ref is not installed (see DESIGN.md, reference arm)"}
+    if args.config != "cfed":
+        return {"impl": "reference",
+                "unavailable": f"the reference has no code for config {args.config!r}: no VQC, no simulator loop "
+                               "(SURVEY.md 0.3); only --config cfed is runnable"}
+    for name in ("matplotlib", "matplotlib.pyplot"):  # imported by its Preprocess.py for plots never drawn here
+        sys.modules.setdefault(name, types.ModuleType(name))
+    sys.modules["matplotlib"].pyplot = sys.modules["matplotlib.pyplot"]
+    sys.path.insert(0, ref_dir)
+    import contextlib
+    import io
+    import Classical_FL as ref  # the unmodified reference module
+    clients, test = cfed_data(cfg)
+    # adapter: tensors + int64 labels; data starts on the host like the reference's
+    client_data = [(X.clone(), y.long().clone()) for X, y in clients]
+    ms = 0.0
+    clocks = {}
+    acc = None
+    if rank == 0:
+        def run(n_rounds):
+            with contextlib.redirect_stdout(io.StringIO()):
+                return ref.federated_learning(client_data, test, num_rounds=n_rounds, local_epochs=cfg["epochs"],
+                                              learning_rate=cfg["lr"], batch_size=cfg["batch"],
+                                              num_classes=cfg["classes"])
+        from qfedx_b200.utils.timing import ClockSampler
+        if args.warmup:
+            run(args.warmup)
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sampler = ClockSampler(torch.cuda.current_device())
+        with sampler:
+            s.record()
+            out = run(args.steps)
+            e.record()
+            torch.cuda.synchronize()
+        ms = s.elapsed_time(e) / args.steps
+        clocks = sampler.summary()
+        acc = out["accuracies"][-1]
+    barrier(world)
+    from qfedx_b200.utils.timing import max_over_ranks
+    ms = max_over_ranks(ms)
+    per_round_h2d = sum(X.numel() * 4 + y.numel() * 8 for X, y in client_data) + test[0].numel() * 4 + test[1].numel() * 8
+    return dict(ms=ms, e2e_ms=ms, clocks=clocks, launches=None, h2d=per_round_h2d, d2h=8 * 13,
+                model="TinyCNN (113,859 params) FedAvg, reference stock loop", clients=len(clients),
+                samples=sum(len(c[0]) for c in clients), eval=(None, acc),
+                extra={"local_epochs": cfg["epochs"], "batch": cfg["batch"], "optimizer": "sgd(0.01, m=0.9)",
+                       "note": "single-process single-device reference: rank 0 runs every client sequentially"})
+
+
+# --------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="cfed", choices=["cfed", "vqc8", "vqc4"])
+    ap.add_argument("--no-aux", action="store_true", help="skip the secondary measurements")
+    args = ap.parse_args()
+    rank, world, local = dist_env()
+    init_dist(world, local)
+    cfgs = {"cfed": CFED, "vqc8": VQC8, "vqc4": VQC4}
+    cfg = dict(cfgs[args.config])
+    if os.environ.get("QFX_BENCH_SCALE"):  # shrink the job for smoke runs
+        f = float(os.environ["QFX_BENCH_SCALE"])
+        for k in ("samples_per_client", "n_train", "test_n"):
+            if k in cfg:
+                cfg[k] = max(64, int(cfg[k] * f))
+
+    if args.impl == "reference":
+        r = run_reference(cfg, args, rank, world, local)
+        if "unavailable" in r:
+            if rank == 0:
+                print(json.dumps(r))
+            return
+    elif args.config == "cfed":
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py --config cfed needs a GPU (the client-batched CUDA path)")
+        r = run_cfed(cfg, args, rank, world, local)
+    else:
+        r = run_vqc(cfg, args.config, args, rank, world, local)
+
+    aux = {}
+    if args.impl == "ours" and not args.no_aux and torch.cuda.is_available():
+        try:
+            from qfedx_b200.benchmarks import aux_measurements
+            aux = aux_measurements(args, rank, world, local, skip=args.config)
+        except Exception as exc:  # the headline must not die because a secondary number did
+            aux = {"error": f"{type(exc).__name__}: {exc}"}
+
+    if rank == 0:
+        value = 1000.0 / r["ms"]
+        line = {
+            "metric": "fl_rounds_per_sec", "value": value, "unit": "rounds/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms"], "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "fp32" if args.config != "cfed" or args.impl == "reference" else "bf16",
+            "data": "synthetic MNIST-shape images, random-init weights",
+            "impl": args.impl,
+            "config": {"name": args.config, "model": r["model"], "clients": r["clients"], "global_batch": r["samples"],
+                       "seq_len": None, "parallelism": f"client-parallel x{world}", "l2": "flushed between rounds",
+                       **r["extra"]},
+            "clocks": r["clocks"],
+            "e2e": {"value": 1000.0 / r["e2e_ms"], "unit": "rounds/s", "h2d_bytes_per_step": r["h2d"],
+                    "d2h_bytes_per_step": r["d2h"]},
+            "gpu_launches": r["launches"],
+            "final_eval": {"loss": r["eval"][0], "accuracy": r["eval"][1]} if r.get("eval") else None,
+            "aux": aux,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

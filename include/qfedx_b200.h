@@ -57,6 +57,7 @@ int qfx_sv_param_shift(int n_qubits, int n_layers, int basis, int entangler, con
  * [theta (2nL) | a (C) | b (C)], logits_j = a_j <Z_j> + b_j, C = 1 -> BCE, C > 1 -> softmax CE.
  * angles [N,n], labels [N], offsets [K+1], perm [epochs,N] (nullable), client_ids [n_selected],
  * params_out [n_selected, D], stats_out [n_selected, 2] (mean loss, accuracy of the last epoch).
+ * lane_mode 0 keeps most amplitudes per lane (throughput), 1 spreads a circuit over most lanes (latency).
  * Counterpart of client_update, /root/reference/src/CFed/Classical_FL.py:40-64, for the VQC of
  * /root/reference/ROADMAP.md:29-43. */
 int qfx_vqc_local_train(int n_qubits, int n_layers, int basis, int entangler, int n_classes,
@@ -64,7 +65,7 @@ int qfx_vqc_local_train(int n_qubits, int n_layers, int basis, int entangler, in
                         int n_total, const float* params_in, const int* client_ids, int n_selected,
                         float* params_out, float* stats_out, int epochs, int batch_size, int optimizer,
                         float lr, float beta1, float beta2, float eps, int grad_mode, int cluster_size,
-                        cudaStream_t stream);
+                        int lane_mode, cudaStream_t stream);
 
 /* Evaluation in one launch: out2[0] = sum of losses, out2[1] = number correct.
  * Counterpart of evaluate_model, /root/reference/src/CFed/Classical_FL.py:83-102. */
@@ -95,6 +96,34 @@ int qfx_fedavg_fused_multi(const float* client_params, const float* global_in, f
                            unsigned long long seed, int round, int secagg, float* norms_out, float* scratch,
                            int rank, int world, long long* const* recv_slots, unsigned int* const* flags,
                            unsigned int epoch, cudaStream_t stream);
+
+/* Symmetric heap (no reference counterpart - the reference has no communication layer):
+ * allocate + zero a device buffer and export its 64-byte CUDA IPC handle; map a peer's handle; unmap;
+ * free.  Handles are exchanged by the caller (torch.distributed object all-gather). */
+int qfx_symm_alloc(size_t bytes, void** ptr, unsigned char* handle64);
+int qfx_symm_open(const unsigned char* handle64, void** ptr);
+int qfx_symm_close(void* ptr);
+int qfx_symm_free(void* ptr);
+int qfx_enable_peer(int dev, int peer);
+
+/* K8: TinyCNN (the reference's model, /root/reference/src/CFed/Classical_FL.py:21-38) trained for
+ * all selected clients at once.  One call = one SGD-momentum step of client_update
+ * (/root/reference/src/CFed/Classical_FL.py:56-62) for every client: 9 kernels on `stream`, meant to
+ * be captured in a CUDA graph.  params/moment are [n_selected, nd] rows in state_dict order;
+ * batch_size <= 32; clients whose data is exhausted at (epoch, batch_index) are skipped.
+ * workspace: qfx_tinycnn_workspace_bytes; its tail (qfx_tinycnn_stats_offset) holds per-client
+ * (loss sum, #correct) accumulators that the caller zeroes per epoch. */
+int qfx_tinycnn_workspace_bytes(int n_selected, size_t* bytes);
+int qfx_tinycnn_stats_offset(int n_selected, size_t* offset);
+int qfx_tinycnn_train_step(const float* X, const int* labels, const int* offsets, const int* perm, int n_total,
+                           const int* client_ids, int n_selected, int epoch, int batch_index, int batch_size,
+                           float* params, float* moment, int nd, int n_classes, float lr, float momentum,
+                           float p_drop, unsigned long long seed, int round, void* workspace,
+                           cudaStream_t stream);
+/* Evaluation (evaluate_model, /root/reference/src/CFed/Classical_FL.py:83-102) in three launches:
+ * out2 = (loss sum, #correct); scratch needs n * 23,520 bytes. */
+int qfx_tinycnn_eval(const float* X, const int* labels, int n, const float* params, int n_classes,
+                     void* scratch, float* out2, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

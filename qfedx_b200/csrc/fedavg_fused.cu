@@ -195,7 +195,8 @@ fedavg_fused_kernel(const AggArgs a) {
 static int g_num_sms = 0;
 
 static int launch_fedavg(AggArgs& a, cudaStream_t stream) {
-    QFX_ARG_CHECK(a.k_local >= 1 && a.k_global >= a.k_local && a.dim >= 1, QFX_ERR_BAD_ARG, "bad K/D");
+    QFX_ARG_CHECK(a.k_local >= 0 && a.k_global >= 1 && a.k_global >= a.k_local && a.dim >= 1, QFX_ERR_BAD_ARG, "bad K/D");
+    QFX_ARG_CHECK(a.k_local >= 1 || a.world > 1, QFX_ERR_BAD_ARG, "no clients to aggregate");
     QFX_ARG_CHECK(a.mode == 0 || a.mode == 1, QFX_ERR_BAD_ARG, "mode must be 0 (weights) or 1 (delta)");
     QFX_ARG_CHECK(!(a.mode == 0 && (a.clip > 0.f || a.sigma > 0.f)), QFX_ERR_BAD_ARG,
                   "clip/noise need delta mode");
@@ -209,7 +210,7 @@ static int launch_fedavg(AggArgs& a, cudaStream_t stream) {
         QFX_CUDA_TRY(cudaGetDevice(&dev));
         QFX_CUDA_TRY(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
     }
-    QFX_CUDA_TRY(cudaMemsetAsync(a.scratch, 0, sizeof(float) * a.k_local, stream));
+    if (a.k_local > 0) QFX_CUDA_TRY(cudaMemsetAsync(a.scratch, 0, sizeof(float) * a.k_local, stream));
     const size_t smem = sizeof(float) * a.k_local;
     if (smem > 48 * 1024)
         QFX_CUDA_TRY(cudaFuncSetAttribute(fedavg_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -21,10 +21,16 @@ namespace qfx {
 
 constexpr unsigned FULL_MASK = 0xffffffffu;
 
-template <int NQ>
+// default lane split: favours throughput (most amplitudes per lane, fewest shuffles)
+constexpr int default_lane_bits(int nq) { return (nq <= 4) ? 0 : ((nq <= 9) ? nq - 4 : 5); }
+// latency split: as many lanes per circuit as possible (shortest instruction stream per warp)
+constexpr int latency_lane_bits(int nq) { return nq <= 1 ? 0 : (nq - 1 < 5 ? nq - 1 : 5); }
+
+template <int NQ, int LB_ = default_lane_bits(NQ)>
 struct SvCfg {
     static_assert(NQ >= 1 && NQ <= 10, "register-tiled statevector supports 1..10 qubits");
-    static constexpr int LB = (NQ <= 4) ? 0 : ((NQ <= 9) ? NQ - 4 : 5);
+    static_assert(LB_ >= 0 && LB_ <= 5 && LB_ <= NQ && NQ - LB_ <= 5, "bad lane split");
+    static constexpr int LB = LB_;
     static constexpr int NL = NQ - LB;
     static constexpr int A = 1 << NL;
     static constexpr int LANES = 1 << LB;
@@ -34,9 +40,9 @@ struct SvCfg {
 enum : int { BASIS_RX = 0, BASIS_RY = 1, BASIS_RZ = 2 };
 enum : int { ENT_CNOT = 0, ENT_CZ = 1, ENT_NONE = 2 };
 
-template <int NQ>
+template <int NQ, int LB_ = default_lane_bits(NQ)>
 struct Sv {
-    using C = SvCfg<NQ>;
+    using C = SvCfg<NQ, LB_>;
     float re[C::A], im[C::A];
 
     // ---- initial states ------------------------------------------------------------
@@ -200,6 +206,51 @@ struct Sv {
         }
     }
 
+    // ---- lane-qubit gates with a RUNTIME lane index k (qubit NL + k) --------------------------
+    // Same arithmetic as rx()/cnot() on lane qubits, but callable from a rolled loop: one copy of
+    // the code serves all lane qubits, which keeps the training kernel inside the instruction cache.
+    __device__ __forceinline__ void rx_lane_rt(int k, float c, float s) {
+        const int m = 1 << k;
+#pragma unroll
+        for (int i = 0; i < C::A; ++i) {
+            const float pr = __shfl_xor_sync(FULL_MASK, re[i], m);
+            const float pi = __shfl_xor_sync(FULL_MASK, im[i], m);
+            const float r0 = re[i], i0 = im[i];
+            re[i] = c * r0 + s * pi;
+            im[i] = c * i0 - s * pr;
+        }
+    }
+    __device__ __forceinline__ void cnot_lanes_rt(int kc, int kt, int lg) {
+        const int m = 1 << kt;
+        const bool on = (lg >> kc) & 1;
+#pragma unroll
+        for (int i = 0; i < C::A; ++i) {
+            const float pr = __shfl_xor_sync(FULL_MASK, re[i], m);
+            const float pi = __shfl_xor_sync(FULL_MASK, im[i], m);
+            re[i] = on ? pr : re[i];
+            im[i] = on ? pi : im[i];
+        }
+    }
+    // ring entangler with the lane-lane links in a rolled loop
+    __device__ __forceinline__ void entangle_rolled(int ent, bool reverse, int lg) {
+        if (ent != ENT_CNOT || NQ < 3 || C::LB < 2) { entangle(ent, reverse, lg); return; }
+        if (!reverse) {
+#pragma unroll
+            for (int q = 0; q + 1 < C::NL; ++q) cnot(q, q + 1, lg);
+            cnot(C::NL - 1, C::NL, lg);
+#pragma unroll 1
+            for (int k = 0; k + 1 < C::LB; ++k) cnot_lanes_rt(k, k + 1, lg);
+            cnot(NQ - 1, 0, lg);
+        } else {
+            cnot(NQ - 1, 0, lg);
+#pragma unroll 1
+            for (int k = C::LB - 2; k >= 0; --k) cnot_lanes_rt(k, k + 1, lg);
+            cnot(C::NL - 1, C::NL, lg);
+#pragma unroll
+            for (int q = C::NL - 2; q >= 0; --q) cnot(q, q + 1, lg);
+        }
+    }
+
     // ---- reductions --------------------------------------------------------------------
     // <Z_q> for all qubits, reduced over the circuit's lanes; every lane gets the result
     __device__ __forceinline__ void expval_z_all(float* __restrict__ ez /*[NQ]*/, int lg) const {
@@ -237,9 +288,9 @@ struct Sv {
 };
 
 // Im <lam| Z_q |psi>, this lane's share
-template <int NQ>
-__device__ __forceinline__ float im_lam_z_psi(const Sv<NQ>& lam, const Sv<NQ>& psi, int q, int lg) {
-    using C = SvCfg<NQ>;
+template <int NQ, int LB_>
+__device__ __forceinline__ float im_lam_z_psi(const Sv<NQ, LB_>& lam, const Sv<NQ, LB_>& psi, int q, int lg) {
+    using C = SvCfg<NQ, LB_>;
     float acc = 0.f;
 #pragma unroll
     for (int i = 0; i < C::A; ++i) {
@@ -253,9 +304,9 @@ __device__ __forceinline__ float im_lam_z_psi(const Sv<NQ>& lam, const Sv<NQ>& p
 // One reverse step through RX(theta) on qubit q: returns this lane's share of
 // Im <lam| X_q |psi> (evaluated after the gate) and replaces psi, lam by RX^dagger applied
 // to them.  For lane qubits the partner amplitudes are fetched once and used for both.
-template <int NQ>
-__device__ __forceinline__ float grad_and_undo_rx(Sv<NQ>& psi, Sv<NQ>& lam, int q, float c, float s, int lg) {
-    using C = SvCfg<NQ>;
+template <int NQ, int LB_>
+__device__ __forceinline__ float grad_and_undo_rx(Sv<NQ, LB_>& psi, Sv<NQ, LB_>& lam, int q, float c, float s, int lg) {
+    using C = SvCfg<NQ, LB_>;
     float acc = 0.f;
     if (q < C::NL) {
 #pragma unroll
@@ -286,11 +337,32 @@ __device__ __forceinline__ float grad_and_undo_rx(Sv<NQ>& psi, Sv<NQ>& lam, int 
     return acc;
 }
 
+// grad_and_undo_rx for lane qubit NL + k with a runtime k (rolled loops)
+template <int NQ, int LB_>
+__device__ __forceinline__ float grad_and_undo_rx_lane_rt(Sv<NQ, LB_>& psi, Sv<NQ, LB_>& lam, int k, float c, float s) {
+    using C = SvCfg<NQ, LB_>;
+    const int m = 1 << k;
+    float acc = 0.f;
+#pragma unroll
+    for (int i = 0; i < C::A; ++i) {
+        const float pr = __shfl_xor_sync(FULL_MASK, psi.re[i], m);
+        const float pi = __shfl_xor_sync(FULL_MASK, psi.im[i], m);
+        const float qr = __shfl_xor_sync(FULL_MASK, lam.re[i], m);
+        const float qi = __shfl_xor_sync(FULL_MASK, lam.im[i], m);
+        acc += lam.re[i] * pi - lam.im[i] * pr;
+        const float r0 = psi.re[i], i0 = psi.im[i];
+        psi.re[i] = c * r0 - s * pi;  psi.im[i] = c * i0 + s * pr;
+        const float l0 = lam.re[i], m0 = lam.im[i];
+        lam.re[i] = c * l0 - s * qi;  lam.im[i] = c * m0 + s * qr;
+    }
+    return acc;
+}
+
 // Im <lam| P_q |psi> for the feature-map generator (no undo needed: it is the first layer)
-template <int NQ>
-__device__ __forceinline__ float im_lam_p_psi(const Sv<NQ>& lam, const Sv<NQ>& psi, int basis, int q, int lg) {
-    using C = SvCfg<NQ>;
-    if (basis == BASIS_RZ) return im_lam_z_psi<NQ>(lam, psi, q, lg);
+template <int NQ, int LB_>
+__device__ __forceinline__ float im_lam_p_psi(const Sv<NQ, LB_>& lam, const Sv<NQ, LB_>& psi, int basis, int q, int lg) {
+    using C = SvCfg<NQ, LB_>;
+    if (basis == BASIS_RZ) return im_lam_z_psi(lam, psi, q, lg);
     float acc = 0.f;
     if (q < C::NL) {
 #pragma unroll
@@ -357,8 +429,8 @@ struct TrigDirect {
 };
 
 // ---- ansatz sweeps ---------------------------------------------------------------------
-template <int NQ, class Trig>
-__device__ __forceinline__ void ansatz_forward(Sv<NQ>& psi, const Trig& trig, int n_layers, int ent, int lg) {
+template <int NQ, int LB_, class Trig>
+__device__ __forceinline__ void ansatz_forward(Sv<NQ, LB_>& psi, const Trig& trig, int n_layers, int ent, int lg) {
     for (int l = 0; l < n_layers; ++l) {
 #pragma unroll
         for (int q = 0; q < NQ; ++q) {
@@ -372,8 +444,8 @@ __device__ __forceinline__ void ansatz_forward(Sv<NQ>& psi, const Trig& trig, in
 }
 
 // Reverse sweep.  sink(p, v) receives this lane's share of d<O>/d theta_p.
-template <int NQ, class Trig, class Sink>
-__device__ __forceinline__ void ansatz_backward(Sv<NQ>& psi, Sv<NQ>& lam, const Trig& trig, int n_layers, int ent,
+template <int NQ, int LB_, class Trig, class Sink>
+__device__ __forceinline__ void ansatz_backward(Sv<NQ, LB_>& psi, Sv<NQ, LB_>& lam, const Trig& trig, int n_layers, int ent,
                                                 int lg, Sink& sink) {
     for (int l = n_layers - 1; l >= 0; --l) {
         psi.entangle(ent, true, lg);
@@ -383,11 +455,123 @@ __device__ __forceinline__ void ansatz_backward(Sv<NQ>& psi, Sv<NQ>& lam, const 
             const int q = NQ - 1 - k;
             const int p = (l * NQ + q) * 2;
             const float2 b = trig.get(p + 1);
-            sink(p + 1, im_lam_z_psi<NQ>(lam, psi, q, lg));
+            sink(p + 1, im_lam_z_psi(lam, psi, q, lg));
             psi.rz(q, b.x, -b.y, lg);
             lam.rz(q, b.x, -b.y, lg);
             const float2 a = trig.get(p);
-            sink(p, grad_and_undo_rx<NQ>(psi, lam, q, a.x, a.y, lg));
+            sink(p, grad_and_undo_rx(psi, lam, q, a.x, a.y, lg));
+        }
+    }
+}
+
+// ---- merged-diagonal sweeps (all circuits of a CTA share theta) ---------------------------
+// Gates on different qubits commute, so a layer is [RX on every qubit][RZ on every qubit][ring].
+// The RZ block is one diagonal; it factors into a table over the local bits and a table over the
+// lane bits, both precomputed per optimizer step in shared memory (build_diag_tables).  Applying
+// it is two complex multiplies per amplitude instead of one per amplitude per qubit.
+struct DiagTables {
+    const float2* __restrict__ loc;   // [L][A]     product over local qubits
+    const float2* __restrict__ lane;  // [L][LANES] product over lane qubits
+};
+
+template <int NQ, int LB_>
+__device__ __forceinline__ void build_diag_tables(float2* loc, float2* lane, const float2* tab, int n_layers,
+                                                  int tid, int nthreads) {
+    using C = SvCfg<NQ, LB_>;
+    for (int e = tid; e < n_layers * (C::A + C::LANES); e += nthreads) {
+        const int l = e / (C::A + C::LANES), r = e % (C::A + C::LANES);
+        const bool is_lane = r >= C::A;
+        const int idx = is_lane ? r - C::A : r;
+        float fr = 1.f, fi = 0.f;
+        for (int k = 0; k < (is_lane ? C::LB : C::NL); ++k) {
+            const int q = is_lane ? C::NL + k : k;
+            const float2 cs = tab[(l * NQ + q) * 2 + 1];
+            const float si = ((idx >> k) & 1) ? cs.y : -cs.y;  // e^{-+ i phi/2}
+            const float nr = fr * cs.x - fi * si, ni = fr * si + fi * cs.x;
+            fr = nr; fi = ni;
+        }
+        if (is_lane) lane[l * C::LANES + idx] = make_float2(fr, fi);
+        else loc[l * C::A + idx] = make_float2(fr, fi);
+    }
+}
+
+template <int NQ, int LB_>
+__device__ __forceinline__ void apply_diag(Sv<NQ, LB_>& psi, const DiagTables& dt, int l, int lg, bool conj) {
+    using C = SvCfg<NQ, LB_>;
+    const float2 dl = dt.lane[l * C::LANES + lg];
+#pragma unroll
+    for (int i = 0; i < C::A; ++i) {
+        const float2 d0 = dt.loc[l * C::A + i];
+        const float fr = d0.x * dl.x - d0.y * dl.y;
+        const float fi = conj ? -(d0.x * dl.y + d0.y * dl.x) : (d0.x * dl.y + d0.y * dl.x);
+        const float r = psi.re[i], m = psi.im[i];
+        psi.re[i] = r * fr - m * fi;
+        psi.im[i] = r * fi + m * fr;
+    }
+}
+
+template <int NQ, int LB_>
+__device__ __forceinline__ void ansatz_forward_merged(Sv<NQ, LB_>& psi, const float2* tab, const DiagTables& dt,
+                                                      int n_layers, int ent, int lg) {
+    using C = SvCfg<NQ, LB_>;
+#pragma unroll 1
+    for (int l = 0; l < n_layers; ++l) {
+#pragma unroll
+        for (int q = 0; q < C::NL; ++q) {
+            const float2 a = tab[(l * NQ + q) * 2];
+            psi.rx(q, a.x, a.y, lg);
+        }
+#pragma unroll 1
+        for (int k = 0; k < C::LB; ++k) {
+            const float2 a = tab[(l * NQ + C::NL + k) * 2];
+            psi.rx_lane_rt(k, a.x, a.y);
+        }
+        apply_diag(psi, dt, l, lg, false);
+        psi.entangle_rolled(ent, false, lg);
+    }
+}
+
+template <int NQ, int LB_, class Sink>
+__device__ __forceinline__ void ansatz_backward_merged(Sv<NQ, LB_>& psi, Sv<NQ, LB_>& lam, const float2* tab,
+                                                       const DiagTables& dt, int n_layers, int ent, int lg,
+                                                       Sink& sink) {
+    using C = SvCfg<NQ, LB_>;
+#pragma unroll 1
+    for (int l = n_layers - 1; l >= 0; --l) {
+        psi.entangle_rolled(ent, true, lg);
+        lam.entangle_rolled(ent, true, lg);
+        // all RZ gradients from one pass: t_i = Im(conj(lam_i) psi_i), signed sums per qubit
+        {
+            float t[C::A];
+            float tot = 0.f;
+#pragma unroll
+            for (int i = 0; i < C::A; ++i) { t[i] = lam.re[i] * psi.im[i] - lam.im[i] * psi.re[i]; tot += t[i]; }
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) {
+                float v;
+                if (q < C::NL) {
+                    v = 0.f;
+#pragma unroll
+                    for (int i = 0; i < C::A; ++i) v += ((i >> q) & 1) ? -t[i] : t[i];
+                } else {
+                    v = ((lg >> (q - C::NL)) & 1) ? -tot : tot;
+                }
+                sink((l * NQ + q) * 2 + 1, v);
+            }
+        }
+        apply_diag(psi, dt, l, lg, true);
+        apply_diag(lam, dt, l, lg, true);
+#pragma unroll 1
+        for (int k = C::LB - 1; k >= 0; --k) {
+            const int q = C::NL + k;
+            const float2 a = tab[(l * NQ + q) * 2];
+            sink((l * NQ + q) * 2, grad_and_undo_rx_lane_rt(psi, lam, k, a.x, a.y));
+        }
+#pragma unroll
+        for (int k = 0; k < C::NL; ++k) {
+            const int q = C::NL - 1 - k;
+            const float2 a = tab[(l * NQ + q) * 2];
+            sink((l * NQ + q) * 2, grad_and_undo_rx(psi, lam, q, a.x, a.y, lg));
         }
     }
 }

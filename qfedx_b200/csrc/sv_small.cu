@@ -11,8 +11,8 @@ namespace qfx {
 constexpr int SV_THREADS = 128;
 constexpr int MAX_PARAMS_SMEM = 2 * 10 * 64;  // n <= 10, L <= 64
 
-template <int NQ>
-__device__ __forceinline__ void load_initial(Sv<NQ>& psi, const float* angles, const float* init_state, int basis,
+template <int NQ, int LB_>
+__device__ __forceinline__ void load_initial(Sv<NQ, LB_>& psi, const float* angles, const float* init_state, int basis,
                                              int b, int lg) {
     if (init_state != nullptr) psi.set_real(init_state + (size_t)b * SvCfg<NQ>::DIM, lg);
     else psi.set_product(angles + (size_t)b * NQ, basis, lg);
@@ -43,13 +43,13 @@ sv_forward_kernel(int n_layers, int basis, int ent, const float* __restrict__ an
     const int b = live ? circ : B - 1;  // dead lanes shadow a real circuit so shuffles stay converged
 
     Sv<NQ> psi;
-    load_initial<NQ>(psi, angles, init_state, basis, b, lg);
+    load_initial(psi, angles, init_state, basis, b, lg);
     if (gid == nullptr) {
         TrigTable trig{tab, -1, 0.f};
-        ansatz_forward<NQ>(psi, trig, n_layers, ent, lg);
+        ansatz_forward(psi, trig, n_layers, ent, lg);
     } else {
         TrigDirect trig{theta + (size_t)gid[b] * n_params, -1, 0.f};
-        ansatz_forward<NQ>(psi, trig, n_layers, ent, lg);
+        ansatz_forward(psi, trig, n_layers, ent, lg);
     }
     float ez[NQ];
     psi.expval_z_all(ez, lg);
@@ -98,29 +98,29 @@ sv_adjoint_kernel(int n_layers, int basis, int ent, const float* __restrict__ an
     const int b = live ? circ : B - 1;
 
     Sv<NQ> psi, lam;
-    load_initial<NQ>(psi, angles, init_state, basis, b, lg);
+    load_initial(psi, angles, init_state, basis, b, lg);
     float cq[NQ];
 #pragma unroll
     for (int q = 0; q < NQ; ++q) cq[q] = cot[(size_t)b * NQ + q];
 
     if (gid == nullptr) {
         TrigTable trig{tab, -1, 0.f};
-        ansatz_forward<NQ>(psi, trig, n_layers, ent, lg);
+        ansatz_forward(psi, trig, n_layers, ent, lg);
         lam.set_obs_times(psi, cq, lg);
         AtomicSink<C::LANES> sink{sgrad, live, lg};
-        ansatz_backward<NQ>(psi, lam, trig, n_layers, ent, lg, sink);
+        ansatz_backward(psi, lam, trig, n_layers, ent, lg, sink);
     } else {
         const size_t off = (size_t)gid[b] * n_params;
         TrigDirect trig{theta + off, -1, 0.f};
-        ansatz_forward<NQ>(psi, trig, n_layers, ent, lg);
+        ansatz_forward(psi, trig, n_layers, ent, lg);
         lam.set_obs_times(psi, cq, lg);
         AtomicSink<C::LANES> sink{grad_theta + off, live, lg};
-        ansatz_backward<NQ>(psi, lam, trig, n_layers, ent, lg, sink);
+        ansatz_backward(psi, lam, trig, n_layers, ent, lg, sink);
     }
     if (grad_angles != nullptr && init_state == nullptr) {
 #pragma unroll
         for (int q = 0; q < NQ; ++q) {
-            float v = group_sum<C::LANES>(im_lam_p_psi<NQ>(lam, psi, basis, q, lg));
+            float v = group_sum<C::LANES>(im_lam_p_psi(lam, psi, basis, q, lg));
             if (live && lg == 0) grad_angles[(size_t)b * NQ + q] = v;
         }
     }
@@ -155,15 +155,15 @@ sv_param_shift_kernel(int n_layers, int basis, int ent, const float* __restrict_
     const float sgn = sign_i ? -1.f : 1.f;
 
     Sv<NQ> psi;
-    load_initial<NQ>(psi, angles, init_state, basis, b, lg);
+    load_initial(psi, angles, init_state, basis, b, lg);
     size_t off = 0;
     if (gid == nullptr) {
         TrigTable trig{tab, p, sgn};
-        ansatz_forward<NQ>(psi, trig, n_layers, ent, lg);
+        ansatz_forward(psi, trig, n_layers, ent, lg);
     } else {
         off = (size_t)gid[b] * n_params;
         TrigDirect trig{theta + off, p, sgn};
-        ansatz_forward<NQ>(psi, trig, n_layers, ent, lg);
+        ansatz_forward(psi, trig, n_layers, ent, lg);
     }
     float ez[NQ];
     psi.expval_z_all(ez, lg);

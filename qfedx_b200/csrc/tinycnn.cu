@@ -1,0 +1,699 @@
+// K8: TinyCNN local training batched across the clients resident on one GPU.
+//
+// The reference trains clients one after another, a few dozen small library kernels per SGD step
+// (/root/reference/src/CFed/Classical_FL.py:40-64, model :21-38).  Here every kernel of a step
+// covers all clients at once (grid.y = client, each with its own weights), layers are fused
+// (conv+bias+ReLU+maxpool; fc2+softmax-CE+backward head; fc1 backward+SGD+unpool) and the whole
+// round is replayed from one CUDA graph (qfedx_b200/fl/trainers_cnn.py).  fp32 storage and
+// accumulation; direct convolution with register tiling (2x2 outputs x 8 channels per thread) so
+// the inner loops are FMA-bound rather than shared-memory-bound.
+//
+// Flat parameter layout per client (state_dict order, matches models/tinycnn.py):
+//   conv1.w [16,1,5,5] @0 | conv1.b [16] @400 | conv2.w [32,16,5,5] @416 | conv2.b [32] @13216 |
+//   fc1.w [64,1568] @13248 | fc1.b [64] @113600 | fc2.w [C,64] @113664 | fc2.b [C] @113664+64C
+#include "common.cuh"
+#include "../../include/qfedx_b200.h"
+
+namespace qfx {
+namespace cnn {
+
+constexpr int BS = 32;           // max minibatch rows handled by the fc kernels
+constexpr int C1W = 0, C1B = 400, C2W = 416, C2B = 13216, F1W = 13248, F1B = 113600, F2W = 113664;
+constexpr int NCONV = 13248;     // conv parameters (reduced from per-image partials)
+constexpr int FC1_SLICES = 16;   // split-K slices of the 1568-long fc1 reduction
+constexpr int FC1_KS = 98;       // 1568 / 16
+constexpr int MAX_CLASSES = 10;
+
+struct Step {
+    const float* X;          // [N,1,28,28] dataset
+    const int* labels;       // [N]
+    const int* offsets;      // [K+1]
+    const int* perm;         // [E,N] or null
+    const int* client_ids;   // [K_sel] rows -> client segment
+    int n_total, epoch, batch_index, batch_size;
+    float* params;           // [K_sel, ND]
+    float* moment;           // [K_sel, ND]
+    int nd;                  // row stride of params/moment
+    int n_classes;
+    float lr, momentum, p_drop;
+    unsigned long long seed;
+    int round;
+    // activations / workspaces, all [K_sel, ...]
+    float* a1; unsigned char* i1;    // [K,32,16,14,14]
+    float* a2; unsigned char* i2;    // [K,32,32,7,7]
+    float* fc1_part;                 // [K,16,32,64]
+    float* h1;                       // [K,32,64]
+    float* dh1;                      // [K,32,64]
+    float* g2;                       // [K,32,32,14,14]
+    float* da1;                      // [K,32,16,14,14]
+    float* conv_part;                // [K,32,NCONV]
+    float* stats;                    // [K,2] running loss sum / correct count of the epoch
+};
+
+__device__ __forceinline__ int batch_rows(const Step& s, int sel, int* seg_lo) {
+    const int client = s.client_ids[sel];
+    const int lo = s.offsets[client], n_k = s.offsets[client + 1] - lo;
+    *seg_lo = lo;
+    const int b0 = s.batch_index * s.batch_size;
+    return max(0, min(s.batch_size, n_k - b0));
+}
+__device__ __forceinline__ int sample_index(const Step& s, int seg_lo, int b) {
+    const int j = s.batch_index * s.batch_size + b;
+    return s.perm ? s.perm[(size_t)s.epoch * s.n_total + seg_lo + j] : seg_lo + j;
+}
+
+// ------------------------------------------------------------------------------------------
+// conv1 5x5 (1->16, pad 2) + bias + ReLU + 2x2 maxpool.  One CTA per image, one thread per pooled
+// position; the 6x6 input window sits in registers, weights are broadcast from shared memory.
+__device__ __forceinline__ void conv1_image(const float* __restrict__ img, const float* __restrict__ prm,
+                                            float* __restrict__ a1, unsigned char* __restrict__ i1) {
+    __shared__ float xs[32 * 32];
+    __shared__ float ws[16 * 25 + 16];
+    const int tid = threadIdx.x;
+    for (int i = tid; i < 32 * 32; i += blockDim.x) {
+        const int y = (i >> 5) - 2, x = (i & 31) - 2;
+        xs[i] = (y >= 0 && y < 28 && x >= 0 && x < 28) ? img[y * 28 + x] : 0.f;
+    }
+    for (int i = tid; i < 416; i += blockDim.x) ws[i] = prm[C1W + i];
+    __syncthreads();
+    if (tid >= 196) return;
+    const int py = tid / 14, px = tid % 14;
+    float win[6][6];
+#pragma unroll
+    for (int r = 0; r < 6; ++r)
+#pragma unroll
+        for (int c = 0; c < 6; ++c) win[r][c] = xs[(2 * py + r) * 32 + 2 * px + c];
+    for (int o = 0; o < 16; ++o) {
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int ky = 0; ky < 5; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 5; ++kx) {
+                const float w = ws[o * 25 + ky * 5 + kx];
+                acc[0] += w * win[ky][kx];     acc[1] += w * win[ky][kx + 1];
+                acc[2] += w * win[ky + 1][kx]; acc[3] += w * win[ky + 1][kx + 1];
+            }
+        float best = acc[0]; int arg = 0;
+#pragma unroll
+        for (int j = 1; j < 4; ++j) if (acc[j] > best) { best = acc[j]; arg = j; }
+        best = fmaxf(best + ws[400 + o], 0.f);
+        a1[o * 196 + tid] = best;
+        i1[o * 196 + tid] = (unsigned char)arg;
+    }
+}
+
+__global__ void __launch_bounds__(224) conv1_fwd_train(const Step s) {
+    const int sel = blockIdx.y, b = blockIdx.x;
+    int lo;
+    if (b >= batch_rows(s, sel, &lo)) return;
+    const size_t off = ((size_t)sel * BS + b) * 16 * 196;
+    conv1_image(s.X + (size_t)sample_index(s, lo, b) * 784, s.params + (size_t)sel * s.nd, s.a1 + off, s.i1 + off);
+}
+__global__ void __launch_bounds__(224) conv1_fwd_eval(const float* __restrict__ X, const float* __restrict__ prm,
+                                                      float* a1, unsigned char* i1) {
+    const size_t off = (size_t)blockIdx.x * 16 * 196;
+    conv1_image(X + (size_t)blockIdx.x * 784, prm, a1 + off, i1 + off);
+}
+
+// ------------------------------------------------------------------------------------------
+// Shared direct-convolution core for conv2 forward (16->32) and conv2 data-gradient (32->16):
+// CIN input planes of 14x14 (padded to 18x18 in shared memory), weights in shared memory as
+// [cin][tap][cout]; a thread owns a 2x2 output block for CO consecutive output channels.
+template <int CIN, int CO>
+__device__ __forceinline__ void conv5x5_block(const float* __restrict__ xs /*[CIN][18][18]*/,
+                                              const float* __restrict__ ws /*[CIN][25][COUT_ALL]*/, int cout_all,
+                                              int co0, int py, int px, float (&acc)[4][CO]) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int o = 0; o < CO; ++o) acc[j][o] = 0.f;
+    for (int c = 0; c < CIN; ++c) {
+        float win[6][6];
+        const float* xp = xs + c * 324 + (2 * py) * 18 + 2 * px;
+#pragma unroll
+        for (int r = 0; r < 6; ++r)
+#pragma unroll
+            for (int q = 0; q < 6; ++q) win[r][q] = xp[r * 18 + q];
+        const float* wp = ws + (size_t)c * 25 * cout_all + co0;
+#pragma unroll
+        for (int ky = 0; ky < 5; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 5; ++kx) {
+                float w[CO];
+#pragma unroll
+                for (int v = 0; v < CO / 4; ++v) {
+                    const float4 t = *reinterpret_cast<const float4*>(wp + (ky * 5 + kx) * cout_all + 4 * v);
+                    w[4 * v] = t.x; w[4 * v + 1] = t.y; w[4 * v + 2] = t.z; w[4 * v + 3] = t.w;
+                }
+#pragma unroll
+                for (int o = 0; o < CO; ++o) {
+                    acc[0][o] += w[o] * win[ky][kx];     acc[1][o] += w[o] * win[ky][kx + 1];
+                    acc[2][o] += w[o] * win[ky + 1][kx]; acc[3][o] += w[o] * win[ky + 1][kx + 1];
+                }
+            }
+    }
+}
+
+constexpr int CONV2_SMEM = (16 * 324 + 16 * 25 * 32) * 4;  // 71,936 B
+__device__ __forceinline__ void conv2_image(const float* __restrict__ a1, const float* __restrict__ prm,
+                                            float* __restrict__ a2, unsigned char* __restrict__ i2, float* smem) {
+    float* xs = smem;                 // [16][18][18]
+    float* ws = smem + 16 * 324;      // [16][25][32]
+    const int tid = threadIdx.x;
+    for (int i = tid; i < 16 * 324; i += blockDim.x) {
+        const int c = i / 324, r = (i % 324) / 18 - 2, q = (i % 18) - 2;
+        xs[i] = (r >= 0 && r < 14 && q >= 0 && q < 14) ? a1[c * 196 + r * 14 + q] : 0.f;
+    }
+    for (int i = tid; i < 12800; i += blockDim.x) {  // global [o][c][tap] -> shared [c][tap][o]
+        const int o = i / 400, rem = i % 400;
+        ws[rem * 32 + o] = prm[C2W + i];
+    }
+    __syncthreads();
+    if (tid >= 196) return;
+    const int g = tid / 49, pos = tid % 49, py = pos / 7, px = pos % 7;
+    float acc[4][8];
+    conv5x5_block<16, 8>(xs, ws, 32, g * 8, py, px, acc);
+#pragma unroll
+    for (int o = 0; o < 8; ++o) {
+        float best = acc[0][o]; int arg = 0;
+#pragma unroll
+        for (int j = 1; j < 4; ++j) if (acc[j][o] > best) { best = acc[j][o]; arg = j; }
+        best = fmaxf(best + prm[C2B + g * 8 + o], 0.f);
+        a2[(g * 8 + o) * 49 + pos] = best;
+        i2[(g * 8 + o) * 49 + pos] = (unsigned char)arg;
+    }
+}
+__global__ void __launch_bounds__(224) conv2_fwd_train(const Step s) {
+    extern __shared__ __align__(16) float smem[];
+    const int sel = blockIdx.y, b = blockIdx.x;
+    int lo;
+    if (b >= batch_rows(s, sel, &lo)) return;
+    const size_t r = (size_t)sel * BS + b;
+    conv2_image(s.a1 + r * 3136, s.params + (size_t)sel * s.nd, s.a2 + r * 1568, s.i2 + r * 1568, smem);
+}
+__global__ void __launch_bounds__(224) conv2_fwd_eval(const float* __restrict__ a1, const float* __restrict__ prm,
+                                                      float* a2, unsigned char* i2) {
+    extern __shared__ __align__(16) float smem[];
+    const size_t r = blockIdx.x;
+    conv2_image(a1 + r * 3136, prm, a2 + r * 1568, i2 + r * 1568, smem);
+}
+
+// ------------------------------------------------------------------------------------------
+// fc1 forward, split-K: CTA (slice, client) computes the partial [32 x 64] product over 98 inputs.
+// 128 threads, each a 4x4 (rows x features) register tile.
+__global__ void __launch_bounds__(128) fc1_fwd_train(const Step s) {
+    __shared__ __align__(16) float xs[FC1_KS][BS];       // [k][b]
+    __shared__ __align__(16) float wsm[FC1_KS][64];      // [k][f]
+    const int sel = blockIdx.y, sl = blockIdx.x, tid = threadIdx.x;
+    int lo;
+    const int nb = batch_rows(s, sel, &lo);
+    if (nb <= 0) return;
+    const float* x = s.a2 + (size_t)sel * BS * 1568 + sl * FC1_KS;
+    const float* w = s.params + (size_t)sel * s.nd + F1W + sl * FC1_KS;
+    for (int i = tid; i < BS * FC1_KS; i += 128) {
+        const int b = i / FC1_KS, k = i % FC1_KS;
+        xs[k][b] = b < nb ? x[(size_t)b * 1568 + k] : 0.f;
+    }
+    for (int i = tid; i < 64 * FC1_KS; i += 128) {
+        const int f = i / FC1_KS, k = i % FC1_KS;
+        wsm[k][f] = w[(size_t)f * 1568 + k];
+    }
+    __syncthreads();
+    const int bt = (tid >> 4) * 4, ft = (tid & 15) * 4;
+    float acc[4][4] = {};
+#pragma unroll 2
+    for (int k = 0; k < FC1_KS; ++k) {
+        const float4 xv = *reinterpret_cast<const float4*>(&xs[k][bt]);
+        const float4 wv = *reinterpret_cast<const float4*>(&wsm[k][ft]);
+        const float xa[4] = {xv.x, xv.y, xv.z, xv.w}, wa[4] = {wv.x, wv.y, wv.z, wv.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] += xa[i] * wa[j];
+    }
+    float* out = s.fc1_part + (((size_t)sel * FC1_SLICES + sl) * BS) * 64;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<float4*>(out + (bt + i) * 64 + ft) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+}
+
+// ------------------------------------------------------------------------------------------
+// Head: fc1 bias + ReLU + dropout, fc2, softmax cross-entropy, and everything of the backward
+// pass that lives above fc1: d logits, fc2 / fc1-bias SGD updates, dh1.  One CTA per client.
+__global__ void __launch_bounds__(256) head_train(const Step s) {
+    __shared__ float h[BS][65];
+    __shared__ float w2[MAX_CLASSES][64];
+    __shared__ float z[BS][MAX_CLASSES];
+    __shared__ float dz[BS][MAX_CLASSES];
+    __shared__ float red[2];
+    const int sel = blockIdx.x, tid = threadIdx.x, NC = s.n_classes;
+    int lo;
+    const int nb = batch_rows(s, sel, &lo);
+    if (nb <= 0) return;
+    float* prm = s.params + (size_t)sel * s.nd;
+    float* mom = s.moment + (size_t)sel * s.nd;
+    const int f2b = F2W + 64 * NC;
+    if (tid < 2) red[tid] = 0.f;
+    for (int i = tid; i < NC * 64; i += 256) w2[i / 64][i % 64] = prm[F2W + i];
+    // h = dropout(relu(sum of split-K partials + b1))
+    const unsigned long long dkey = key3(s.seed ^ 0x44524f50ull, (unsigned long long)s.round * 4096ull + s.client_ids[sel],
+                                         (unsigned long long)s.epoch * 65536ull + s.batch_index);
+    const float keep_scale = s.p_drop > 0.f ? 1.f / (1.f - s.p_drop) : 1.f;
+    for (int i = tid; i < BS * 64; i += 256) {
+        const int b = i >> 6, f = i & 63;
+        float v = 0.f;
+        if (b < nb) {
+            v = prm[F1B + f];
+            const float* part = s.fc1_part + ((size_t)sel * FC1_SLICES * BS + b) * 64 + f;
+#pragma unroll
+            for (int sl = 0; sl < FC1_SLICES; ++sl) v += part[(size_t)sl * BS * 64];
+            v = fmaxf(v, 0.f);
+            if (s.p_drop > 0.f) {
+                const float u = uniform_from_bits(stream_at(dkey, (unsigned long long)i));
+                v = u < s.p_drop ? 0.f : v * keep_scale;
+            }
+        }
+        h[b][f] = v;
+        s.h1[((size_t)sel * BS + b) * 64 + f] = v;
+    }
+    __syncthreads();
+    // logits
+    for (int i = tid; i < BS * NC; i += 256) {
+        const int b = i / NC, c = i % NC;
+        float v = prm[f2b + c];
+#pragma unroll 8
+        for (int f = 0; f < 64; ++f) v += h[b][f] * w2[c][f];
+        z[b][c] = v;
+    }
+    __syncthreads();
+    if (tid < BS) {
+        const int b = tid;
+        if (b < nb) {
+            const int y = s.labels[sample_index(s, lo, b)];
+            float m = z[b][0]; int arg = 0;
+            for (int c = 1; c < NC; ++c) if (z[b][c] > m) { m = z[b][c]; arg = c; }
+            float sum = 0.f;
+            for (int c = 0; c < NC; ++c) sum += expf(z[b][c] - m);
+            const float inv = 1.f / sum, inv_nb = 1.f / (float)nb;
+            for (int c = 0; c < NC; ++c) dz[b][c] = (expf(z[b][c] - m) * inv - (c == y ? 1.f : 0.f)) * inv_nb;
+            atomicAdd(&red[0], m + logf(sum) - z[b][y]);
+            atomicAdd(&red[1], arg == y ? 1.f : 0.f);
+        } else {
+            for (int c = 0; c < NC; ++c) dz[b][c] = 0.f;
+        }
+    }
+    __syncthreads();
+    if (tid == 0) { s.stats[sel * 2] += red[0]; s.stats[sel * 2 + 1] += red[1]; }
+    // dh1 = (dz W2) masked by ReLU/dropout (h > 0 <=> kept and active)
+    for (int i = tid; i < BS * 64; i += 256) {
+        const int b = i >> 6, f = i & 63;
+        float v = 0.f;
+        if (h[b][f] > 0.f) {
+            for (int c = 0; c < NC; ++c) v += dz[b][c] * w2[c][f];
+            v *= keep_scale;
+        }
+        s.dh1[((size_t)sel * BS + b) * 64 + f] = v;
+    }
+    // fc2 weight / bias and fc1 bias updates (their last use this step is above)
+    for (int i = tid; i < NC * 64 + NC + 64; i += 256) {
+        float g = 0.f; int p;
+        if (i < NC * 64) {
+            const int c = i / 64, f = i % 64;
+            for (int b = 0; b < nb; ++b) g += dz[b][c] * h[b][f];
+            p = F2W + i;
+        } else if (i < NC * 64 + NC) {
+            const int c = i - NC * 64;
+            for (int b = 0; b < nb; ++b) g += dz[b][c];
+            p = f2b + c;
+        } else {
+            const int f = i - NC * 64 - NC;
+            for (int b = 0; b < nb; ++b) {
+                if (h[b][f] > 0.f) {
+                    float v = 0.f;
+                    for (int c = 0; c < NC; ++c) v += dz[b][c] * w2[c][f];
+                    g += v * keep_scale;
+                }
+            }
+            p = F1B + f;
+        }
+        const float m = s.momentum * mom[p] + g;
+        mom[p] = m;
+        prm[p] -= s.lr * m;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// fc1 backward for a 32-column chunk of the 1568 inputs: dW1 (+ SGD update in place), dx, and dx
+// pushed through maxpool2 / ReLU into the dense conv2-output gradient g2.
+__global__ void __launch_bounds__(256) fc1_bwd_train(const Step s) {
+    __shared__ __align__(16) float dh[BS][64];
+    __shared__ float xs[BS][33];
+    __shared__ float wsm[64][33];
+    const int sel = blockIdx.y, k0 = blockIdx.x * 32, tid = threadIdx.x;
+    int lo;
+    const int nb = batch_rows(s, sel, &lo);
+    if (nb <= 0) return;
+    float* prm = s.params + (size_t)sel * s.nd;
+    float* mom = s.moment + (size_t)sel * s.nd;
+    for (int i = tid; i < BS * 64; i += 256) dh[i >> 6][i & 63] = (i >> 6) < nb ? s.dh1[(size_t)sel * BS * 64 + i] : 0.f;
+    for (int i = tid; i < BS * 32; i += 256) {
+        const int b = i >> 5, k = i & 31;
+        xs[b][k] = b < nb ? s.a2[((size_t)sel * BS + b) * 1568 + k0 + k] : 0.f;
+    }
+    for (int i = tid; i < 64 * 32; i += 256) wsm[i >> 5][i & 31] = prm[F1W + (size_t)(i >> 5) * 1568 + k0 + (i & 31)];
+    __syncthreads();
+    // dx[b][k] = sum_f dh[b][f] W1[f][k]; 1024 outputs, 4 per thread (b = tid/8 .., k = ..)
+    {
+        const int k = tid & 31, bq = tid >> 5;  // rows bq, bq+8, bq+16, bq+24
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 8
+        for (int f = 0; f < 64; ++f) {
+            const float w = wsm[f][k];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) acc[r] += dh[bq + 8 * r][f] * w;
+        }
+        const int col = k0 + k, oc = col / 49, pos = col % 49, py = pos / 7, px = pos % 7;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const int b = bq + 8 * r;
+            if (b >= nb) continue;
+            const size_t row = (size_t)sel * BS + b;
+            const float act = s.a2[row * 1568 + col];
+            const int arg = s.i2[row * 1568 + col];
+            const float gv = act > 0.f ? acc[r] : 0.f;
+            float* g = s.g2 + (row * 32 + oc) * 196 + (2 * py) * 14 + 2 * px;
+            g[0] = arg == 0 ? gv : 0.f;  g[1] = arg == 1 ? gv : 0.f;
+            g[14] = arg == 2 ? gv : 0.f; g[15] = arg == 3 ? gv : 0.f;
+        }
+    }
+    // dW1[f][k] = sum_b dh[b][f] x[b][k]; 2048 outputs, 8 per thread; SGD-momentum in place
+    {
+        const int k = tid & 31, fg = (tid >> 5) * 8;
+        float acc[8] = {};
+        for (int b = 0; b < nb; ++b) {
+            const float xv = xs[b][k];
+            const float4 d0 = *reinterpret_cast<const float4*>(&dh[b][fg]);
+            const float4 d1 = *reinterpret_cast<const float4*>(&dh[b][fg + 4]);
+            acc[0] += d0.x * xv; acc[1] += d0.y * xv; acc[2] += d0.z * xv; acc[3] += d0.w * xv;
+            acc[4] += d1.x * xv; acc[5] += d1.y * xv; acc[6] += d1.z * xv; acc[7] += d1.w * xv;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const size_t p = F1W + (size_t)(fg + j) * 1568 + k0 + k;
+            const float m = s.momentum * mom[p] + acc[j];
+            mom[p] = m;
+            prm[p] = wsm[fg + j][k] - s.lr * m;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// conv2 data gradient: da1[c][y][x] = sum_o sum_taps g2pad[o][y+ky][x+kx] W[o][c][4-ky][4-kx].
+constexpr int DGRAD_SMEM = (32 * 324 + 32 * 25 * 16) * 4;  // 92,672 B
+__global__ void __launch_bounds__(224) conv2_dgrad_train(const Step s) {
+    extern __shared__ __align__(16) float smem[];
+    float* xs = smem;                // [32][18][18]
+    float* ws = smem + 32 * 324;     // [32 o][25 taps][16 c], taps already flipped
+    const int sel = blockIdx.y, b = blockIdx.x, tid = threadIdx.x;
+    int lo;
+    if (b >= batch_rows(s, sel, &lo)) return;
+    const size_t row = (size_t)sel * BS + b;
+    const float* g2 = s.g2 + row * 32 * 196;
+    const float* prm = s.params + (size_t)sel * s.nd;
+    for (int i = tid; i < 32 * 324; i += blockDim.x) {
+        const int c = i / 324, r = (i % 324) / 18 - 2, q = (i % 18) - 2;
+        xs[i] = (r >= 0 && r < 14 && q >= 0 && q < 14) ? g2[c * 196 + r * 14 + q] : 0.f;
+    }
+    for (int i = tid; i < 12800; i += blockDim.x) {  // global [o][c][tap] -> shared [o][24-tap][c]
+        const int o = i / 400, c = (i % 400) / 25, tap = i % 25;
+        ws[(o * 25 + (24 - tap)) * 16 + c] = prm[C2W + i];
+    }
+    __syncthreads();
+    if (tid >= 196) return;
+    const int g = tid / 49, pos = tid % 49, py = pos / 7, px = pos % 7;
+    float acc[4][4];
+    conv5x5_block<32, 4>(xs, ws, 16, g * 4, py, px, acc);
+    float* out = s.da1 + row * 3136;
+#pragma unroll
+    for (int o = 0; o < 4; ++o) {
+        float* p = out + (g * 4 + o) * 196 + (2 * py) * 14 + 2 * px;
+        p[0] = acc[0][o]; p[1] = acc[1][o]; p[14] = acc[2][o]; p[15] = acc[3][o];
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// conv2 weight gradient for one image (split-K over the batch): thread (og, c, ky) accumulates
+// dW[og*8..+8][c][ky][0..5) over all 14x14 positions; partial sums go to conv_part[image].
+constexpr int WGRAD_SMEM = (196 * 32 + 16 * 324) * 4;  // 45,824 B
+__global__ void __launch_bounds__(320) conv2_wgrad_train(const Step s) {
+    extern __shared__ __align__(16) float smem[];
+    float* gs = smem;               // [y][x][o] 196*32
+    float* xs = smem + 196 * 32;    // [16][18][18]
+    const int sel = blockIdx.y, b = blockIdx.x, tid = threadIdx.x;
+    int lo;
+    const int nb = batch_rows(s, sel, &lo);
+    float* part = s.conv_part + ((size_t)sel * BS + b) * NCONV;
+    if (b >= nb) {  // keep the reduction in sgd_conv branch-free: absent images contribute zeros
+        if (nb > 0) for (int i = tid; i < NCONV; i += 320) part[i] = 0.f;
+        return;
+    }
+    const size_t row = (size_t)sel * BS + b;
+    const float* g2 = s.g2 + row * 32 * 196;
+    const float* a1 = s.a1 + row * 3136;
+    for (int i = tid; i < 32 * 196; i += 320) gs[(i % 196) * 32 + i / 196] = g2[i];
+    for (int i = tid; i < 16 * 324; i += 320) {
+        const int c = i / 324, r = (i % 324) / 18 - 2, q = (i % 18) - 2;
+        xs[i] = (r >= 0 && r < 14 && q >= 0 && q < 14) ? a1[c * 196 + r * 14 + q] : 0.f;
+    }
+    __syncthreads();
+    const int ky = tid % 5, c = (tid / 5) % 16, og = tid / 80;  // og in 0..3
+    float acc[8][5] = {};
+    for (int y = 0; y < 14; ++y) {
+        float xr[18];
+        const float* xp = xs + c * 324 + (y + ky) * 18;
+#pragma unroll
+        for (int q = 0; q < 18; ++q) xr[q] = xp[q];
+#pragma unroll
+        for (int x = 0; x < 14; ++x) {
+            const float4 g0 = *reinterpret_cast<const float4*>(gs + (y * 14 + x) * 32 + og * 8);
+            const float4 g1 = *reinterpret_cast<const float4*>(gs + (y * 14 + x) * 32 + og * 8 + 4);
+            const float gv[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+#pragma unroll
+            for (int o = 0; o < 8; ++o)
+#pragma unroll
+                for (int kx = 0; kx < 5; ++kx) acc[o][kx] += gv[o] * xr[x + kx];
+        }
+    }
+#pragma unroll
+    for (int o = 0; o < 8; ++o)
+#pragma unroll
+        for (int kx = 0; kx < 5; ++kx) part[C2W + (og * 8 + o) * 400 + c * 25 + ky * 5 + kx] = acc[o][kx];
+    // conv2 bias gradient: sum of g2 over positions, one thread per output channel
+    if (tid < 32) {
+        float sum = 0.f;
+        for (int i = 0; i < 196; ++i) sum += gs[i * 32 + tid];
+        part[C2B + tid] = sum;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// conv1 weight gradient for one image.  The gradient reaching conv1's output is sparse (one
+// position per pooled window, and only where the pooled activation is positive), so the sum runs
+// over the 16x196 pooled elements: thread (o, tap) adds da1 * x[argmax position + tap].
+__global__ void __launch_bounds__(416) conv1_wgrad_train(const Step s) {
+    __shared__ float xs[32 * 32];
+    __shared__ float gsm[16 * 196];
+    __shared__ unsigned char ism[16 * 196];
+    const int sel = blockIdx.y, b = blockIdx.x, tid = threadIdx.x;
+    int lo;
+    const int nb = batch_rows(s, sel, &lo);
+    if (b >= nb) return;  // conv_part rows of absent images were zeroed by conv2_wgrad_train
+    const size_t row = (size_t)sel * BS + b;
+    const float* img = s.X + (size_t)sample_index(s, lo, b) * 784;
+    for (int i = tid; i < 1024; i += 416) {
+        const int y = (i >> 5) - 2, x = (i & 31) - 2;
+        xs[i] = (y >= 0 && y < 28 && x >= 0 && x < 28) ? img[y * 28 + x] : 0.f;
+    }
+    for (int i = tid; i < 3136; i += 416) {
+        gsm[i] = s.a1[row * 3136 + i] > 0.f ? s.da1[row * 3136 + i] : 0.f;
+        ism[i] = s.i1[row * 3136 + i];
+    }
+    __syncthreads();
+    float* part = s.conv_part + row * NCONV;
+    if (tid < 400) {
+        const int o = tid / 25, ky = (tid % 25) / 5, kx = tid % 5;
+        float acc = 0.f;
+        for (int p = 0; p < 196; ++p) {
+            const int arg = ism[o * 196 + p];
+            const int y = 2 * (p / 14) + (arg >> 1), x = 2 * (p % 14) + (arg & 1);
+            acc += gsm[o * 196 + p] * xs[(y + ky) * 32 + x + kx];
+        }
+        part[C1W + tid] = acc;
+    } else {
+        const int o = tid - 400;
+        float acc = 0.f;
+        for (int p = 0; p < 196; ++p) acc += gsm[o * 196 + p];
+        part[C1B + o] = acc;
+    }
+}
+
+// reduce the per-image partials and apply SGD-momentum to the 13,248 conv parameters
+__global__ void __launch_bounds__(256) sgd_conv_train(const Step s) {
+    const int sel = blockIdx.y, p = blockIdx.x * 256 + threadIdx.x;
+    int lo;
+    if (batch_rows(s, sel, &lo) <= 0 || p >= NCONV) return;
+    const float* part = s.conv_part + (size_t)sel * BS * NCONV + p;
+    float g = 0.f;
+#pragma unroll 8
+    for (int b = 0; b < BS; ++b) g += part[(size_t)b * NCONV];
+    float* prm = s.params + (size_t)sel * s.nd;
+    float* mom = s.moment + (size_t)sel * s.nd;
+    const float m = s.momentum * mom[p] + g;
+    mom[p] = m;
+    prm[p] -= s.lr * m;
+}
+
+// ------------------------------------------------------------------------------------------
+// Evaluation head: fc1 + ReLU + fc2 + loss/argmax for 4 images per CTA (no dropout).
+constexpr int EVB = 4;
+__global__ void __launch_bounds__(256) head_eval(const float* __restrict__ a2, const int* __restrict__ labels,
+                                                 const float* __restrict__ prm, int n_classes, int N,
+                                                 float* __restrict__ out2) {
+    __shared__ float xs[EVB][1568];
+    __shared__ float h[EVB][64];
+    __shared__ float z[EVB][MAX_CLASSES];
+    const int tid = threadIdx.x, i0 = blockIdx.x * EVB;
+    for (int i = tid; i < EVB * 1568; i += 256) {
+        const int b = i / 1568;
+        xs[b][i % 1568] = (i0 + b) < N ? a2[(size_t)(i0 + b) * 1568 + i % 1568] : 0.f;
+    }
+    __syncthreads();
+    // 512 hidden outputs, 2 per thread: warp w handles feature pairs; coalesced W1 reads along k
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int f = warp; f < 64; f += 8) {
+        float acc[EVB] = {};
+        const float* w = prm + F1W + (size_t)f * 1568;
+        for (int k = lane; k < 1568; k += 32) {
+            const float wv = w[k];
+#pragma unroll
+            for (int b = 0; b < EVB; ++b) acc[b] += wv * xs[b][k];
+        }
+#pragma unroll
+        for (int b = 0; b < EVB; ++b) {
+            const float v = warp_sum(acc[b]);
+            if (lane == 0) h[b][f] = fmaxf(v + prm[F1B + f], 0.f);
+        }
+    }
+    __syncthreads();
+    if (tid < EVB * n_classes) {
+        const int b = tid / n_classes, c = tid % n_classes;
+        float v = prm[F2W + 64 * n_classes + c];
+        for (int f = 0; f < 64; ++f) v += h[b][f] * prm[F2W + c * 64 + f];
+        z[b][c] = v;
+    }
+    __syncthreads();
+    if (tid < EVB && i0 + tid < N) {
+        const int b = tid, y = labels[i0 + b];
+        float m = z[b][0]; int arg = 0;
+        for (int c = 1; c < n_classes; ++c) if (z[b][c] > m) { m = z[b][c]; arg = c; }
+        float sum = 0.f;
+        for (int c = 0; c < n_classes; ++c) sum += expf(z[b][c] - m);
+        atomicAdd(out2, m + logf(sum) - z[b][y]);
+        atomicAdd(out2 + 1, arg == y ? 1.f : 0.f);
+    }
+}
+
+static bool g_attr_set = false;
+static int set_attrs() {
+    if (g_attr_set) return 0;
+    QFX_CUDA_TRY(cudaFuncSetAttribute(conv2_fwd_train, cudaFuncAttributeMaxDynamicSharedMemorySize, CONV2_SMEM));
+    QFX_CUDA_TRY(cudaFuncSetAttribute(conv2_fwd_eval, cudaFuncAttributeMaxDynamicSharedMemorySize, CONV2_SMEM));
+    QFX_CUDA_TRY(cudaFuncSetAttribute(conv2_dgrad_train, cudaFuncAttributeMaxDynamicSharedMemorySize, DGRAD_SMEM));
+    QFX_CUDA_TRY(cudaFuncSetAttribute(conv2_wgrad_train, cudaFuncAttributeMaxDynamicSharedMemorySize, WGRAD_SMEM));
+    g_attr_set = true;
+    return 0;
+}
+
+}  // namespace cnn
+}  // namespace qfx
+
+using namespace qfx;
+using namespace qfx::cnn;
+
+extern "C" int qfx_tinycnn_workspace_bytes(int n_selected, size_t* bytes) {
+    // a1,i1,a2,i2,fc1_part,h1,dh1,g2,da1,conv_part,stats  (256-byte aligned pieces)
+    const size_t K = (size_t)n_selected;
+    size_t tot = 0;
+    auto add = [&](size_t n) { tot += (n + 255) & ~(size_t)255; };
+    add(K * BS * 3136 * 4); add(K * BS * 3136); add(K * BS * 1568 * 4); add(K * BS * 1568);
+    add(K * FC1_SLICES * BS * 64 * 4); add(K * BS * 64 * 4); add(K * BS * 64 * 4);
+    add(K * BS * 32 * 196 * 4); add(K * BS * 3136 * 4); add(K * BS * NCONV * 4); add(K * 2 * 4);
+    *bytes = tot;
+    return 0;
+}
+
+// One SGD step for every selected client: 9 kernels on `stream` (capture them in a CUDA graph).
+// `workspace` comes from qfx_tinycnn_workspace_bytes; stats (last 2K floats of it) accumulate the
+// epoch's loss sum and correct count - zero them with qfx_tinycnn_reset_stats.
+extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const int* offsets, const int* perm,
+                                      int n_total, const int* client_ids, int n_selected, int epoch,
+                                      int batch_index, int batch_size, float* params, float* moment, int nd,
+                                      int n_classes, float lr, float momentum, float p_drop,
+                                      unsigned long long seed, int round, void* workspace, cudaStream_t stream) {
+    QFX_ARG_CHECK(batch_size >= 1 && batch_size <= BS, QFX_ERR_UNSUPPORTED,
+                  "client-batched TinyCNN supports batch_size <= %d, got %d", BS, batch_size);
+    QFX_ARG_CHECK(n_classes >= 2 && n_classes <= MAX_CLASSES, QFX_ERR_UNSUPPORTED, "n_classes %d not in 2..10", n_classes);
+    QFX_ARG_CHECK(nd >= F2W + 65 * n_classes, QFX_ERR_BAD_ARG, "parameter row stride too small");
+    QFX_ARG_CHECK(n_selected >= 1 && p_drop >= 0.f && p_drop < 1.f, QFX_ERR_BAD_ARG, "bad n_selected / p_drop");
+    if (int e = set_attrs()) return e;
+    const size_t K = (size_t)n_selected;
+    Step s;
+    s.X = X; s.labels = labels; s.offsets = offsets; s.perm = perm; s.client_ids = client_ids;
+    s.n_total = n_total; s.epoch = epoch; s.batch_index = batch_index; s.batch_size = batch_size;
+    s.params = params; s.moment = moment; s.nd = nd; s.n_classes = n_classes;
+    s.lr = lr; s.momentum = momentum; s.p_drop = p_drop; s.seed = seed; s.round = round;
+    char* w = (char*)workspace;
+    auto take = [&](size_t n) { char* p = w; w += (n + 255) & ~(size_t)255; return p; };
+    s.a1 = (float*)take(K * BS * 3136 * 4); s.i1 = (unsigned char*)take(K * BS * 3136);
+    s.a2 = (float*)take(K * BS * 1568 * 4); s.i2 = (unsigned char*)take(K * BS * 1568);
+    s.fc1_part = (float*)take(K * FC1_SLICES * BS * 64 * 4);
+    s.h1 = (float*)take(K * BS * 64 * 4); s.dh1 = (float*)take(K * BS * 64 * 4);
+    s.g2 = (float*)take(K * BS * 32 * 196 * 4); s.da1 = (float*)take(K * BS * 3136 * 4);
+    s.conv_part = (float*)take(K * BS * NCONV * 4); s.stats = (float*)take(K * 2 * 4);
+    const dim3 gimg(batch_size, n_selected);
+    conv1_fwd_train<<<gimg, 224, 0, stream>>>(s);
+    conv2_fwd_train<<<gimg, 224, CONV2_SMEM, stream>>>(s);
+    fc1_fwd_train<<<dim3(FC1_SLICES, n_selected), 128, 0, stream>>>(s);
+    head_train<<<n_selected, 256, 0, stream>>>(s);
+    fc1_bwd_train<<<dim3(49, n_selected), 256, 0, stream>>>(s);
+    conv2_dgrad_train<<<gimg, 224, DGRAD_SMEM, stream>>>(s);
+    conv2_wgrad_train<<<dim3(BS, n_selected), 320, WGRAD_SMEM, stream>>>(s);
+    conv1_wgrad_train<<<gimg, 416, 0, stream>>>(s);
+    sgd_conv_train<<<dim3((NCONV + 255) / 256, n_selected), 256, 0, stream>>>(s);
+    return check_launch("tinycnn_train_step");
+}
+
+extern "C" int qfx_tinycnn_stats_offset(int n_selected, size_t* offset) {
+    size_t tot = 0;
+    qfx_tinycnn_workspace_bytes(n_selected, &tot);
+    *offset = tot - (((size_t)n_selected * 8 + 255) & ~(size_t)255);
+    return 0;
+}
+
+// Evaluation: forward over N images with one parameter vector; out2 = (loss sum, #correct).
+// scratch: N*(3136*4 + 3136 + 1568*4 + 1568) bytes.
+extern "C" int qfx_tinycnn_eval(const float* X, const int* labels, int n, const float* params, int n_classes,
+                                void* scratch, float* out2, cudaStream_t stream) {
+    QFX_ARG_CHECK(n >= 1 && n_classes >= 2 && n_classes <= MAX_CLASSES, QFX_ERR_BAD_ARG, "bad n / n_classes");
+    if (int e = set_attrs()) return e;
+    char* w = (char*)scratch;
+    float* a1 = (float*)w; w += (size_t)n * 3136 * 4;
+    float* a2 = (float*)w; w += (size_t)n * 1568 * 4;
+    unsigned char* i1 = (unsigned char*)w; w += (size_t)n * 3136;
+    unsigned char* i2 = (unsigned char*)w;
+    QFX_CUDA_TRY(cudaMemsetAsync(out2, 0, 2 * sizeof(float), stream));
+    conv1_fwd_eval<<<n, 224, 0, stream>>>(X, params, a1, i1);
+    conv2_fwd_eval<<<n, 224, CONV2_SMEM, stream>>>(a1, params, a2, i2);
+    head_eval<<<(n + EVB - 1) / EVB, 256, 0, stream>>>(a2, labels, params, n_classes, n, out2);
+    return check_launch("tinycnn_eval");
+}

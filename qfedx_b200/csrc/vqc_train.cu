@@ -40,20 +40,16 @@ struct TrainArgs {
     int grad_mode;            // 0 adjoint, 1 parameter shift
 };
 
-struct SmemSink {
-    float* dst;
+// Gradient sink: reduce over the whole warp (dead circuits contribute zero), then lane 0 adds into
+// the warp's private row of the shared-memory gradient matrix - no atomics, no contention.
+struct WarpRowSink {
+    float* row;
     bool live;
-    int lg;
-    template <int LANES>
-    __device__ __forceinline__ void add(int p, float v) {
-        v = group_sum<LANES>(v);
-        if (live && lg == 0) atomicAdd(dst + p, v);
+    int lane;
+    __device__ __forceinline__ void operator()(int p, float v) {
+        v = warp_sum(live ? v : 0.f);
+        if (lane == 0) row[p] += v;
     }
-};
-template <int LANES>
-struct SmemSinkFn {
-    SmemSink s;
-    __device__ __forceinline__ void operator()(int p, float v) { s.add<LANES>(p, v); }
 };
 
 // loss and d loss / d logits for one sample; z has n_classes entries (1 => BCE-with-logits)
@@ -81,10 +77,10 @@ __device__ __forceinline__ float loss_and_grad(const float* z, float* dz, int n_
     return m + logf(sum) - zy;
 }
 
-template <int NQ>
+template <int NQ, int LB_>
 __global__ void __launch_bounds__(TR_THREADS)
 vqc_local_train_kernel(const TrainArgs a) {
-    using C = SvCfg<NQ>;
+    using C = SvCfg<NQ, LB_>;
     cg::cluster_group cluster = cg::this_cluster();
     const int cs = (int)cluster.num_blocks();
     const int crank = (int)cluster.block_rank();
@@ -94,12 +90,20 @@ vqc_local_train_kernel(const TrainArgs a) {
     const int NC = a.n_classes;
     const int D = P + 2 * NC;
 
-    __shared__ float2 tab[TR_MAX_P];
-    __shared__ float prm[TR_MAX_D];
-    __shared__ float sgrad[TR_MAX_D + 2];  // [D] loss sum, [D+1] correct count
-    __shared__ float m1[TR_MAX_D];
-    __shared__ float m2[TR_MAX_D];
-    __shared__ float scot[TR_MAX_BS_SHIFT * NQ];  // parameter-shift mode: per-sample cotangents
+    // dynamic shared memory: tab float2[P] | dloc float2[L*A] | dlane float2[L*LANES] | prm[D] | m1[D] |
+    // m2[D] | sgrad[NW][DS] | scot[bs*NQ]
+    extern __shared__ __align__(16) float smem[];
+    constexpr int NW = TR_THREADS / 32;
+    const int DS = (D + 2 + 3) & ~3;  // row stride; [D] loss sum, [D+1] correct count
+    float2* tab = reinterpret_cast<float2*>(smem);
+    float2* dloc = tab + P;
+    float2* dlane = dloc + a.n_layers * C::A;
+    float* prm = reinterpret_cast<float*>(dlane + a.n_layers * C::LANES);
+    const DiagTables dt{dloc, dlane};
+    float* m1 = prm + D;
+    float* m2 = m1 + D;
+    float* sgrad = m2 + D;
+    float* scot = sgrad + NW * DS;
 
     const int tid = threadIdx.x;
     for (int p = tid; p < D; p += TR_THREADS) {
@@ -107,6 +111,8 @@ vqc_local_train_kernel(const TrainArgs a) {
         prm[p] = v; m1[p] = 0.f; m2[p] = 0.f;
         if (p < P) { float s, c; sincosf(0.5f * v, &s, &c); tab[p] = make_float2(c, s); }
     }
+    __syncthreads();
+    build_diag_tables<NQ, LB_>(dloc, dlane, tab, a.n_layers, tid, TR_THREADS);
     __syncthreads();
 
     const int lg = tid & (C::LANES - 1);
@@ -118,7 +124,7 @@ vqc_local_train_kernel(const TrainArgs a) {
     const int n_k = a.offsets[client + 1] - seg_lo;
     const int n_batches = (n_k + a.batch_size - 1) / a.batch_size;
     float epoch_loss = 0.f, epoch_correct = 0.f;
-    int step = 0;
+    float b1t = 1.f, b2t = 1.f;  // beta^t for the Adam bias correction
 
     for (int e = 0; e < a.epochs; ++e) {
         epoch_loss = 0.f; epoch_correct = 0.f;
@@ -126,8 +132,10 @@ vqc_local_train_kernel(const TrainArgs a) {
         for (int bi = 0; bi < n_batches; ++bi) {
             const int b_lo = bi * a.batch_size;
             const int nb = min(a.batch_size, n_k - b_lo);
-            for (int p = tid; p < D + 2; p += TR_THREADS) sgrad[p] = 0.f;
+            for (int p = tid; p < NW * DS; p += TR_THREADS) sgrad[p] = 0.f;
             __syncthreads();
+            float* my_row = sgrad + (tid >> 5) * DS;
+            const int lane = tid & 31;
 
             const int n_pass = (nb + slots_all - 1) / slots_all;
             for (int ps = 0; ps < n_pass; ++ps) {
@@ -137,10 +145,9 @@ vqc_local_train_kernel(const TrainArgs a) {
                 const int sidx = perm_e ? perm_e[b_lo + jj] : (seg_lo + b_lo + jj);
                 const int y = a.labels[sidx];
 
-                Sv<NQ> psi;
+                Sv<NQ, LB_> psi;
                 psi.set_product(a.angles + (size_t)sidx * NQ, a.basis, lg);
-                TrigTable trig{tab, -1, 0.f};
-                ansatz_forward<NQ>(psi, trig, a.n_layers, a.ent, lg);
+                ansatz_forward_merged(psi, tab, dt, a.n_layers, a.ent, lg);
                 float ez[NQ];
                 psi.expval_z_all(ez, lg);
 
@@ -153,21 +160,23 @@ vqc_local_train_kernel(const TrainArgs a) {
                 float cot[NQ];
 #pragma unroll
                 for (int q = 0; q < NQ; ++q) cot[q] = (q < NC) ? dz[q] * prm[P + q] : 0.f;
-                if (live && lg == 0) {
+                {
+                    // readout and statistics: one contribution per circuit (its lane 0)
+                    WarpRowSink once{my_row, live && lg == 0, lane};
 #pragma unroll
                     for (int q = 0; q < NQ; ++q)
                         if (q < NC) {
-                            atomicAdd(&sgrad[P + q], dz[q] * ez[q]);
-                            atomicAdd(&sgrad[P + NC + q], dz[q]);
+                            once(P + q, dz[q] * ez[q]);
+                            once(P + NC + q, dz[q]);
                         }
-                    atomicAdd(&sgrad[D], loss);
-                    atomicAdd(&sgrad[D + 1], correct ? 1.f : 0.f);
+                    once(D, loss);
+                    once(D + 1, correct ? 1.f : 0.f);
                 }
                 if (a.grad_mode == 0) {
-                    Sv<NQ> lam;
+                    Sv<NQ, LB_> lam;
                     lam.set_obs_times(psi, cot, lg);
-                    SmemSinkFn<C::LANES> sink{{sgrad, live, lg}};
-                    ansatz_backward<NQ>(psi, lam, trig, a.n_layers, a.ent, lg, sink);
+                    WarpRowSink sink{my_row, live, lane};
+                    ansatz_backward_merged(psi, lam, tab, dt, a.n_layers, a.ent, lg, sink);
                 } else if (live && lg == 0) {
 #pragma unroll
                     for (int q = 0; q < NQ; ++q) scot[j * NQ + q] = cot[q];
@@ -190,15 +199,16 @@ vqc_local_train_kernel(const TrainArgs a) {
                     const int sidx = perm_e ? perm_e[b_lo + j] : (seg_lo + b_lo + j);
                     const int owner = (j % slots_all) / slots_cta;
                     const float* cot_src = cluster.map_shared_rank(scot, owner);
-                    Sv<NQ> psi;
+                    Sv<NQ, LB_> psi;
                     psi.set_product(a.angles + (size_t)sidx * NQ, a.basis, lg);
                     TrigTable trig{tab, p, sgn};
-                    ansatz_forward<NQ>(psi, trig, a.n_layers, a.ent, lg);
+                    ansatz_forward(psi, trig, a.n_layers, a.ent, lg);
                     float ez[NQ];
                     psi.expval_z_all(ez, lg);
                     float v = 0.f;
 #pragma unroll
                     for (int q = 0; q < NQ; ++q) v += cot_src[j * NQ + q] * ez[q];
+                    // p differs between the circuits of a warp here, so this one stays an atomic
                     if (live && lg == 0) atomicAdd(&sgrad[p], 0.5f * sgn * v);
                 }
             }
@@ -211,16 +221,16 @@ vqc_local_train_kernel(const TrainArgs a) {
                 const int p = tid + r * TR_THREADS;
                 float acc = 0.f;
                 if (p < D + 2) {
-                    if (cs > 1) {
-                        for (int c = 0; c < cs; ++c) acc += cluster.map_shared_rank(sgrad, c)[p];
-                    } else {
-                        acc = sgrad[p];
+                    for (int c = 0; c < cs; ++c) {
+                        const float* src = cs > 1 ? cluster.map_shared_rank(sgrad, c) : sgrad;
+#pragma unroll
+                        for (int w = 0; w < NW; ++w) acc += src[w * DS + p];
                     }
                 }
                 gsum[r] = acc;
             }
             if (cs > 1) cluster.sync(); else __syncthreads();
-            ++step;
+            b1t *= a.beta1; b2t *= a.beta2;
             const float inv_nb = 1.f / (float)nb;
 #pragma unroll
             for (int r = 0; r < (TR_MAX_D + 2 + TR_THREADS - 1) / TR_THREADS; ++r) {
@@ -236,9 +246,7 @@ vqc_local_train_kernel(const TrainArgs a) {
                         const float mm = a.beta1 * m1[p] + (1.f - a.beta1) * g;
                         const float vv = a.beta2 * m2[p] + (1.f - a.beta2) * g * g;
                         m1[p] = mm; m2[p] = vv;
-                        const float bc1 = 1.f - powf(a.beta1, (float)step);
-                        const float bc2 = 1.f - powf(a.beta2, (float)step);
-                        w -= a.lr * (mm / bc1) / (sqrtf(vv / bc2) + a.eps);
+                        w -= a.lr * (mm / (1.f - b1t)) / (sqrtf(vv / (1.f - b2t)) + a.eps);
                     }
                     prm[p] = w;
                     if (p < P) { float s, c; sincosf(0.5f * w, &s, &c); tab[p] = make_float2(c, s); }
@@ -248,6 +256,8 @@ vqc_local_train_kernel(const TrainArgs a) {
                     epoch_correct += gsum[r];
                 }
             }
+            __syncthreads();
+            build_diag_tables<NQ, LB_>(dloc, dlane, tab, a.n_layers, tid, TR_THREADS);
             __syncthreads();
         }
     }
@@ -290,7 +300,7 @@ vqc_eval_kernel(int n_layers, int basis, int ent, int n_classes, const float* __
         Sv<NQ> psi;
         psi.set_product(angles + (size_t)jj * NQ, basis, lg);
         TrigTable trig{tab, -1, 0.f};
-        ansatz_forward<NQ>(psi, trig, n_layers, ent, lg);
+        ansatz_forward(psi, trig, n_layers, ent, lg);
         float ez[NQ];
         psi.expval_z_all(ez, lg);
         float z[TR_MAX_C], dz[TR_MAX_C];
@@ -308,23 +318,40 @@ vqc_eval_kernel(int n_layers, int basis, int ent, int n_classes, const float* __
     if (tid < 2) atomicAdd(out + tid, red[tid]);
 }
 
+template <int NQ, int LB_>
+static int launch_train(const TrainArgs& a, int n_sel, int cluster_size, cudaStream_t st) {
+    using C = SvCfg<NQ, LB_>;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(n_sel * cluster_size));
+    cfg.blockDim = dim3(TR_THREADS);
+    const int P = 2 * NQ * a.n_layers, D = P + 2 * a.n_classes;
+    const int DS = (D + 2 + 3) & ~3;
+    const size_t smem = sizeof(float) * (size_t)(2 * P + 2 * a.n_layers * (C::A + C::LANES) + 3 * D +
+                                                 (TR_THREADS / 32) * DS + (a.grad_mode == 1 ? a.batch_size * NQ : 0));
+    QFX_ARG_CHECK(smem <= 200 * 1024, QFX_ERR_TOO_LARGE, "training state needs %zu bytes of shared memory", smem);
+    if (smem > 48 * 1024)
+        QFX_CUDA_TRY(cudaFuncSetAttribute(vqc_local_train_kernel<NQ, LB_>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)cluster_size;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    QFX_CUDA_TRY(cudaLaunchKernelEx(&cfg, vqc_local_train_kernel<NQ, LB_>, a));
+    return 0;
+}
+
+// lane_mode 0: throughput split (most amplitudes per lane); 1: latency split (most lanes per circuit)
 template <int NQ>
 struct TrainLaunch {
-    static int run(const TrainArgs& a, int n_sel, int cluster_size, cudaStream_t st) {
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3((unsigned)(n_sel * cluster_size));
-        cfg.blockDim = dim3(TR_THREADS);
-        cfg.dynamicSmemBytes = 0;
-        cfg.stream = st;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = (unsigned)cluster_size;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        QFX_CUDA_TRY(cudaLaunchKernelEx(&cfg, vqc_local_train_kernel<NQ>, a));
-        return 0;
+    static int run(const TrainArgs& a, int n_sel, int cluster_size, int lane_mode, cudaStream_t st) {
+        constexpr int LT = default_lane_bits(NQ), LL = latency_lane_bits(NQ);
+        if (lane_mode == 1 && LL != LT) return launch_train<NQ, LL>(a, n_sel, cluster_size, st);
+        return launch_train<NQ, LT>(a, n_sel, cluster_size, st);
     }
 };
 template <int NQ>
@@ -367,7 +394,7 @@ extern "C" int qfx_vqc_local_train(int n_qubits, int n_layers, int basis, int en
                                    int n_total, const float* params_in, const int* client_ids, int n_selected,
                                    float* params_out, float* stats_out, int epochs, int batch_size, int optimizer,
                                    float lr, float beta1, float beta2, float eps, int grad_mode, int cluster_size,
-                                   cudaStream_t stream) {
+                                   int lane_mode, cudaStream_t stream) {
     QFX_ARG_CHECK(n_qubits >= 1 && n_qubits <= 10, QFX_ERR_UNSUPPORTED, "n_qubits %d not in 1..10", n_qubits);
     QFX_ARG_CHECK(n_layers >= 1 && 2 * n_qubits * n_layers <= TR_MAX_P, QFX_ERR_TOO_LARGE, "too many parameters");
     QFX_ARG_CHECK(n_classes >= 1 && n_classes <= n_qubits && n_classes <= TR_MAX_C, QFX_ERR_BAD_ARG,
@@ -383,7 +410,7 @@ extern "C" int qfx_vqc_local_train(int n_qubits, int n_layers, int basis, int en
     a.params_in = params_in; a.client_ids = client_ids; a.params_out = params_out; a.stats_out = stats_out;
     a.epochs = epochs; a.batch_size = batch_size; a.opt = optimizer; a.lr = lr; a.beta1 = beta1; a.beta2 = beta2;
     a.eps = eps; a.grad_mode = grad_mode;
-    return dispatch_nq2<TrainLaunch>(n_qubits, a, n_selected, cluster_size, stream);
+    return dispatch_nq2<TrainLaunch>(n_qubits, a, n_selected, cluster_size, lane_mode, stream);
 }
 
 extern "C" int qfx_vqc_eval(int n_qubits, int n_layers, int basis, int entangler, int n_classes,

@@ -49,15 +49,22 @@ class FLConfig:
 
 
 class FederatedRunner:
-    def __init__(self, trainer, cfg: FLConfig, test_data=None, aggregator=None):
+    def __init__(self, trainer, cfg: FLConfig, test_data=None, aggregator=None, client_gids=None,
+                 global_weights=None):
+        """``client_gids``/``global_weights`` place this process in a multi-rank job: the trainer's
+        local clients have these global ids and ``global_weights`` holds every client's sample
+        count; sampling and dropouts are then decided over the global population (identically on
+        every rank, they are pure functions of seed and round)."""
         self.trainer, self.cfg, self.test_data = trainer, cfg, test_data
         self.aggregator = aggregator  # optional multi-GPU aggregator with the same call signature
+        self.client_gids = None if client_gids is None else [int(g) for g in client_gids]
+        self.global_weights = global_weights
         self.global_flat = trainer.global_flat().clone()
         self.accountant = RDPAccountant()
         self.history = {"accuracy": [], "loss": [], "epsilon": [], "round_ms": []}
         self.round = 0
         self.logger = RoundLogger(cfg.log_path, cfg.tensorboard_dir, cfg.print_every, cfg.quiet)
-        self._weights = trainer.weights
+        self._weights = trainer.weights if global_weights is None else torch.as_tensor(global_weights, dtype=torch.float32)
         if cfg.resume and cfg.checkpoint_dir:
             ck = latest_checkpoint(cfg.checkpoint_dir)
             if ck:
@@ -94,11 +101,25 @@ class FederatedRunner:
         K = len(self._weights)
         selected = sample_clients(K, cfg.client_fraction, rnd, cfg.seed, cfg.poisson_sampling)
         survivors = inject_dropouts(selected, cfg.drop_prob, rnd, cfg.seed)
-        client_params, stats = self.trainer.train(self.global_flat, survivors, rnd)
-        w = self._weights[torch.as_tensor(survivors, dtype=torch.long)]
-        agg = self.aggregator or fedavg_aggregate
-        res = agg(client_params, self.global_flat, w, None, mode=cfg.mode, n_wrap=self.trainer.n_wrap if cfg.mode == "delta" else 0,
-                  clip=cfg.clip, sigma=cfg.sigma, server_lr=cfg.server_lr, seed=cfg.seed, rnd=rnd, secagg=cfg.secagg)
+        n_wrap = self.trainer.n_wrap if cfg.mode == "delta" else 0
+        common = dict(mode=cfg.mode, n_wrap=n_wrap, clip=cfg.clip, sigma=cfg.sigma, server_lr=cfg.server_lr,
+                      seed=cfg.seed, rnd=rnd, secagg=cfg.secagg)
+        if self.client_gids is None:
+            client_params, stats = self.trainer.train(self.global_flat, survivors, rnd)
+            w = self._weights[torch.as_tensor(survivors, dtype=torch.long)]
+            res = (self.aggregator or fedavg_aggregate)(client_params, self.global_flat, w, None, **common)
+        else:
+            alive = set(int(s) for s in survivors)
+            rows = [i for i, g in enumerate(self.client_gids) if g in alive]
+            if rows:
+                client_params, stats = self.trainer.train(self.global_flat, rows, rnd)
+            else:
+                client_params, stats = None, {}
+            part = torch.zeros(K, dtype=torch.int32)
+            part[torch.as_tensor(survivors, dtype=torch.long)] = 1
+            w = self._weights[torch.as_tensor(survivors, dtype=torch.long)]
+            res = self.aggregator(client_params, self.global_flat, self._weights, part,
+                                  gids=[self.client_gids[i] for i in rows], **common)
         self.global_flat = res.new_global
         if cfg.mode == "delta" and cfg.clip > 0 and cfg.sigma > 0:
             # per-client noise sigma*C on each of m averaged updates: the aggregate carries noise of

@@ -115,7 +115,7 @@ class VQCFusedTrainer:
     def __init__(self, model: VQC, data: FederatedDataset, epochs: int = 5, batch_size: int = 32,
                  lr: float = 0.05, optimizer: str = "adam", momentum: float = 0.9, betas=(0.9, 0.999),
                  eps: float = 1e-8, grad_method: str = "adjoint", cluster_size: int = 0, shuffle: bool = True,
-                 generator=None):
+                 generator=None, lane_mode: str = "latency"):
         if model.encoding != "angle":
             raise ValueError("the fused trainer takes angle-encoded features")
         self.model, self.data = model, data
@@ -128,8 +128,13 @@ class VQCFusedTrainer:
         if self.cuda:
             self.angles = data.X.contiguous().float()
             self.labels = data.y.to(torch.int32).contiguous()
-            lanes = 1 << max(0, min(model.n_qubits - 4, 5)) if model.n_qubits <= 9 else 32
-            slots = 256 // lanes
+            n = model.n_qubits
+            self.lane_mode = 1 if lane_mode == "latency" else 0
+            if self.lane_mode == 1:
+                lane_bits = 0 if n <= 1 else min(n - 1, 5)
+            else:
+                lane_bits = 0 if n <= 4 else (n - 4 if n <= 9 else 5)
+            slots = 256 >> lane_bits
             if cluster_size <= 0:  # enough CTAs to cover one minibatch in a single pass, at most 8
                 cluster_size = 1
                 while cluster_size < 8 and slots * cluster_size < batch_size:
@@ -173,7 +178,7 @@ class VQCFusedTrainer:
                   _lib.c_int(OPTIMIZERS[self.optimizer]), _lib.c_float(self.lr), _lib.c_float(beta1),
                   _lib.c_float(self.betas[1]), _lib.c_float(self.eps),
                   _lib.c_int(0 if self.grad_method == "adjoint" else 1), _lib.c_int(self.cluster_size),
-                  _lib.stream_ptr())
+                  _lib.c_int(self.lane_mode), _lib.stream_ptr())
         self.launches += 1
         self._last_stats = stats
         return out, {"train_stats": stats}

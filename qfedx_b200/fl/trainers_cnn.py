@@ -1,0 +1,162 @@
+"""Client-batched TinyCNN trainer (K8): every SGD step of every selected client in one sequence of
+nine kernels, the whole round (epochs x batches) replayed from a single CUDA graph.
+
+Semantics follow the reference's client_update (/root/reference/src/CFed/Classical_FL.py:40-64):
+fresh SGD(momentum) state per round, full passes over shuffled minibatches of 32, dropout 0.5
+before the last layer, cross-entropy loss; and its evaluate_model (:83-102).
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+import torch
+
+from ..models.tinycnn import TinyCNN, flatten_state, unflatten_state
+from ..ops import _lib
+from .dataset import FederatedDataset
+
+KERNELS_PER_STEP = 9
+
+
+class TinyCNNBatchedTrainer:
+    def __init__(self, model: TinyCNN, data: FederatedDataset, epochs: int = 5, batch_size: int = 32,
+                 lr: float = 0.01, momentum: float = 0.9, p_drop: float = 0.5, shuffle: bool = True, seed: int = 0,
+                 use_graph: bool = True, generator=None):
+        if data.device.type != "cuda":
+            raise _lib.QfxError("TinyCNNBatchedTrainer runs on CUDA only; use TorchLocalTrainer on CPU")
+        if batch_size > 32:
+            raise _lib.QfxError("the client-batched TinyCNN kernels support batch_size <= 32")
+        self.model, self.data = model, data
+        self.epochs, self.batch_size, self.lr, self.momentum, self.p_drop = epochs, batch_size, lr, momentum, p_drop
+        self.shuffle, self.seed, self.use_graph, self.generator = shuffle, seed, use_graph, generator
+        self.n_classes = model.num_classes
+        self.n_wrap = 0
+        self._template = {k: v.detach().clone() for k, v in model.state_dict().items()}
+        self.dim = sum(v.numel() for v in self._template.values())
+        self.nd = (self.dim + 63) // 64 * 64
+        dev = data.device
+        self.X = data.X.contiguous().float()
+        self.labels = data.y.to(torch.int32).contiguous()
+        self.launches = 0
+        self._graphs = {}
+        self._perm = None
+        self._eval_scratch = None
+        self._stream = torch.cuda.Stream(device=dev)
+
+    @property
+    def weights(self) -> torch.Tensor:
+        return torch.as_tensor(self.data.sizes, dtype=torch.float32)
+
+    def global_flat(self) -> torch.Tensor:
+        return flatten_state(self.model.state_dict()).to(self.data.device)
+
+    def load_flat(self, flat: torch.Tensor) -> None:
+        self.model.load_state_dict(unflatten_state(flat[: self.dim], self._template))
+
+    def upload(self, host_X: torch.Tensor, host_y: torch.Tensor) -> None:
+        """Refresh the resident dataset from (pinned) host memory - the per-round host->device copy
+        the reference performs at /root/reference/src/CFed/Classical_FL.py:47-48."""
+        self.X.copy_(host_X, non_blocking=True)
+        self.labels.copy_(host_y, non_blocking=True)
+
+    # ------------------------------------------------------------------------------------
+    def _state_for(self, sel_key, sel):
+        st = self._graphs.get(sel_key)
+        if st is not None:
+            return st
+        dev = self.data.device
+        K = len(sel)
+        nbytes = ctypes.c_size_t()
+        _lib.call("qfx_tinycnn_workspace_bytes", _lib.c_int(K), ctypes.byref(nbytes), launches=0)
+        off = ctypes.c_size_t()
+        _lib.call("qfx_tinycnn_stats_offset", _lib.c_int(K), ctypes.byref(off), launches=0)
+        st = {
+            "K": K,
+            "sel": torch.as_tensor(np.asarray(sel), dtype=torch.int32, device=dev),
+            "params": torch.empty(K, self.nd, device=dev),
+            "moment": torch.empty(K, self.nd, device=dev),
+            "ws": torch.empty(nbytes.value, dtype=torch.uint8, device=dev),
+            "stats_off": off.value,
+            "global": torch.empty(self.dim, device=dev),
+            "graph": None,
+            "steps": self.epochs * int(np.ceil(self.data.sizes[np.asarray(sel)].max() / self.batch_size)),
+        }
+        st["stats"] = st["ws"][off.value: off.value + K * 8].view(torch.float32).view(K, 2)
+        self._graphs[sel_key] = st
+        return st
+
+    def _enqueue_round(self, st, rnd_tensor_unused=None, rnd=0):
+        """Everything of one round's local training on the current stream."""
+        K = st["K"]
+        st["params"][:, : self.dim] = st["global"][None, :]
+        st["moment"].zero_()
+        n_batches = int(np.ceil(self.data.sizes[st["sel"].cpu().numpy()].max() / self.batch_size))
+        perm_ptr = _lib.ptr(self._perm) if self._perm is not None else _lib.ptr(None)
+        for e in range(self.epochs):
+            st["stats"].zero_()
+            for b in range(n_batches):
+                _lib.call("qfx_tinycnn_train_step", _lib.ptr(self.X), _lib.ptr(self.labels),
+                          _lib.ptr(self.data.offsets), perm_ptr, _lib.c_int(self.X.shape[0]), _lib.ptr(st["sel"]),
+                          _lib.c_int(K), _lib.c_int(e), _lib.c_int(b), _lib.c_int(self.batch_size),
+                          _lib.ptr(st["params"]), _lib.ptr(st["moment"]), _lib.c_int(self.nd),
+                          _lib.c_int(self.n_classes), _lib.c_float(self.lr), _lib.c_float(self.momentum),
+                          _lib.c_float(self.p_drop), _lib.c_u64(self.seed), _lib.c_int(rnd), _lib.ptr(st["ws"]),
+                          _lib.stream_ptr(), launches=KERNELS_PER_STEP)
+
+    def train(self, global_flat: torch.Tensor, selected, rnd: int):
+        sel = [int(k) for k in selected]
+        st = self._state_for(tuple(sel), sel)
+        if self.shuffle:
+            new_perm = self.data.epoch_permutations(self.epochs, self.generator)
+            if self._perm is None:
+                self._perm = new_perm
+            else:
+                self._perm.copy_(new_perm)  # same storage: the captured graph keeps pointing at it
+        st["global"].copy_(global_flat[: self.dim])
+        if not self.use_graph:
+            self._enqueue_round(st, rnd=rnd)
+        else:
+            if st["graph"] is None:
+                # dropout masks are keyed by (seed, round, client, epoch, batch); a captured graph bakes
+                # `round` in, so the seed is advanced per round through device memory instead: the
+                # kernels read the key from the arguments, hence one graph per distinct round value
+                # would be needed.  We capture with round = 0 and vary `self.seed`-independent masks by
+                # permuting samples each round (the mask of a slot then lands on a different sample).
+                torch.cuda.synchronize()
+                before = _lib.LAUNCH_COUNT
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=self._stream):
+                    self._enqueue_round(st, rnd=0)
+                st["graph"] = g
+                st["graph_launches"] = _lib.LAUNCH_COUNT - before
+                _lib.LAUNCH_COUNT = before
+            st["graph"].replay()
+            _lib.LAUNCH_COUNT += st["graph_launches"]
+        self.launches += st["steps"] * KERNELS_PER_STEP
+        out = st["params"][:, : self.dim]
+        return out, {"train_stats": st["stats"]}
+
+    def evaluate(self, global_flat: torch.Tensor, X: torch.Tensor, y: torch.Tensor, batch_size: int = 0):
+        n = X.shape[0]
+        need = n * 23520
+        if self._eval_scratch is None or self._eval_scratch.numel() < need:
+            self._eval_scratch = torch.empty(need, dtype=torch.uint8, device=X.device)
+        out2 = torch.empty(2, device=X.device)
+        prm = torch.zeros(self.nd, device=X.device)
+        prm[: self.dim] = global_flat[: self.dim]
+        _lib.call("qfx_tinycnn_eval", _lib.ptr(X.contiguous().float()), _lib.ptr(y.to(torch.int32).contiguous()),
+                  _lib.c_int(n), _lib.ptr(prm), _lib.c_int(self.n_classes), _lib.ptr(self._eval_scratch),
+                  _lib.ptr(out2), _lib.stream_ptr(), launches=3)
+        res = out2.cpu()
+        return float(res[0]) / n, float(res[1]) / n
+
+
+def smoke_tinycnn(dev) -> None:
+    from ..data.synthetic import synthetic_mnist
+    X, y = synthetic_mnist(96, 3, seed=0)
+    data = FederatedDataset.from_clients([(X[:48], y[:48]), (X[48:], y[48:])], dev)
+    tr = TinyCNNBatchedTrainer(TinyCNN(3).to(dev), data, epochs=1, batch_size=32, use_graph=False)
+    out, _ = tr.train(tr.global_flat(), [0, 1], 0)
+    loss, acc = tr.evaluate(out[0], X.to(dev), y.to(dev))
+    assert np.isfinite(loss) and torch.isfinite(out).all()

@@ -14,8 +14,6 @@ import numpy as np
 import torch
 
 from . import _lib
-from ..fl import dp as _dp
-from ..fl import secagg as _sa
 
 MODES = {"weights": 0, "delta": 1}
 
@@ -29,6 +27,8 @@ class AggResult:
 
 def _reference(client_params, global_params, weights, participate, mode, n_wrap, clip, sigma, server_lr,
                seed, rnd, secagg, want_masked, generator=None):
+    from ..fl import dp as _dp          # local imports: qfedx_b200.fl imports this module
+    from ..fl import secagg as _sa
     K, D = client_params.shape
     part = torch.ones(K, dtype=torch.bool) if participate is None else participate.bool().cpu()
     w = weights.double().cpu() * part.double()

@@ -100,8 +100,11 @@ def run_ansatz(psi, theta_per_state, entangler="cnot"):
 
 def vqc_state_ref(angles, theta, gid=None, basis="ry", entangler="cnot", init_state=None):
     """angles [B,n]; theta [G,L,n,2]; gid [B] int64 (None -> group 0)."""
-    th = theta[gid] if gid is not None else theta[:1].expand(angles.shape[0], *theta.shape[1:])
+    batch = angles.shape[0] if angles is not None else init_state.shape[0]
+    th = theta[gid] if gid is not None else theta[:1].expand(batch, *theta.shape[1:])
     psi = product_state(angles, basis) if init_state is None else init_state.to(_cdtype(theta.dtype))
+    if psi.real.dtype != th.dtype:
+        th = th.to(psi.real.dtype)
     return run_ansatz(psi, th, entangler)
 
 
