@@ -125,6 +125,24 @@ int qfx_tinycnn_train_step(const float* X, const int* labels, const int* offsets
 int qfx_tinycnn_eval(const float* X, const int* labels, int n, const float* params, int n_classes,
                      void* scratch, float* out2, cudaStream_t stream);
 
+/* K2: batched circuit unitaries as a complex GEMM on tcgen05 / TMEM fed by TMA (no reference
+ * counterpart; accelerates the planned VQC forward, /root/reference/ROADMAP.md:126-128).
+ *   qfx_unitary_pack: U^T as complex64 rows (row b = U|b>, e.g. qfx_sv_forward's state_out for the
+ *     2^n basis states) -> real embedding [[Ur,-Ui],[Ui,Ur]] split into tf32 hi / lo parts,
+ *     each [2*2^n, 2*2^n] fp32.
+ *   qfx_unitary_pack_product_states: feature-map angles [B,n] -> B operand rows [re | im], hi / lo,
+ *     [batch_padded, 2*2^n] (batch_padded multiple of 64, padding rows zero).
+ *   qfx_unitary_split_states: arbitrary input states [B, 2*2^n] -> hi / lo.
+ *   qfx_unitary_gemm: out_states [batch_padded, 2*2^n] (nullable) and/or <Z_q> expvals
+ *     [batch_padded, n] (nullable, fused in the epilogue); precision 3 = 3xTF32, 1 = TF32. */
+int qfx_unitary_pack(const float* u_transposed_c64, int n_qubits, float* a_hi, float* a_lo, cudaStream_t stream);
+int qfx_unitary_pack_product_states(const float* angles, int n_qubits, int basis, int batch, int batch_padded,
+                                    float* b_hi, float* b_lo, cudaStream_t stream);
+int qfx_unitary_split_states(const float* states, int n_qubits, int batch, int batch_padded, float* b_hi,
+                             float* b_lo, cudaStream_t stream);
+int qfx_unitary_gemm(const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, int n_qubits,
+                     int batch_padded, int precision, float* out_states, float* expvals, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -80,8 +80,9 @@ class TinyCNNBatchedTrainer:
             "stats_off": off.value,
             "global": torch.empty(self.dim, device=dev),
             "graph": None,
-            "steps": self.epochs * int(np.ceil(self.data.sizes[np.asarray(sel)].max() / self.batch_size)),
+            "n_batches": int(np.ceil(self.data.sizes[np.asarray(sel)].max() / self.batch_size)),
         }
+        st["steps"] = self.epochs * st["n_batches"]
         st["stats"] = st["ws"][off.value: off.value + K * 8].view(torch.float32).view(K, 2)
         self._graphs[sel_key] = st
         return st
@@ -91,7 +92,7 @@ class TinyCNNBatchedTrainer:
         K = st["K"]
         st["params"][:, : self.dim] = st["global"][None, :]
         st["moment"].zero_()
-        n_batches = int(np.ceil(self.data.sizes[st["sel"].cpu().numpy()].max() / self.batch_size))
+        n_batches = st["n_batches"]
         perm_ptr = _lib.ptr(self._perm) if self._perm is not None else _lib.ptr(None)
         for e in range(self.epochs):
             st["stats"].zero_()
