@@ -115,13 +115,15 @@ int qfx_enable_peer(int dev, int peer);
  * (loss sum, #correct) accumulators that the caller zeroes per epoch. */
 int qfx_tinycnn_workspace_bytes(int n_selected, size_t* bytes);
 int qfx_tinycnn_stats_offset(int n_selected, size_t* offset);
+/* once per round, after the global parameters were copied into every row of `params` */
+int qfx_tinycnn_begin_round(const float* params, int nd, int n_selected, void* workspace, cudaStream_t stream);
 int qfx_tinycnn_train_step(const float* X, const int* labels, const int* offsets, const int* perm, int n_total,
                            const int* client_ids, int n_selected, int epoch, int batch_index, int batch_size,
                            float* params, float* moment, int nd, int n_classes, float lr, float momentum,
                            float p_drop, unsigned long long seed, int round, void* workspace,
                            cudaStream_t stream);
 /* Evaluation (evaluate_model, /root/reference/src/CFed/Classical_FL.py:83-102) in three launches:
- * out2 = (loss sum, #correct); scratch needs n * 23,520 bytes. */
+ * out2 = (loss sum, #correct); scratch needs n * 23,520 + 102,400 bytes. */
 int qfx_tinycnn_eval(const float* X, const int* labels, int n, const float* params, int n_classes,
                      void* scratch, float* out2, cudaStream_t stream);
 

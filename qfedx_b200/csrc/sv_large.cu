@@ -1,0 +1,369 @@
+// K5 / K6: large statevectors (n > 10 qubits) in global memory.
+//
+// K5  sv_large_pass_kernel   one compiled pass (csrc/circuit_passes.cu): a CTA gathers the 2^T
+//     amplitudes of a tile (T <= 12, 32 KB) into shared memory, applies every gate of the pass
+//     there and scatters them back - several gates per trip through L2/HBM.  grid.y batches
+//     independent states (clients, or the 2P shifted circuits of the parameter-shift rule, each
+//     with its own angle shift), so a 20-qubit state (8 MiB, L2-resident on B200) is re-read from
+//     L2 rather than HBM between passes.
+// K3' sv_large_expz_kernel   <Z_q> for every qubit, with the shard's rank bits as high index bits.
+// K6  sv_global_swap_fused_kernel   sharded statevector: the top g "global" qubits are the rank
+//     index.  Exchanging them with the top g local qubits is an all-to-all of contiguous slices;
+//     each thread PULLS its 2^g amplitudes from the 2^g peers with plain loads over NVLink (peer
+//     pointers from the symmetric heap, no NCCL), applies the gates that follow on those qubits in
+//     registers, and writes the result locally - the swap and the next gates cost one pass.
+//
+// No reference counterpart (the reference never simulates more than one 4-qubit state,
+// /root/reference/src/QFed/qAmplitude.py:44-46); configs 4 and 5 of BASELINE.json.
+#include "common.cuh"
+#include "../../include/qfedx_b200.h"
+
+namespace qfx {
+namespace large {
+
+constexpr int MAX_TILE_BITS = 12;
+constexpr int MAX_OPS_PER_PASS = 160;
+constexpr int PASS_THREADS = 256;
+
+struct PassArgs {
+    float2* states;            // [batch][2^n]
+    int n_qubits, tile_bits, low_bits;
+    int tile_q[MAX_TILE_BITS]; // qubit of each tile bit, ascending
+    const int* ops;            // [n_ops][5] (kind, local bit 0, local bit 1, param 0, param 1)
+    int n_ops;
+    const float* theta;        // [theta_rows][n_params]; row = batch index % theta_rows
+    int theta_rows, n_params;
+    const float* angles;       // [angle_rows][n_feature]; feature-map angles (QFX_GATE_RY_FEATURE)
+    int angle_rows, n_feature;
+    const int* shift_param;    // [batch] parameter index to shift, -1 none (nullable)
+    const float* shift_value;  // [batch] shift in radians
+    int init_zero_state;       // 1: ignore memory contents, start from |0..0>
+};
+
+__device__ __forceinline__ void cmul_acc(float2& out, float2 m, float2 v) {
+    out.x += m.x * v.x - m.y * v.y;
+    out.y += m.x * v.y + m.y * v.x;
+}
+
+// 2x2 complex matrix (row-major m00 m01 m10 m11) of one op for this batch element
+__device__ __forceinline__ void op_matrix(const PassArgs& a, const int* op, int batch, float2* m) {
+    const int kind = op[0];
+    const float* th = a.theta ? a.theta + (size_t)(batch % a.theta_rows) * a.n_params : nullptr;
+    auto param = [&](int p) -> float {
+        float v = th[p];
+        if (a.shift_param && a.shift_param[batch] == p) v += a.shift_value[batch];
+        return v;
+    };
+    float s, c;
+    if (kind == QFX_GATE_RX) {
+        sincosf(0.5f * param(op[3]), &s, &c);
+        m[0] = make_float2(c, 0.f); m[1] = make_float2(0.f, -s); m[2] = make_float2(0.f, -s); m[3] = make_float2(c, 0.f);
+    } else if (kind == QFX_GATE_RY) {
+        sincosf(0.5f * param(op[3]), &s, &c);
+        m[0] = make_float2(c, 0.f); m[1] = make_float2(-s, 0.f); m[2] = make_float2(s, 0.f); m[3] = make_float2(c, 0.f);
+    } else if (kind == QFX_GATE_RY_FEATURE) {
+        sincosf(0.5f * a.angles[(size_t)(batch % a.angle_rows) * a.n_feature + op[3]], &s, &c);
+        m[0] = make_float2(c, 0.f); m[1] = make_float2(-s, 0.f); m[2] = make_float2(s, 0.f); m[3] = make_float2(c, 0.f);
+    } else if (kind == QFX_GATE_RZ) {
+        sincosf(0.5f * param(op[3]), &s, &c);
+        m[0] = make_float2(c, -s); m[1] = make_float2(0.f, 0.f); m[2] = make_float2(0.f, 0.f); m[3] = make_float2(c, s);
+    } else if (kind == QFX_GATE_RXRZ) {  // RZ(phi) * RX(theta)
+        float sp, cp;
+        sincosf(0.5f * param(op[3]), &s, &c);
+        sincosf(0.5f * param(op[4]), &sp, &cp);
+        m[0] = make_float2(cp * c, -sp * c);   // e^{-i phi/2} c
+        m[1] = make_float2(-sp * s, -cp * s);  // -i e^{-i phi/2} s
+        m[2] = make_float2(sp * s, -cp * s);   // -i e^{+i phi/2} s
+        m[3] = make_float2(cp * c, sp * c);    // e^{+i phi/2} c
+    } else {
+        m[0] = make_float2(1.f, 0.f); m[1] = make_float2(0.f, 0.f); m[2] = make_float2(0.f, 0.f); m[3] = make_float2(1.f, 0.f);
+    }
+}
+
+__global__ void __launch_bounds__(PASS_THREADS)
+sv_large_pass_kernel(const PassArgs a) {
+    extern __shared__ __align__(16) float2 tile[];        // [2^T]
+    __shared__ float2 mats[MAX_OPS_PER_PASS][4];
+    __shared__ int sops[MAX_OPS_PER_PASS][3];
+    const int tid = threadIdx.x, batch = blockIdx.y;
+    const int T = a.tile_bits, tile_n = 1 << T;
+    float2* st = a.states + ((size_t)batch << a.n_qubits);
+
+    for (int i = tid; i < a.n_ops; i += PASS_THREADS) {
+        const int* op = a.ops + 5 * i;
+        sops[i][0] = op[0]; sops[i][1] = op[1]; sops[i][2] = op[2];
+        op_matrix(a, op, batch, mats[i]);
+    }
+    // base offset of this tile: spread blockIdx.x over the non-tile bit positions
+    unsigned long long tile_mask = 0ull;
+    for (int b = 0; b < T; ++b) tile_mask |= 1ull << a.tile_q[b];
+    unsigned long long base = 0ull;
+    {
+        unsigned long long t = blockIdx.x;
+        for (int q = 0; q < a.n_qubits; ++q)
+            if (!((tile_mask >> q) & 1ull)) { base |= (t & 1ull) << q; t >>= 1; }
+    }
+    // gather: the low `low_bits` tile bits are qubits 0..low-1, so 2^low consecutive amplitudes move together
+    const int low = a.low_bits, chunk = 1 << low;
+    for (int j0 = tid * 1; j0 < tile_n; j0 += PASS_THREADS) {
+        const int jl = j0 & (chunk - 1), jh = j0 >> low;
+        unsigned long long off = base | (unsigned long long)jl;
+        for (int b = low; b < T; ++b) off |= (unsigned long long)((jh >> (b - low)) & 1) << a.tile_q[b];
+        float2 v;
+        if (a.init_zero_state) v = make_float2((off == 0ull) ? 1.f : 0.f, 0.f);
+        else v = st[off];
+        tile[j0] = v;
+    }
+    __syncthreads();
+
+    for (int i = 0; i < a.n_ops; ++i) {
+        const int kind = sops[i][0], b0 = sops[i][1], b1 = sops[i][2];
+        if (kind == QFX_GATE_CNOT) {
+            for (int idx = tid; idx < (tile_n >> 2); idx += PASS_THREADS) {
+                // insert zeros at bit positions lo < hi, then set control, toggle target
+                const int lo = min(b0, b1), hi = max(b0, b1);
+                int j = idx;
+                j = ((j >> lo) << (lo + 1)) | (j & ((1 << lo) - 1));
+                j = ((j >> hi) << (hi + 1)) | (j & ((1 << hi) - 1));
+                const int ja = j | (1 << b0), jb = ja | (1 << b1);
+                const float2 t = tile[ja]; tile[ja] = tile[jb]; tile[jb] = t;
+            }
+        } else if (kind == QFX_GATE_CZ) {
+            for (int idx = tid; idx < (tile_n >> 2); idx += PASS_THREADS) {
+                const int lo = min(b0, b1), hi = max(b0, b1);
+                int j = idx;
+                j = ((j >> lo) << (lo + 1)) | (j & ((1 << lo) - 1));
+                j = ((j >> hi) << (hi + 1)) | (j & ((1 << hi) - 1));
+                j |= (1 << b0) | (1 << b1);
+                tile[j] = make_float2(-tile[j].x, -tile[j].y);
+            }
+        } else if (kind == QFX_GATE_RZ) {
+            const float2 p0 = mats[i][0], p1 = mats[i][3];
+            for (int j = tid; j < tile_n; j += PASS_THREADS) {
+                const float2 v = tile[j], p = ((j >> b0) & 1) ? p1 : p0;
+                tile[j] = make_float2(p.x * v.x - p.y * v.y, p.x * v.y + p.y * v.x);
+            }
+        } else {
+            const float2 m00 = mats[i][0], m01 = mats[i][1], m10 = mats[i][2], m11 = mats[i][3];
+            for (int idx = tid; idx < (tile_n >> 1); idx += PASS_THREADS) {
+                const int j0 = ((idx >> b0) << (b0 + 1)) | (idx & ((1 << b0) - 1)), j1 = j0 | (1 << b0);
+                const float2 v0 = tile[j0], v1 = tile[j1];
+                float2 r0 = make_float2(0.f, 0.f), r1 = make_float2(0.f, 0.f);
+                cmul_acc(r0, m00, v0); cmul_acc(r0, m01, v1);
+                cmul_acc(r1, m10, v0); cmul_acc(r1, m11, v1);
+                tile[j0] = r0; tile[j1] = r1;
+            }
+        }
+        __syncthreads();
+    }
+
+    for (int j0 = tid; j0 < tile_n; j0 += PASS_THREADS) {
+        const int jl = j0 & (chunk - 1), jh = j0 >> low;
+        unsigned long long off = base | (unsigned long long)jl;
+        for (int b = low; b < T; ++b) off |= (unsigned long long)((jh >> (b - low)) & 1) << a.tile_q[b];
+        st[off] = tile[j0];
+    }
+}
+
+// <Z_q> for q < n_local taken from the index bits, for q >= n_local from `high_bits` (the rank)
+__global__ void __launch_bounds__(256)
+sv_large_expz_kernel(const float2* __restrict__ states, int n_local, int n_total, unsigned int high_bits,
+                     float* __restrict__ out /*[batch][n_total]*/) {
+    __shared__ float red[32];
+    const int batch = blockIdx.y, tid = threadIdx.x;
+    const float2* st = states + ((size_t)batch << n_local);
+    const size_t N = (size_t)1 << n_local;
+    float acc[32];
+#pragma unroll
+    for (int q = 0; q < 32; ++q) acc[q] = 0.f;
+    float tot = 0.f;
+    for (size_t i = (size_t)blockIdx.x * 256 + tid; i < N; i += (size_t)gridDim.x * 256) {
+        const float2 v = st[i];
+        const float p = v.x * v.x + v.y * v.y;
+        tot += p;
+#pragma unroll
+        for (int q = 0; q < 32; ++q)
+            if (q < n_local) acc[q] += ((i >> q) & 1) ? -p : p;
+    }
+    if (tid < 32) red[tid] = 0.f;
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < 32; ++q) {
+        if (q < n_total) {
+            float v = q < n_local ? acc[q] : (((high_bits >> (q - n_local)) & 1u) ? -tot : tot);
+            v = warp_sum(v);
+            if ((tid & 31) == 0) atomicAdd(&red[q], v);
+        }
+    }
+    __syncthreads();
+    if (tid < n_total) atomicAdd(out + (size_t)batch * n_total + tid, red[tid]);
+}
+
+// ------------------------------------------------------------------------------------------
+struct SwapArgs {
+    const float2* const* src;  // [world] peer pointers to every rank's current shard
+    float2* dst;               // local destination shard
+    int n_local, g_bits, rank, world;
+    const int* ops;            // fused gates on the swapped-in qubits: local bit = 0..g-1 (slice index bits)
+    int n_ops;
+    const float* theta; int n_params;
+    unsigned int* const* flags;  // [world] peer pointers to flag arrays [world]
+    unsigned int epoch;
+    unsigned int* counter;       // local u32 scratch for the grid-wide arrival count (zero before launch)
+};
+
+__device__ __forceinline__ void st_release_sys_u32(unsigned int* p, unsigned int v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+template <int G>
+__global__ void __launch_bounds__(256)
+sv_global_swap_fused_kernel(const SwapArgs a) {
+    constexpr int R = 1 << G;
+    __shared__ float2 mats[32][4];
+    __shared__ int sops[32][3];
+    const int tid = threadIdx.x;
+    // every rank's source shard must be complete before anyone reads it: one flag per (dst, src)
+    if (a.flags != nullptr) {
+        if (blockIdx.x == 0 && tid < a.world) st_release_sys_u32(a.flags[tid] + a.rank, a.epoch);
+        if (tid < a.world) {
+            const unsigned int* f = a.flags[a.rank] + tid;
+            while ((int)(ld_acquire_sys_u32(f) - a.epoch) < 0) { __nanosleep(32); }
+        }
+    }
+    for (int i = tid; i < a.n_ops; i += 256) {
+        const int* op = a.ops + 5 * i;
+        sops[i][0] = op[0]; sops[i][1] = op[1]; sops[i][2] = op[2];
+        PassArgs pa = {};
+        pa.theta = a.theta; pa.theta_rows = 1; pa.n_params = a.n_params;
+        op_matrix(pa, op, 0, mats[i]);
+    }
+    __syncthreads();
+    const int slice_bits = a.n_local - G;
+    const size_t slice = (size_t)1 << slice_bits;
+    const float2* srcs[R];
+#pragma unroll
+    for (int s = 0; s < R; ++s) srcs[s] = a.src[s] + ((size_t)a.rank << slice_bits);
+    for (size_t j = ((size_t)blockIdx.x * 256 + tid) * 2; j < slice; j += (size_t)gridDim.x * 512) {
+        float4 v[R];  // two consecutive amplitudes from every peer (16-byte loads over NVLink)
+#pragma unroll
+        for (int s = 0; s < R; ++s) v[s] = *reinterpret_cast<const float4*>(srcs[s] + j);
+        for (int i = 0; i < a.n_ops; ++i) {
+            const int kind = sops[i][0], b0 = sops[i][1], b1 = sops[i][2];
+            if (kind == QFX_GATE_CNOT) {
+#pragma unroll
+                for (int s = 0; s < R; ++s)
+                    if (((s >> b0) & 1) && !((s >> b1) & 1)) {
+                        const int t = s | (1 << b1);
+                        if (t < R) { const float4 tmp = v[s]; v[s] = v[t]; v[t] = tmp; }
+                    }
+            } else if (kind == QFX_GATE_CZ) {
+#pragma unroll
+                for (int s = 0; s < R; ++s)
+                    if (((s >> b0) & 1) && ((s >> b1) & 1)) v[s] = make_float4(-v[s].x, -v[s].y, -v[s].z, -v[s].w);
+            } else {
+                const float2 m00 = mats[i][0], m01 = mats[i][1], m10 = mats[i][2], m11 = mats[i][3];
+#pragma unroll
+                for (int s = 0; s < R; ++s)
+                    if (!((s >> b0) & 1)) {
+                        const int t = s | (1 << b0);
+                        if (t < R) {
+                            const float4 x0 = v[s], x1 = v[t];
+                            float2 r0 = make_float2(0.f, 0.f), r1 = r0, r2 = r0, r3 = r0;
+                            cmul_acc(r0, m00, make_float2(x0.x, x0.y)); cmul_acc(r0, m01, make_float2(x1.x, x1.y));
+                            cmul_acc(r1, m10, make_float2(x0.x, x0.y)); cmul_acc(r1, m11, make_float2(x1.x, x1.y));
+                            cmul_acc(r2, m00, make_float2(x0.z, x0.w)); cmul_acc(r2, m01, make_float2(x1.z, x1.w));
+                            cmul_acc(r3, m10, make_float2(x0.z, x0.w)); cmul_acc(r3, m11, make_float2(x1.z, x1.w));
+                            v[s] = make_float4(r0.x, r0.y, r2.x, r2.y);
+                            v[t] = make_float4(r1.x, r1.y, r3.x, r3.y);
+                        }
+                    }
+            }
+        }
+#pragma unroll
+        for (int s = 0; s < R; ++s) *reinterpret_cast<float4*>(a.dst + ((size_t)s << slice_bits) + j) = v[s];
+    }
+}
+
+static int g_sms = 0;
+static int num_sms() {
+    if (g_sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    return g_sms;
+}
+
+}  // namespace large
+}  // namespace qfx
+
+using namespace qfx;
+using namespace qfx::large;
+
+extern "C" int qfx_sv_large_pass(float* states, int n_qubits, int batch, int tile_bits, int low_bits,
+                                 const int* tile_qubits_host, const int* ops_dev, int n_ops, const float* theta,
+                                 int theta_rows, int n_params, const float* angles, int angle_rows, int n_feature,
+                                 const int* shift_param, const float* shift_value, int init_zero_state,
+                                 cudaStream_t stream) {
+    QFX_ARG_CHECK(n_qubits >= 2 && n_qubits <= 34, QFX_ERR_UNSUPPORTED, "n_qubits %d not in 2..34", n_qubits);
+    QFX_ARG_CHECK(tile_bits >= 1 && tile_bits <= MAX_TILE_BITS && tile_bits <= n_qubits, QFX_ERR_BAD_ARG, "bad tile_bits %d", tile_bits);
+    QFX_ARG_CHECK(low_bits >= 0 && low_bits <= tile_bits, QFX_ERR_BAD_ARG, "bad low_bits");
+    QFX_ARG_CHECK(n_ops >= 0 && n_ops <= MAX_OPS_PER_PASS, QFX_ERR_TOO_LARGE, "pass has %d ops (max %d)", n_ops, MAX_OPS_PER_PASS);
+    QFX_ARG_CHECK(batch >= 1 && batch <= 65535, QFX_ERR_BAD_ARG, "bad batch");
+    PassArgs a = {};
+    a.states = reinterpret_cast<float2*>(states);
+    a.n_qubits = n_qubits; a.tile_bits = tile_bits; a.low_bits = low_bits;
+    for (int b = 0; b < tile_bits; ++b) {
+        a.tile_q[b] = tile_qubits_host[b];
+        QFX_ARG_CHECK(b < low_bits ? a.tile_q[b] == b : (a.tile_q[b] > a.tile_q[b - (b > 0)] || b == 0), QFX_ERR_BAD_ARG,
+                      "tile qubits must be ascending and start with 0..low_bits-1");
+    }
+    a.ops = ops_dev; a.n_ops = n_ops; a.theta = theta; a.theta_rows = theta_rows > 0 ? theta_rows : 1; a.n_params = n_params;
+    a.angles = angles; a.angle_rows = angle_rows > 0 ? angle_rows : 1; a.n_feature = n_feature;
+    a.shift_param = shift_param; a.shift_value = shift_value; a.init_zero_state = init_zero_state;
+    const size_t smem = sizeof(float2) << tile_bits;
+    dim3 grid(1u << (n_qubits - tile_bits), batch);
+    sv_large_pass_kernel<<<grid, PASS_THREADS, smem, stream>>>(a);
+    return check_launch("sv_large_pass_kernel");
+}
+
+extern "C" int qfx_sv_large_expz(const float* states, int n_local, int n_total, unsigned int high_bits, int batch,
+                                 float* out, cudaStream_t stream) {
+    QFX_ARG_CHECK(n_local >= 1 && n_total >= n_local && n_total <= 32, QFX_ERR_BAD_ARG, "bad qubit counts");
+    QFX_CUDA_TRY(cudaMemsetAsync(out, 0, sizeof(float) * (size_t)batch * n_total, stream));
+    size_t blocks = (((size_t)1 << n_local) + 256 * 8 - 1) / (256 * 8);
+    const size_t cap = (size_t)num_sms() * 8 / (batch > 8 ? 8 : batch) + 1;
+    if (blocks > cap) blocks = cap;
+    sv_large_expz_kernel<<<dim3((unsigned)blocks, batch), 256, 0, stream>>>(reinterpret_cast<const float2*>(states),
+                                                                          n_local, n_total, high_bits, out);
+    return check_launch("sv_large_expz_kernel");
+}
+
+// src_table: device array of `world` pointers (every rank's source shard, symmetric heap);
+// flags_table: device array of `world` pointers to u32[world] flag arrays (nullable = no barrier,
+// e.g. single-process emulation where the caller orders the launches).
+extern "C" int qfx_sv_global_swap_fused(const float* const* src_table, float* dst, int n_local, int g_bits, int rank,
+                                        int world, const int* ops_dev, int n_ops, const float* theta, int n_params,
+                                        unsigned int* const* flags_table, unsigned int epoch, cudaStream_t stream) {
+    QFX_ARG_CHECK(g_bits >= 1 && g_bits <= 3 && world == (1 << g_bits), QFX_ERR_UNSUPPORTED, "world must be 2, 4 or 8");
+    QFX_ARG_CHECK(n_local - g_bits >= 10, QFX_ERR_BAD_ARG, "shard too small");
+    QFX_ARG_CHECK(n_ops >= 0 && n_ops <= 32, QFX_ERR_TOO_LARGE, "at most 32 fused ops");
+    SwapArgs a = {};
+    a.src = reinterpret_cast<const float2* const*>(src_table); a.dst = reinterpret_cast<float2*>(dst);
+    a.n_local = n_local; a.g_bits = g_bits; a.rank = rank; a.world = world; a.ops = ops_dev; a.n_ops = n_ops;
+    a.theta = theta; a.n_params = n_params; a.flags = flags_table; a.epoch = epoch;
+    const size_t slice = (size_t)1 << (n_local - g_bits);
+    size_t blocks = (slice / 2 + 255) / 256;
+    const size_t cap = (size_t)num_sms() * 4;  // co-resident: every CTA spins on the flags first
+    if (blocks > cap) blocks = cap;
+    if (g_bits == 1) sv_global_swap_fused_kernel<1><<<(unsigned)blocks, 256, 0, stream>>>(a);
+    else if (g_bits == 2) sv_global_swap_fused_kernel<2><<<(unsigned)blocks, 256, 0, stream>>>(a);
+    else sv_global_swap_fused_kernel<3><<<(unsigned)blocks, 256, 0, stream>>>(a);
+    return check_launch("sv_global_swap_fused_kernel");
+}

@@ -47,8 +47,24 @@ struct Step {
     float* g2;                       // [K,32,32,14,14]
     float* da1;                      // [K,32,16,14,14]
     float* conv_part;                // [K,32,NCONV]
+    float* w2f;                      // [K,12800] conv2 weights as [c][tap][o]      (forward operand)
+    float* w2b;                      // [K,12800] conv2 weights as [o][24-tap][c]   (data-gradient operand)
     float* stats;                    // [K,2] running loss sum / correct count of the epoch
 };
+
+// padded 18x18 planes in shared memory from dense 14x14 planes in global memory
+__device__ __forceinline__ void fill_padded_planes(float* __restrict__ xs, const float* __restrict__ src, int planes) {
+    for (int i = threadIdx.x; i < planes * 324; i += blockDim.x) xs[i] = 0.f;
+    __syncthreads();
+    for (int i = threadIdx.x; i < planes * 196; i += blockDim.x) {
+        const int c = i / 196, rem = i - c * 196, r = rem / 14, q = rem - r * 14;
+        xs[c * 324 + (r + 2) * 18 + q + 2] = src[i];
+    }
+}
+__device__ __forceinline__ void copy_f4(float* __restrict__ dst, const float* __restrict__ src, int n) {
+    for (int i = threadIdx.x * 4; i < n; i += blockDim.x * 4)
+        *reinterpret_cast<float4*>(dst + i) = *reinterpret_cast<const float4*>(src + i);
+}
 
 __device__ __forceinline__ int batch_rows(const Step& s, int sel, int* seg_lo) {
     const int client = s.client_ids[sel];
@@ -155,22 +171,20 @@ __device__ __forceinline__ void conv5x5_block(const float* __restrict__ xs /*[CI
 }
 
 constexpr int CONV2_SMEM = (16 * 324 + 16 * 25 * 32) * 4;  // 71,936 B
-__device__ __forceinline__ void conv2_image(const float* __restrict__ a1, const float* __restrict__ prm,
-                                            float* __restrict__ a2, unsigned char* __restrict__ i2, float* smem) {
+// 256 threads: 4 channel groups x 64 lanes (49 active) so that every warp reads ONE weight address
+// (a broadcast) per tap.  w2f is the pre-transposed [c][tap][o] copy kept current by sgd_conv_train.
+__device__ __forceinline__ void conv2_image(const float* __restrict__ a1, const float* __restrict__ w2f,
+                                            const float* __restrict__ bias, float* __restrict__ a2,
+                                            unsigned char* __restrict__ i2, float* smem) {
     float* xs = smem;                 // [16][18][18]
     float* ws = smem + 16 * 324;      // [16][25][32]
     const int tid = threadIdx.x;
-    for (int i = tid; i < 16 * 324; i += blockDim.x) {
-        const int c = i / 324, r = (i % 324) / 18 - 2, q = (i % 18) - 2;
-        xs[i] = (r >= 0 && r < 14 && q >= 0 && q < 14) ? a1[c * 196 + r * 14 + q] : 0.f;
-    }
-    for (int i = tid; i < 12800; i += blockDim.x) {  // global [o][c][tap] -> shared [c][tap][o]
-        const int o = i / 400, rem = i % 400;
-        ws[rem * 32 + o] = prm[C2W + i];
-    }
+    copy_f4(ws, w2f, 12800);
+    fill_padded_planes(xs, a1, 16);
     __syncthreads();
-    if (tid >= 196) return;
-    const int g = tid / 49, pos = tid % 49, py = pos / 7, px = pos % 7;
+    const int g = tid >> 6, pos = tid & 63;
+    if (pos >= 49) return;
+    const int py = pos / 7, px = pos % 7;
     float acc[4][8];
     conv5x5_block<16, 8>(xs, ws, 32, g * 8, py, px, acc);
 #pragma unroll
@@ -178,32 +192,47 @@ __device__ __forceinline__ void conv2_image(const float* __restrict__ a1, const 
         float best = acc[0][o]; int arg = 0;
 #pragma unroll
         for (int j = 1; j < 4; ++j) if (acc[j][o] > best) { best = acc[j][o]; arg = j; }
-        best = fmaxf(best + prm[C2B + g * 8 + o], 0.f);
+        best = fmaxf(best + bias[g * 8 + o], 0.f);
         a2[(g * 8 + o) * 49 + pos] = best;
         i2[(g * 8 + o) * 49 + pos] = (unsigned char)arg;
     }
 }
-__global__ void __launch_bounds__(224) conv2_fwd_train(const Step s) {
+__global__ void __launch_bounds__(256) conv2_fwd_train(const Step s) {
     extern __shared__ __align__(16) float smem[];
     const int sel = blockIdx.y, b = blockIdx.x;
     int lo;
     if (b >= batch_rows(s, sel, &lo)) return;
     const size_t r = (size_t)sel * BS + b;
-    conv2_image(s.a1 + r * 3136, s.params + (size_t)sel * s.nd, s.a2 + r * 1568, s.i2 + r * 1568, smem);
+    conv2_image(s.a1 + r * 3136, s.w2f + (size_t)sel * 12800, s.params + (size_t)sel * s.nd + C2B, s.a2 + r * 1568,
+                s.i2 + r * 1568, smem);
 }
-__global__ void __launch_bounds__(224) conv2_fwd_eval(const float* __restrict__ a1, const float* __restrict__ prm,
-                                                      float* a2, unsigned char* i2) {
+__global__ void __launch_bounds__(256) conv2_fwd_eval(const float* __restrict__ a1, const float* __restrict__ w2f,
+                                                      const float* __restrict__ prm, float* a2, unsigned char* i2) {
     extern __shared__ __align__(16) float smem[];
     const size_t r = blockIdx.x;
-    conv2_image(a1 + r * 3136, prm, a2 + r * 1568, i2 + r * 1568, smem);
+    conv2_image(a1 + r * 3136, w2f, prm + C2B, a2 + r * 1568, i2 + r * 1568, smem);
+}
+
+// [o][c][tap] -> forward copy [c][tap][o] and data-gradient copy [o][24-tap][c]
+__device__ __forceinline__ void transpose_conv2_weight(const float* __restrict__ w, float* __restrict__ w2f,
+                                                       float* __restrict__ w2b, int i) {
+    const int o = i / 400, rem = i - o * 400, c = rem / 25, tap = rem - c * 25;
+    const float v = w[i];
+    w2f[rem * 32 + o] = v;
+    w2b[(o * 25 + (24 - tap)) * 16 + c] = v;
+}
+__global__ void __launch_bounds__(256) conv2_weight_prep(const float* __restrict__ params, int nd, float* w2f, float* w2b) {
+    const int sel = blockIdx.y, i = blockIdx.x * 256 + threadIdx.x;
+    if (i < 12800) transpose_conv2_weight(params + (size_t)sel * nd + C2W, w2f + (size_t)sel * 12800,
+                                          w2b + (size_t)sel * 12800, i);
 }
 
 // ------------------------------------------------------------------------------------------
 // fc1 forward, split-K: CTA (slice, client) computes the partial [32 x 64] product over 98 inputs.
 // 128 threads, each a 4x4 (rows x features) register tile.
 __global__ void __launch_bounds__(128) fc1_fwd_train(const Step s) {
-    __shared__ __align__(16) float xs[FC1_KS][BS];       // [k][b]
-    __shared__ __align__(16) float wsm[FC1_KS][64];      // [k][f]
+    __shared__ float xs[BS][FC1_KS + 1];       // [b][k], coalesced fill, conflict-free column reads
+    __shared__ float wsm[64][FC1_KS + 1];      // [f][k]
     const int sel = blockIdx.y, sl = blockIdx.x, tid = threadIdx.x;
     int lo;
     const int nb = batch_rows(s, sel, &lo);
@@ -211,21 +240,21 @@ __global__ void __launch_bounds__(128) fc1_fwd_train(const Step s) {
     const float* x = s.a2 + (size_t)sel * BS * 1568 + sl * FC1_KS;
     const float* w = s.params + (size_t)sel * s.nd + F1W + sl * FC1_KS;
     for (int i = tid; i < BS * FC1_KS; i += 128) {
-        const int b = i / FC1_KS, k = i % FC1_KS;
-        xs[k][b] = b < nb ? x[(size_t)b * 1568 + k] : 0.f;
+        const int b = i / FC1_KS, k = i - b * FC1_KS;
+        xs[b][k] = b < nb ? x[(size_t)b * 1568 + k] : 0.f;
     }
     for (int i = tid; i < 64 * FC1_KS; i += 128) {
-        const int f = i / FC1_KS, k = i % FC1_KS;
-        wsm[k][f] = w[(size_t)f * 1568 + k];
+        const int f = i / FC1_KS, k = i - f * FC1_KS;
+        wsm[f][k] = w[(size_t)f * 1568 + k];
     }
     __syncthreads();
     const int bt = (tid >> 4) * 4, ft = (tid & 15) * 4;
     float acc[4][4] = {};
 #pragma unroll 2
     for (int k = 0; k < FC1_KS; ++k) {
-        const float4 xv = *reinterpret_cast<const float4*>(&xs[k][bt]);
-        const float4 wv = *reinterpret_cast<const float4*>(&wsm[k][ft]);
-        const float xa[4] = {xv.x, xv.y, xv.z, xv.w}, wa[4] = {wv.x, wv.y, wv.z, wv.w};
+        float xa[4], wa[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { xa[i] = xs[bt + i][k]; wa[i] = wsm[ft + i][k]; }
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -410,27 +439,20 @@ __global__ void __launch_bounds__(256) fc1_bwd_train(const Step s) {
 // ------------------------------------------------------------------------------------------
 // conv2 data gradient: da1[c][y][x] = sum_o sum_taps g2pad[o][y+ky][x+kx] W[o][c][4-ky][4-kx].
 constexpr int DGRAD_SMEM = (32 * 324 + 32 * 25 * 16) * 4;  // 92,672 B
-__global__ void __launch_bounds__(224) conv2_dgrad_train(const Step s) {
+__global__ void __launch_bounds__(256) conv2_dgrad_train(const Step s) {
     extern __shared__ __align__(16) float smem[];
     float* xs = smem;                // [32][18][18]
-    float* ws = smem + 32 * 324;     // [32 o][25 taps][16 c], taps already flipped
+    float* ws = smem + 32 * 324;     // [32 o][25 taps][16 c], taps already flipped (w2b)
     const int sel = blockIdx.y, b = blockIdx.x, tid = threadIdx.x;
     int lo;
     if (b >= batch_rows(s, sel, &lo)) return;
     const size_t row = (size_t)sel * BS + b;
-    const float* g2 = s.g2 + row * 32 * 196;
-    const float* prm = s.params + (size_t)sel * s.nd;
-    for (int i = tid; i < 32 * 324; i += blockDim.x) {
-        const int c = i / 324, r = (i % 324) / 18 - 2, q = (i % 18) - 2;
-        xs[i] = (r >= 0 && r < 14 && q >= 0 && q < 14) ? g2[c * 196 + r * 14 + q] : 0.f;
-    }
-    for (int i = tid; i < 12800; i += blockDim.x) {  // global [o][c][tap] -> shared [o][24-tap][c]
-        const int o = i / 400, c = (i % 400) / 25, tap = i % 25;
-        ws[(o * 25 + (24 - tap)) * 16 + c] = prm[C2W + i];
-    }
+    copy_f4(ws, s.w2b + (size_t)sel * 12800, 12800);
+    fill_padded_planes(xs, s.g2 + row * 32 * 196, 32);
     __syncthreads();
-    if (tid >= 196) return;
-    const int g = tid / 49, pos = tid % 49, py = pos / 7, px = pos % 7;
+    const int g = tid >> 6, pos = tid & 63;
+    if (pos >= 49) return;
+    const int py = pos / 7, px = pos % 7;
     float acc[4][4];
     conv5x5_block<32, 4>(xs, ws, 16, g * 4, py, px, acc);
     float* out = s.da1 + row * 3136;
@@ -447,7 +469,7 @@ __global__ void __launch_bounds__(224) conv2_dgrad_train(const Step s) {
 constexpr int WGRAD_SMEM = (196 * 32 + 16 * 324) * 4;  // 45,824 B
 __global__ void __launch_bounds__(320) conv2_wgrad_train(const Step s) {
     extern __shared__ __align__(16) float smem[];
-    float* gs = smem;               // [y][x][o] 196*32
+    float* gs = smem;               // [o][y][x] 32*196 (planar, straight copy)
     float* xs = smem + 196 * 32;    // [16][18][18]
     const int sel = blockIdx.y, b = blockIdx.x, tid = threadIdx.x;
     int lo;
@@ -458,13 +480,8 @@ __global__ void __launch_bounds__(320) conv2_wgrad_train(const Step s) {
         return;
     }
     const size_t row = (size_t)sel * BS + b;
-    const float* g2 = s.g2 + row * 32 * 196;
-    const float* a1 = s.a1 + row * 3136;
-    for (int i = tid; i < 32 * 196; i += 320) gs[(i % 196) * 32 + i / 196] = g2[i];
-    for (int i = tid; i < 16 * 324; i += 320) {
-        const int c = i / 324, r = (i % 324) / 18 - 2, q = (i % 18) - 2;
-        xs[i] = (r >= 0 && r < 14 && q >= 0 && q < 14) ? a1[c * 196 + r * 14 + q] : 0.f;
-    }
+    copy_f4(gs, s.g2 + row * 32 * 196, 32 * 196);
+    fill_padded_planes(xs, s.a1 + row * 3136, 16);
     __syncthreads();
     const int ky = tid % 5, c = (tid / 5) % 16, og = tid / 80;  // og in 0..3
     float acc[8][5] = {};
@@ -475,9 +492,9 @@ __global__ void __launch_bounds__(320) conv2_wgrad_train(const Step s) {
         for (int q = 0; q < 18; ++q) xr[q] = xp[q];
 #pragma unroll
         for (int x = 0; x < 14; ++x) {
-            const float4 g0 = *reinterpret_cast<const float4*>(gs + (y * 14 + x) * 32 + og * 8);
-            const float4 g1 = *reinterpret_cast<const float4*>(gs + (y * 14 + x) * 32 + og * 8 + 4);
-            const float gv[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+            float gv[8];  // same address for every lane of a warp: broadcast reads
+#pragma unroll
+            for (int o = 0; o < 8; ++o) gv[o] = gs[(og * 8 + o) * 196 + y * 14 + x];
 #pragma unroll
             for (int o = 0; o < 8; ++o)
 #pragma unroll
@@ -491,7 +508,7 @@ __global__ void __launch_bounds__(320) conv2_wgrad_train(const Step s) {
     // conv2 bias gradient: sum of g2 over positions, one thread per output channel
     if (tid < 32) {
         float sum = 0.f;
-        for (int i = 0; i < 196; ++i) sum += gs[i * 32 + tid];
+        for (int i = 0; i < 196; ++i) sum += gs[tid * 196 + i];
         part[C2B + tid] = sum;
     }
 }
@@ -500,8 +517,9 @@ __global__ void __launch_bounds__(320) conv2_wgrad_train(const Step s) {
 // conv1 weight gradient for one image.  The gradient reaching conv1's output is sparse (one
 // position per pooled window, and only where the pooled activation is positive), so the sum runs
 // over the 16x196 pooled elements: thread (o, tap) adds da1 * x[argmax position + tap].
+constexpr int XS1 = 37;  // row stride: bank = 5*ky + kx is distinct for the 25 taps of a warp
 __global__ void __launch_bounds__(416) conv1_wgrad_train(const Step s) {
-    __shared__ float xs[32 * 32];
+    __shared__ float xs[32 * XS1];
     __shared__ float gsm[16 * 196];
     __shared__ unsigned char ism[16 * 196];
     const int sel = blockIdx.y, b = blockIdx.x, tid = threadIdx.x;
@@ -512,7 +530,7 @@ __global__ void __launch_bounds__(416) conv1_wgrad_train(const Step s) {
     const float* img = s.X + (size_t)sample_index(s, lo, b) * 784;
     for (int i = tid; i < 1024; i += 416) {
         const int y = (i >> 5) - 2, x = (i & 31) - 2;
-        xs[i] = (y >= 0 && y < 28 && x >= 0 && x < 28) ? img[y * 28 + x] : 0.f;
+        xs[(i >> 5) * XS1 + (i & 31)] = (y >= 0 && y < 28 && x >= 0 && x < 28) ? img[y * 28 + x] : 0.f;
     }
     for (int i = tid; i < 3136; i += 416) {
         gsm[i] = s.a1[row * 3136 + i] > 0.f ? s.da1[row * 3136 + i] : 0.f;
@@ -526,7 +544,7 @@ __global__ void __launch_bounds__(416) conv1_wgrad_train(const Step s) {
         for (int p = 0; p < 196; ++p) {
             const int arg = ism[o * 196 + p];
             const int y = 2 * (p / 14) + (arg >> 1), x = 2 * (p % 14) + (arg & 1);
-            acc += gsm[o * 196 + p] * xs[(y + ky) * 32 + x + kx];
+            acc += gsm[o * 196 + p] * xs[(y + ky) * XS1 + x + kx];
         }
         part[C1W + tid] = acc;
     } else {
@@ -550,7 +568,13 @@ __global__ void __launch_bounds__(256) sgd_conv_train(const Step s) {
     float* mom = s.moment + (size_t)sel * s.nd;
     const float m = s.momentum * mom[p] + g;
     mom[p] = m;
-    prm[p] -= s.lr * m;
+    const float w = prm[p] - s.lr * m;
+    prm[p] = w;
+    if (p >= C2W && p < C2B) {  // keep the operand copies of the conv2 weights current
+        const int i = p - C2W, o = i / 400, rem = i - o * 400, c = rem / 25, tap = rem - c * 25;
+        s.w2f[(size_t)sel * 12800 + rem * 32 + o] = w;
+        s.w2b[(size_t)sel * 12800 + (o * 25 + (24 - tap)) * 16 + c] = w;
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -627,14 +651,38 @@ extern "C" int qfx_tinycnn_workspace_bytes(int n_selected, size_t* bytes) {
     auto add = [&](size_t n) { tot += (n + 255) & ~(size_t)255; };
     add(K * BS * 3136 * 4); add(K * BS * 3136); add(K * BS * 1568 * 4); add(K * BS * 1568);
     add(K * FC1_SLICES * BS * 64 * 4); add(K * BS * 64 * 4); add(K * BS * 64 * 4);
-    add(K * BS * 32 * 196 * 4); add(K * BS * 3136 * 4); add(K * BS * NCONV * 4); add(K * 2 * 4);
+    add(K * BS * 32 * 196 * 4); add(K * BS * 3136 * 4); add(K * BS * NCONV * 4); add(K * 12800 * 4); add(K * 12800 * 4);
+    add(K * 2 * 4);
     *bytes = tot;
     return 0;
 }
 
+static void carve(Step& s, void* workspace, size_t K) {
+    char* w = (char*)workspace;
+    auto take = [&](size_t n) { char* p = w; w += (n + 255) & ~(size_t)255; return p; };
+    s.a1 = (float*)take(K * BS * 3136 * 4); s.i1 = (unsigned char*)take(K * BS * 3136);
+    s.a2 = (float*)take(K * BS * 1568 * 4); s.i2 = (unsigned char*)take(K * BS * 1568);
+    s.fc1_part = (float*)take(K * FC1_SLICES * BS * 64 * 4);
+    s.h1 = (float*)take(K * BS * 64 * 4); s.dh1 = (float*)take(K * BS * 64 * 4);
+    s.g2 = (float*)take(K * BS * 32 * 196 * 4); s.da1 = (float*)take(K * BS * 3136 * 4);
+    s.conv_part = (float*)take(K * BS * NCONV * 4);
+    s.w2f = (float*)take(K * 12800 * 4); s.w2b = (float*)take(K * 12800 * 4); s.stats = (float*)take(K * 2 * 4);
+}
+
+// Call once per round after the global parameters were broadcast into `params`: builds the
+// operand-layout copies of the conv2 weights that the step kernels keep current afterwards.
+extern "C" int qfx_tinycnn_begin_round(const float* params, int nd, int n_selected, void* workspace,
+                                       cudaStream_t stream) {
+    QFX_ARG_CHECK(n_selected >= 1 && params && workspace, QFX_ERR_BAD_ARG, "bad arguments");
+    Step s;
+    carve(s, workspace, (size_t)n_selected);
+    conv2_weight_prep<<<dim3(50, n_selected), 256, 0, stream>>>(params, nd, s.w2f, s.w2b);
+    return check_launch("conv2_weight_prep");
+}
+
 // One SGD step for every selected client: 9 kernels on `stream` (capture them in a CUDA graph).
 // `workspace` comes from qfx_tinycnn_workspace_bytes; stats (last 2K floats of it) accumulate the
-// epoch's loss sum and correct count - zero them with qfx_tinycnn_reset_stats.
+// epoch's loss sum and correct count - the caller zeroes them per epoch.
 extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const int* offsets, const int* perm,
                                       int n_total, const int* client_ids, int n_selected, int epoch,
                                       int batch_index, int batch_size, float* params, float* moment, int nd,
@@ -646,27 +694,19 @@ extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const i
     QFX_ARG_CHECK(nd >= F2W + 65 * n_classes, QFX_ERR_BAD_ARG, "parameter row stride too small");
     QFX_ARG_CHECK(n_selected >= 1 && p_drop >= 0.f && p_drop < 1.f, QFX_ERR_BAD_ARG, "bad n_selected / p_drop");
     if (int e = set_attrs()) return e;
-    const size_t K = (size_t)n_selected;
     Step s;
     s.X = X; s.labels = labels; s.offsets = offsets; s.perm = perm; s.client_ids = client_ids;
     s.n_total = n_total; s.epoch = epoch; s.batch_index = batch_index; s.batch_size = batch_size;
     s.params = params; s.moment = moment; s.nd = nd; s.n_classes = n_classes;
     s.lr = lr; s.momentum = momentum; s.p_drop = p_drop; s.seed = seed; s.round = round;
-    char* w = (char*)workspace;
-    auto take = [&](size_t n) { char* p = w; w += (n + 255) & ~(size_t)255; return p; };
-    s.a1 = (float*)take(K * BS * 3136 * 4); s.i1 = (unsigned char*)take(K * BS * 3136);
-    s.a2 = (float*)take(K * BS * 1568 * 4); s.i2 = (unsigned char*)take(K * BS * 1568);
-    s.fc1_part = (float*)take(K * FC1_SLICES * BS * 64 * 4);
-    s.h1 = (float*)take(K * BS * 64 * 4); s.dh1 = (float*)take(K * BS * 64 * 4);
-    s.g2 = (float*)take(K * BS * 32 * 196 * 4); s.da1 = (float*)take(K * BS * 3136 * 4);
-    s.conv_part = (float*)take(K * BS * NCONV * 4); s.stats = (float*)take(K * 2 * 4);
+    carve(s, workspace, (size_t)n_selected);
     const dim3 gimg(batch_size, n_selected);
     conv1_fwd_train<<<gimg, 224, 0, stream>>>(s);
-    conv2_fwd_train<<<gimg, 224, CONV2_SMEM, stream>>>(s);
+    conv2_fwd_train<<<gimg, 256, CONV2_SMEM, stream>>>(s);
     fc1_fwd_train<<<dim3(FC1_SLICES, n_selected), 128, 0, stream>>>(s);
     head_train<<<n_selected, 256, 0, stream>>>(s);
     fc1_bwd_train<<<dim3(49, n_selected), 256, 0, stream>>>(s);
-    conv2_dgrad_train<<<gimg, 224, DGRAD_SMEM, stream>>>(s);
+    conv2_dgrad_train<<<gimg, 256, DGRAD_SMEM, stream>>>(s);
     conv2_wgrad_train<<<dim3(BS, n_selected), 320, WGRAD_SMEM, stream>>>(s);
     conv1_wgrad_train<<<gimg, 416, 0, stream>>>(s);
     sgd_conv_train<<<dim3((NCONV + 255) / 256, n_selected), 256, 0, stream>>>(s);
@@ -681,19 +721,22 @@ extern "C" int qfx_tinycnn_stats_offset(int n_selected, size_t* offset) {
 }
 
 // Evaluation: forward over N images with one parameter vector; out2 = (loss sum, #correct).
-// scratch: N*(3136*4 + 3136 + 1568*4 + 1568) bytes.
+// scratch: n * 23,520 + 102,400 bytes.
 extern "C" int qfx_tinycnn_eval(const float* X, const int* labels, int n, const float* params, int n_classes,
                                 void* scratch, float* out2, cudaStream_t stream) {
     QFX_ARG_CHECK(n >= 1 && n_classes >= 2 && n_classes <= MAX_CLASSES, QFX_ERR_BAD_ARG, "bad n / n_classes");
     if (int e = set_attrs()) return e;
     char* w = (char*)scratch;
+    float* w2f = (float*)w; w += 12800 * 4;
+    float* w2b = (float*)w; w += 12800 * 4;
     float* a1 = (float*)w; w += (size_t)n * 3136 * 4;
     float* a2 = (float*)w; w += (size_t)n * 1568 * 4;
     unsigned char* i1 = (unsigned char*)w; w += (size_t)n * 3136;
     unsigned char* i2 = (unsigned char*)w;
     QFX_CUDA_TRY(cudaMemsetAsync(out2, 0, 2 * sizeof(float), stream));
+    conv2_weight_prep<<<dim3(50, 1), 256, 0, stream>>>(params, 0, w2f, w2b);
     conv1_fwd_eval<<<n, 224, 0, stream>>>(X, params, a1, i1);
-    conv2_fwd_eval<<<n, 224, CONV2_SMEM, stream>>>(a1, params, a2, i2);
+    conv2_fwd_eval<<<n, 256, CONV2_SMEM, stream>>>(a1, w2f, params, a2, i2);
     head_eval<<<(n + EVB - 1) / EVB, 256, 0, stream>>>(a2, labels, params, n_classes, n, out2);
     return check_launch("tinycnn_eval");
 }

@@ -92,6 +92,8 @@ class TinyCNNBatchedTrainer:
         K = st["K"]
         st["params"][:, : self.dim] = st["global"][None, :]
         st["moment"].zero_()
+        _lib.call("qfx_tinycnn_begin_round", _lib.ptr(st["params"]), _lib.c_int(self.nd), _lib.c_int(K),
+                  _lib.ptr(st["ws"]), _lib.stream_ptr())
         n_batches = st["n_batches"]
         perm_ptr = _lib.ptr(self._perm) if self._perm is not None else _lib.ptr(None)
         for e in range(self.epochs):
@@ -140,7 +142,7 @@ class TinyCNNBatchedTrainer:
 
     def evaluate(self, global_flat: torch.Tensor, X: torch.Tensor, y: torch.Tensor, batch_size: int = 0):
         n = X.shape[0]
-        need = n * 23520
+        need = n * 23520 + 102400
         if self._eval_scratch is None or self._eval_scratch.numel() < need:
             self._eval_scratch = torch.empty(need, dtype=torch.uint8, device=X.device)
         out2 = torch.empty(2, device=X.device)
@@ -148,7 +150,7 @@ class TinyCNNBatchedTrainer:
         prm[: self.dim] = global_flat[: self.dim]
         _lib.call("qfx_tinycnn_eval", _lib.ptr(X.contiguous().float()), _lib.ptr(y.to(torch.int32).contiguous()),
                   _lib.c_int(n), _lib.ptr(prm), _lib.c_int(self.n_classes), _lib.ptr(self._eval_scratch),
-                  _lib.ptr(out2), _lib.stream_ptr(), launches=3)
+                  _lib.ptr(out2), _lib.stream_ptr(), launches=4)
         res = out2.cpu()
         return float(res[0]) / n, float(res[1]) / n
 
