@@ -23,6 +23,15 @@ extern "C" {
 #define QFX_ERR_UNSUPPORTED (-2)
 #define QFX_ERR_TOO_LARGE (-3)
 
+/* gate kinds of the large-state engine (K5/K6) */
+#define QFX_GATE_RX 0
+#define QFX_GATE_RY 1
+#define QFX_GATE_RZ 2
+#define QFX_GATE_CNOT 3
+#define QFX_GATE_CZ 4
+#define QFX_GATE_RXRZ 5        /* RZ(p1) * RX(p0), produced by the compiler's fusion */
+#define QFX_GATE_RY_FEATURE 6  /* RY(angles[sample][p0]): the feature map */
+
 /* basis: 0 rx, 1 ry, 2 rz (feature-map rotation, /root/reference/src/QFed/qAngle.py:43-50)
  * entangler: 0 CNOT ring, 1 CZ ring, 2 none (/root/reference/ROADMAP.md:127) */
 
@@ -144,6 +153,35 @@ int qfx_unitary_split_states(const float* states, int n_qubits, int batch, int b
                              float* b_lo, cudaStream_t stream);
 int qfx_unitary_gemm(const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, int n_qubits,
                      int batch_padded, int precision, float* out_states, float* expvals, cudaStream_t stream);
+
+/* K5/K6 large-state engine (no reference counterpart: BASELINE.json configs 4 and 5; the reference's
+ * only simulator call is a 4-qubit Statevector, /root/reference/src/QFed/qAmplitude.py:44-46).
+ *
+ * qfx_circuit_compile (HOST arrays): schedule a gate list (n_gates x {kind, q0, q1, param}) into passes
+ *   that each touch <= tile_bits qubits including qubits 0..low_bits-1; returns the pass count.
+ * qfx_sv_large_pass: run one pass on `batch` states [batch][2^n] complex64; tile_qubits_host is a HOST
+ *   array, ops_dev a DEVICE array of n_ops x 5 ints from the compiler; theta [theta_rows][n_params],
+ *   angles [angle_rows][n_feature] (row = batch index modulo rows); shift_param/shift_value [batch]
+ *   add a per-state shift to one parameter (parameter-shift rule, /root/reference/ROADMAP.md:130-135).
+ * qfx_sv_large_expz: <Z_q> for all n_total qubits -> out [batch][n_total]; qubits >= n_local are
+ *   read from high_bits (the shard's rank).
+ * qfx_sv_global_swap_fused: sharded state, world = 2^g_bits ranks: exchange the g global qubits with
+ *   the top g local qubits by pulling slices from every peer's shard (src_table: device array of
+ *   world peer pointers) and apply n_ops <= 32 gates on the swapped-in qubits (local bits 0..g-1 of the
+ *   slice index) in registers before storing to dst.  flags_table (nullable) gives the in-kernel
+ *   cross-GPU barrier; epoch must increase per call. */
+int qfx_circuit_compile(int n_qubits, int n_gates, const int* gates_in, int tile_bits, int low_bits, int max_passes,
+                        int max_ops, int* pass_tile_qubits, int* pass_op_begin, int* ops_out);
+int qfx_sv_large_pass(float* states, int n_qubits, int batch, int tile_bits, int low_bits,
+                      const int* tile_qubits_host, const int* ops_dev, int n_ops, const float* theta, int theta_rows,
+                      int n_params, const float* angles, int angle_rows, int n_feature, const int* shift_param,
+                      const float* shift_value, int init_zero_state, cudaStream_t stream);
+int qfx_sv_large_expz(const float* states, int n_local, int n_total, unsigned int high_bits, int batch, float* out,
+                      cudaStream_t stream);
+int qfx_sv_global_swap_fused(const float* const* src_table, float* dst, int n_local, int g_bits, int rank, int world,
+                             const int* ops_dev, int n_ops, const float* theta, int n_params, const float* angles,
+                             int n_feature, unsigned int* const* flags_table, unsigned int epoch,
+                             cudaStream_t stream);
 
 #ifdef __cplusplus
 }

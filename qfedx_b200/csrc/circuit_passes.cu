@@ -64,23 +64,29 @@ extern "C" int qfx_circuit_compile(int n_qubits, int n_gates, const int* gates_i
     pass_op_begin[0] = 0;
     while (n_done < G) {
         QFX_ARG_CHECK(n_pass < max_passes, QFX_ERR_TOO_LARGE, "more than %d passes", max_passes);
-        std::vector<char> in_tile(n_qubits, 0), blocked(n_qubits, 0);
-        int used = 0;
-        for (int q = 0; q < low_bits; ++q) { in_tile[q] = 1; ++used; }
+        std::vector<char> in_tile, blocked;
         std::vector<int> chosen;
-        for (int i = 0; i < G; ++i) {
-            if (done[i]) continue;
-            const Gate& g = gates[i];
-            const bool two = g.kind == QFX_GATE_CNOT || g.kind == QFX_GATE_CZ;
-            const int need = (in_tile[g.q0] ? 0 : 1) + ((two && !in_tile[g.q1]) ? 1 : 0);
-            const bool free_qubits = !blocked[g.q0] && !(two && blocked[g.q1]);
-            if (free_qubits && used + need <= tile_bits) {
-                if (!in_tile[g.q0]) { in_tile[g.q0] = 1; ++used; }
-                if (two && !in_tile[g.q1]) { in_tile[g.q1] = 1; ++used; }
-                chosen.push_back(i);
-            } else {
-                blocked[g.q0] = 1;
-                if (two) blocked[g.q1] = 1;
+        int used = 0;
+        // reserve the low qubits for coalescing; if nothing fits next to them, give some of them up
+        for (int lb = low_bits; lb >= 0 && chosen.empty(); --lb) {
+            in_tile.assign(n_qubits, 0);
+            blocked.assign(n_qubits, 0);
+            used = 0;
+            for (int q = 0; q < lb; ++q) { in_tile[q] = 1; ++used; }
+            for (int i = 0; i < G; ++i) {
+                if (done[i]) continue;
+                const Gate& g = gates[i];
+                const bool two = g.kind == QFX_GATE_CNOT || g.kind == QFX_GATE_CZ;
+                const int need = (in_tile[g.q0] ? 0 : 1) + ((two && !in_tile[g.q1]) ? 1 : 0);
+                const bool free_qubits = !blocked[g.q0] && !(two && blocked[g.q1]);
+                if (free_qubits && used + need <= tile_bits) {
+                    if (!in_tile[g.q0]) { in_tile[g.q0] = 1; ++used; }
+                    if (two && !in_tile[g.q1]) { in_tile[g.q1] = 1; ++used; }
+                    chosen.push_back(i);
+                } else {
+                    blocked[g.q0] = 1;
+                    if (two) blocked[g.q1] = 1;
+                }
             }
         }
         QFX_ARG_CHECK(!chosen.empty(), QFX_ERR_BAD_ARG, "scheduler made no progress (tile too small?)");

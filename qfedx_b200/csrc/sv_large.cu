@@ -207,6 +207,7 @@ struct SwapArgs {
     const int* ops;            // fused gates on the swapped-in qubits: local bit = 0..g-1 (slice index bits)
     int n_ops;
     const float* theta; int n_params;
+    const float* angles; int n_feature;   // feature-map angles of the (single) sample
     unsigned int* const* flags;  // [world] peer pointers to flag arrays [world]
     unsigned int epoch;
     unsigned int* counter;       // local u32 scratch for the grid-wide arrival count (zero before launch)
@@ -241,6 +242,7 @@ sv_global_swap_fused_kernel(const SwapArgs a) {
         sops[i][0] = op[0]; sops[i][1] = op[1]; sops[i][2] = op[2];
         PassArgs pa = {};
         pa.theta = a.theta; pa.theta_rows = 1; pa.n_params = a.n_params;
+        pa.angles = a.angles; pa.angle_rows = 1; pa.n_feature = a.n_feature;
         op_matrix(pa, op, 0, mats[i]);
     }
     __syncthreads();
@@ -350,14 +352,16 @@ extern "C" int qfx_sv_large_expz(const float* states, int n_local, int n_total, 
 // e.g. single-process emulation where the caller orders the launches).
 extern "C" int qfx_sv_global_swap_fused(const float* const* src_table, float* dst, int n_local, int g_bits, int rank,
                                         int world, const int* ops_dev, int n_ops, const float* theta, int n_params,
-                                        unsigned int* const* flags_table, unsigned int epoch, cudaStream_t stream) {
+                                        const float* angles, int n_feature, unsigned int* const* flags_table,
+                                        unsigned int epoch, cudaStream_t stream) {
     QFX_ARG_CHECK(g_bits >= 1 && g_bits <= 3 && world == (1 << g_bits), QFX_ERR_UNSUPPORTED, "world must be 2, 4 or 8");
-    QFX_ARG_CHECK(n_local - g_bits >= 10, QFX_ERR_BAD_ARG, "shard too small");
+    QFX_ARG_CHECK(n_local - g_bits >= 1, QFX_ERR_BAD_ARG, "shard too small: a slice must hold at least two amplitudes");
     QFX_ARG_CHECK(n_ops >= 0 && n_ops <= 32, QFX_ERR_TOO_LARGE, "at most 32 fused ops");
     SwapArgs a = {};
     a.src = reinterpret_cast<const float2* const*>(src_table); a.dst = reinterpret_cast<float2*>(dst);
     a.n_local = n_local; a.g_bits = g_bits; a.rank = rank; a.world = world; a.ops = ops_dev; a.n_ops = n_ops;
-    a.theta = theta; a.n_params = n_params; a.flags = flags_table; a.epoch = epoch;
+    a.theta = theta; a.n_params = n_params; a.angles = angles; a.n_feature = n_feature;
+    a.flags = flags_table; a.epoch = epoch;
     const size_t slice = (size_t)1 << (n_local - g_bits);
     size_t blocks = (slice / 2 + 255) / 256;
     const size_t cap = (size_t)num_sms() * 4;  // co-resident: every CTA spins on the flags first

@@ -1,0 +1,62 @@
+"""Pass compiler (host C++) - runs without a GPU."""
+import numpy as np
+import pytest
+
+from qfedx_b200.ops import _lib
+
+pytestmark = pytest.mark.skipif(not _lib.available(), reason="CUDA library not built")
+
+
+def _check_schedule(n, gates, passes, tile_bits, low_bits):
+    from qfedx_b200.ops.large import GATE, TWO_QUBIT
+    # every pass: ascending tile qubits, starts with the low qubits, ops only use tile bits
+    seen = []
+    for p in passes:
+        tq = p.tile_qubits.tolist()
+        assert tq == sorted(tq) and len(set(tq)) == len(tq) == min(tile_bits, n)
+        for kind, b0, b1, p0, p1 in p.ops.tolist():
+            assert 0 <= b0 < len(tq)
+            q0 = tq[b0]
+            q1 = tq[b1] if kind in TWO_QUBIT else -1
+            seen.append((kind, q0, q1, p0, p1))
+    # per-qubit order of the original program is preserved (after RX+RZ fusion)
+    def per_qubit(seq):
+        out = {}
+        for kind, q0, q1, p0, p1 in seq:
+            params = [p for p in (p0, p1) if p >= 0] or [-1]
+            for q in (q0, q1):
+                if q >= 0:
+                    out.setdefault(q, []).extend((kind if kind != GATE["rxrz"] else "f", p) for p in params)
+        return out
+    orig = []
+    for kind, q0, q1, p in gates:
+        orig.append((kind, q0, q1, p, -1))
+    a, b = per_qubit(orig), per_qubit(seen)
+    for q in a:
+        pa = [p for _, p in a[q]]
+        pb = [p for _, p in b[q]]
+        assert pa == pb, (q, pa, pb)
+
+
+def test_ring_ansatz_20q_two_passes_per_layer():
+    from qfedx_b200.ops.large import ansatz_gates, compile_passes
+    gates = ansatz_gates(20, 3)
+    passes = compile_passes(20, gates, 12, 3)
+    _check_schedule(20, gates, passes, 12, 3)
+    assert len(passes) <= 2 * 3 + 2
+    n_ops = sum(len(p.ops) for p in passes)
+    assert n_ops == 20 + 3 * (20 + 20)        # feature + per layer (20 fused RX.RZ + 20 CNOT)
+
+
+@pytest.mark.parametrize("n,L,tile,low", [(5, 2, 4, 2), (5, 2, 4, 3), (13, 2, 12, 3), (16, 1, 10, 3), (3, 1, 12, 3)])
+def test_schedules_are_valid(n, L, tile, low):
+    from qfedx_b200.ops.large import ansatz_gates, compile_passes
+    gates = ansatz_gates(n, L, "cz")
+    passes = compile_passes(n, gates, tile, low)
+    _check_schedule(n, gates, passes, min(tile, n), min(low, n))
+
+
+def test_bad_gate_is_rejected():
+    from qfedx_b200.ops.large import compile_passes
+    with pytest.raises(_lib.QfxError):
+        compile_passes(4, [(0, 7, -1, 0)], 4, 2)
