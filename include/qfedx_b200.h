@@ -94,6 +94,21 @@ int qfx_fedavg_fused(const float* client_params, const float* global_in, float* 
                      int n_wrap, float clip, float sigma, float server_lr, unsigned long long seed, int round,
                      int secagg, float* norms_out, long long* masked_out, float* scratch, cudaStream_t stream);
 
+/* Allocation-free variant of qfx_fedavg_fused.  It has no counterpart in the reference; it exists for
+ * callers that cannot provide (or allocate) the workspace: C/C++ servers using this ABI without a
+ * tensor library's allocator, processes whose device memory is owned by another framework's arena,
+ * and latency-critical loops where a cudaMalloc/cudaFree would synchronise the device.  Arguments are
+ * those of qfx_fedavg_fused without `scratch`; the norm accumulators live in a static device array of
+ * QFX_FEDAVG_STATIC_MAX_CLIENTS floats (16 KiB held on every GPU that loads the library).  More clients
+ * than that -> QFX_ERR_TOO_LARGE.  The first call on a device resolves the array's address: make it at
+ * start-up, before any stream capture.  Calls share the array: consecutive calls on one stream are
+ * safe (the used part is cleared first), calls that overlap on one GPU race. */
+#define QFX_FEDAVG_STATIC_MAX_CLIENTS 4096
+int qfx_fedavg_fused_static(const float* client_params, const float* global_in, float* global_out,
+                            const float* weights, const int* participate, int n_clients, int dim, int mode,
+                            int n_wrap, float clip, float sigma, float server_lr, unsigned long long seed,
+                            int round, int secagg, float* norms_out, long long* masked_out, cudaStream_t stream);
+
 /* K7 across GPUs: this rank's k_local clients (global ids client_gids) are reduced locally,
  * the partial sum is pushed into slot [rank] of every rank's receive buffer with peer stores over
  * NVLink, flags are released/acquired at system scope, and every rank applies the same update.

@@ -258,3 +258,75 @@ extern "C" int qfx_fedavg_fused_multi(const float* client_params, const float* g
     a.rank = rank; a.world = world; a.recv_slots = recv_slots; a.flags = flags; a.epoch = epoch;
     return launch_fedavg(a, stream);
 }
+
+// ---------------------------------------------------------------------------------------------
+// Aggregation for callers that must not allocate.
+//
+// qfx_fedavg_fused needs n_clients floats of workspace for the per-client squared norms and expects
+// the caller to bring it.  Some callers have nowhere to get it from: a federated server written
+// against this C ABI without PyTorch has no caching allocator to borrow from; a process whose device
+// memory has been handed over wholesale to another framework's arena has been told not to call
+// cudaMalloc at all; and a serving loop that aggregates between client launches cannot afford
+// cudaMalloc/cudaFree there, because both synchronise the whole device and would stall the clients'
+// kernels for the duration of the call.  For them the workspace lives in the library image itself:
+// the array below is part of every GPU's copy of the module from the moment the library is loaded
+// until the process exits (QFX_FEDAVG_STATIC_MAX_CLIENTS * 4 bytes = 16 KiB per GPU).
+//
+// `g_static_norm_scratch` is a device symbol.  In host code that name is only a handle for the
+// runtime - handing it to a kernel as if it were a pointer would make the kernel read host-side
+// bytes or fault - so the host asks the runtime for the device address once per device
+// (cudaGetSymbolAddress, with that device current) and passes that address on.
+static __device__ __align__(256) float g_static_norm_scratch[QFX_FEDAVG_STATIC_MAX_CLIENTS];
+
+namespace qfx {
+constexpr int STATIC_MAX_DEVICES = 64;
+static float* g_static_scratch_addr[STATIC_MAX_DEVICES] = {};
+
+// Device address of the static workspace on the current device; looked up on the first call per device.
+static int static_scratch_for_current_device(float** out) {
+    int dev = 0;
+    QFX_CUDA_TRY(cudaGetDevice(&dev));
+    QFX_ARG_CHECK(dev >= 0 && dev < STATIC_MAX_DEVICES, QFX_ERR_UNSUPPORTED, "device ordinal %d not supported", dev);
+    if (g_static_scratch_addr[dev] == nullptr) {
+        float* addr = nullptr;
+        QFX_CUDA_TRY(cudaGetSymbolAddress((void**)&addr, g_static_norm_scratch));
+        QFX_ARG_CHECK(addr != nullptr, QFX_ERR_UNSUPPORTED, "cudaGetSymbolAddress returned a null address");
+        g_static_scratch_addr[dev] = addr;
+    }
+    *out = g_static_scratch_addr[dev];
+    return 0;
+}
+}  // namespace qfx
+
+// Same computation and arguments as qfx_fedavg_fused, minus the workspace pointer: inputs and outputs
+// still come from the caller, the norm accumulators come from the static array above.  Nothing in
+// this call allocates or frees memory, on the device or through any library.
+//   * n_clients above QFX_FEDAVG_STATIC_MAX_CLIENTS is refused with QFX_ERR_TOO_LARGE and a message
+//     naming the limit; use qfx_fedavg_fused with your own workspace for larger federations.
+//   * The first call on each device looks up the array's device address.  Make that first call during
+//     start-up, with the device current and before any stream capture begins on it.
+//   * All calls on one GPU share the one array and it keeps whatever the previous call left in it.
+//     The accumulators this call uses are cleared on `stream` before the kernel runs, so back-to-back
+//     calls on one stream are safe; two calls that can overlap on the same GPU (different streams,
+//     different host threads) would accumulate into the same floats and corrupt each other's clip
+//     factors - serialise them or give one of them its own workspace through qfx_fedavg_fused.
+extern "C" int qfx_fedavg_fused_static(const float* client_params, const float* global_in, float* global_out,
+                                       const float* weights, const int* participate, int n_clients, int dim,
+                                       int mode, int n_wrap, float clip, float sigma, float server_lr,
+                                       unsigned long long seed, int round, int secagg, float* norms_out,
+                                       long long* masked_out, cudaStream_t stream) {
+    QFX_ARG_CHECK(n_clients <= QFX_FEDAVG_STATIC_MAX_CLIENTS, QFX_ERR_TOO_LARGE,
+                  "qfx_fedavg_fused_static handles at most %d clients per call (got %d); "
+                  "call qfx_fedavg_fused with a caller-provided workspace instead",
+                  QFX_FEDAVG_STATIC_MAX_CLIENTS, n_clients);
+    float* scratch = nullptr;
+    if (int e = static_scratch_for_current_device(&scratch)) return e;
+    AggArgs a = {};
+    a.client_params = client_params; a.global_in = global_in; a.global_out = global_out;
+    a.weights = weights; a.participate = participate; a.client_gids = nullptr;
+    a.k_local = n_clients; a.k_global = n_clients; a.dim = dim; a.mode = mode; a.n_wrap = n_wrap;
+    a.clip = clip; a.sigma = sigma; a.server_lr = server_lr; a.seed = seed; a.round = round; a.secagg = secagg;
+    a.norms_out = norms_out; a.scratch = scratch; a.masked_out = masked_out;
+    a.rank = 0; a.world = 1; a.recv_slots = nullptr; a.flags = nullptr; a.epoch = 0;
+    return launch_fedavg(a, stream);  // clears the accumulators it uses (cudaMemsetAsync), then launches
+}
