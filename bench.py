@@ -301,6 +301,8 @@ def main():
     init_dist(world, local)
     cfgs = {"cfed": CFED, "vqc8": VQC8, "vqc4": VQC4}
     cfg = dict(cfgs[args.config])
+    if os.environ.get("QFX_BENCH_CLIENTS"):  # profiling aid: change the client count
+        cfg["clients"] = int(os.environ["QFX_BENCH_CLIENTS"])
     if os.environ.get("QFX_BENCH_SCALE"):  # shrink the job for smoke runs
         f = float(os.environ["QFX_BENCH_SCALE"])
         for k in ("samples_per_client", "n_train", "test_n"):

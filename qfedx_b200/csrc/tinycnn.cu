@@ -20,8 +20,8 @@ namespace cnn {
 constexpr int BS = 32;           // max minibatch rows handled by the fc kernels
 constexpr int C1W = 0, C1B = 400, C2W = 416, C2B = 13216, F1W = 13248, F1B = 113600, F2W = 113664;
 constexpr int NCONV = 13248;     // conv parameters (reduced from per-image partials)
-constexpr int FC1_SLICES = 16;   // split-K slices of the 1568-long fc1 reduction
-constexpr int FC1_KS = 98;       // 1568 / 16
+constexpr int FC1_SLICES = 14;   // split-K slices of the 1568-long fc1 reduction
+constexpr int FC1_KS = 112;      // 1568 / 14
 constexpr int MAX_CLASSES = 10;
 
 struct Step {
@@ -52,18 +52,31 @@ struct Step {
     float* stats;                    // [K,2] running loss sum / correct count of the epoch
 };
 
-// padded 18x18 planes in shared memory from dense 14x14 planes in global memory
+// Asynchronous global->shared copies (LDGSTS): every copy of a staging loop is in flight at once, so a
+// CTA pays one memory latency for its whole working set instead of one per loop iteration.
+__device__ __forceinline__ void cp_async4(void* smem, const void* gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// padded 18x18 planes in shared memory from dense 14x14 planes in global memory (async; the caller
+// waits with cp_async_wait_all + __syncthreads)
 __device__ __forceinline__ void fill_padded_planes(float* __restrict__ xs, const float* __restrict__ src, int planes) {
     for (int i = threadIdx.x; i < planes * 324; i += blockDim.x) xs[i] = 0.f;
     __syncthreads();
-    for (int i = threadIdx.x; i < planes * 196; i += blockDim.x) {
-        const int c = i / 196, rem = i - c * 196, r = rem / 14, q = rem - r * 14;
-        xs[c * 324 + (r + 2) * 18 + q + 2] = src[i];
+    for (int i = threadIdx.x; i < planes * 98; i += blockDim.x) {  // 7 float2 per 14-float row
+        const int c = i / 98, rem = i - c * 98, r = rem / 7, q2 = rem - r * 7;
+        cp_async8(xs + c * 324 + (r + 2) * 18 + 2 + 2 * q2, src + c * 196 + r * 14 + 2 * q2);
     }
 }
 __device__ __forceinline__ void copy_f4(float* __restrict__ dst, const float* __restrict__ src, int n) {
-    for (int i = threadIdx.x * 4; i < n; i += blockDim.x * 4)
-        *reinterpret_cast<float4*>(dst + i) = *reinterpret_cast<const float4*>(src + i);
+    for (int i = threadIdx.x * 4; i < n; i += blockDim.x * 4) cp_async16(dst + i, src + i);
 }
 
 __device__ __forceinline__ int batch_rows(const Step& s, int sel, int* seg_lo) {
@@ -83,14 +96,17 @@ __device__ __forceinline__ int sample_index(const Step& s, int seg_lo, int b) {
 // position; the 6x6 input window sits in registers, weights are broadcast from shared memory.
 __device__ __forceinline__ void conv1_image(const float* __restrict__ img, const float* __restrict__ prm,
                                             float* __restrict__ a1, unsigned char* __restrict__ i1) {
-    __shared__ float xs[32 * 32];
-    __shared__ float ws[16 * 25 + 16];
+    __shared__ __align__(16) float xs[32 * 32];
+    __shared__ __align__(16) float ws[16 * 25 + 16];
     const int tid = threadIdx.x;
-    for (int i = tid; i < 32 * 32; i += blockDim.x) {
-        const int y = (i >> 5) - 2, x = (i & 31) - 2;
-        xs[i] = (y >= 0 && y < 28 && x >= 0 && x < 28) ? img[y * 28 + x] : 0.f;
+    for (int i = tid; i < 32 * 32; i += blockDim.x) xs[i] = 0.f;
+    __syncthreads();
+    for (int i = tid; i < 28 * 14; i += blockDim.x) {  // 14 float2 per image row
+        const int y = i / 14, x2 = i - y * 14;
+        cp_async8(xs + (y + 2) * 32 + 2 + 2 * x2, img + y * 28 + 2 * x2);
     }
-    for (int i = tid; i < 416; i += blockDim.x) ws[i] = prm[C1W + i];
+    for (int i = tid; i < 104; i += blockDim.x) cp_async16(ws + 4 * i, prm + C1W + 4 * i);
+    cp_async_wait_all();
     __syncthreads();
     if (tid >= 196) return;
     const int py = tid / 14, px = tid % 14;
@@ -181,6 +197,7 @@ __device__ __forceinline__ void conv2_image(const float* __restrict__ a1, const 
     const int tid = threadIdx.x;
     copy_f4(ws, w2f, 12800);
     fill_padded_planes(xs, a1, 16);
+    cp_async_wait_all();
     __syncthreads();
     const int g = tid >> 6, pos = tid & 63;
     if (pos >= 49) return;
@@ -231,30 +248,32 @@ __global__ void __launch_bounds__(256) conv2_weight_prep(const float* __restrict
 // fc1 forward, split-K: CTA (slice, client) computes the partial [32 x 64] product over 98 inputs.
 // 128 threads, each a 4x4 (rows x features) register tile.
 __global__ void __launch_bounds__(128) fc1_fwd_train(const Step s) {
-    __shared__ float xs[BS][FC1_KS + 1];       // [b][k], coalesced fill, conflict-free column reads
+    __shared__ float xs[BS][FC1_KS + 1];       // [b][k]; odd row stride -> conflict-free column reads
     __shared__ float wsm[64][FC1_KS + 1];      // [f][k]
     const int sel = blockIdx.y, sl = blockIdx.x, tid = threadIdx.x;
     int lo;
     const int nb = batch_rows(s, sel, &lo);
     if (nb <= 0) return;
-    const float* x = s.a2 + (size_t)sel * BS * 1568 + sl * FC1_KS;
-    const float* w = s.params + (size_t)sel * s.nd + F1W + sl * FC1_KS;
+    const float* __restrict__ x = s.a2 + (size_t)sel * BS * 1568 + sl * FC1_KS;
+    const float* __restrict__ w = s.params + (size_t)sel * s.nd + F1W + sl * FC1_KS;
     for (int i = tid; i < BS * FC1_KS; i += 128) {
         const int b = i / FC1_KS, k = i - b * FC1_KS;
-        xs[b][k] = b < nb ? x[(size_t)b * 1568 + k] : 0.f;
+        if (b < nb) cp_async4(&xs[b][k], x + (size_t)b * 1568 + k); else xs[b][k] = 0.f;
     }
     for (int i = tid; i < 64 * FC1_KS; i += 128) {
         const int f = i / FC1_KS, k = i - f * FC1_KS;
-        wsm[f][k] = w[(size_t)f * 1568 + k];
+        cp_async4(&wsm[f][k], w + (size_t)f * 1568 + k);
     }
+    cp_async_wait_all();
     __syncthreads();
-    const int bt = (tid >> 4) * 4, ft = (tid & 15) * 4;
+    // 4 rows x 4 features per thread; features strided by 16 so a warp reads 16 consecutive rows of wsm
+    const int bt = (tid >> 4) * 4, f0 = tid & 15;
     float acc[4][4] = {};
-#pragma unroll 2
+#pragma unroll 4
     for (int k = 0; k < FC1_KS; ++k) {
         float xa[4], wa[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) { xa[i] = xs[bt + i][k]; wa[i] = wsm[ft + i][k]; }
+        for (int i = 0; i < 4; ++i) { xa[i] = xs[bt + i][k]; wa[i] = wsm[f0 + 16 * i][k]; }
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -263,7 +282,8 @@ __global__ void __launch_bounds__(128) fc1_fwd_train(const Step s) {
     float* out = s.fc1_part + (((size_t)sel * FC1_SLICES + sl) * BS) * 64;
 #pragma unroll
     for (int i = 0; i < 4; ++i)
-        *reinterpret_cast<float4*>(out + (bt + i) * 64 + ft) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) out[(bt + i) * 64 + f0 + 16 * j] = acc[i][j];
 }
 
 // ------------------------------------------------------------------------------------------
@@ -293,9 +313,12 @@ __global__ void __launch_bounds__(256) head_train(const Step s) {
         float v = 0.f;
         if (b < nb) {
             v = prm[F1B + f];
-            const float* part = s.fc1_part + ((size_t)sel * FC1_SLICES * BS + b) * 64 + f;
+            const float* __restrict__ part = s.fc1_part + ((size_t)sel * FC1_SLICES * BS + b) * 64 + f;
+            float pv[FC1_SLICES];
 #pragma unroll
-            for (int sl = 0; sl < FC1_SLICES; ++sl) v += part[(size_t)sl * BS * 64];
+            for (int sl = 0; sl < FC1_SLICES; ++sl) pv[sl] = __ldg(part + (size_t)sl * BS * 64);
+#pragma unroll
+            for (int sl = 0; sl < FC1_SLICES; ++sl) v += pv[sl];
             v = fmaxf(v, 0.f);
             if (s.p_drop > 0.f) {
                 const float u = uniform_from_bits(stream_at(dkey, (unsigned long long)i));
@@ -384,12 +407,16 @@ __global__ void __launch_bounds__(256) fc1_bwd_train(const Step s) {
     if (nb <= 0) return;
     float* prm = s.params + (size_t)sel * s.nd;
     float* mom = s.moment + (size_t)sel * s.nd;
-    for (int i = tid; i < BS * 64; i += 256) dh[i >> 6][i & 63] = (i >> 6) < nb ? s.dh1[(size_t)sel * BS * 64 + i] : 0.f;
+    for (int i = tid * 4; i < BS * 64; i += 1024) {
+        if ((i >> 6) < nb) cp_async16(&dh[0][0] + i, s.dh1 + (size_t)sel * BS * 64 + i);
+        else *reinterpret_cast<float4*>(&dh[0][0] + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     for (int i = tid; i < BS * 32; i += 256) {
         const int b = i >> 5, k = i & 31;
-        xs[b][k] = b < nb ? s.a2[((size_t)sel * BS + b) * 1568 + k0 + k] : 0.f;
+        if (b < nb) cp_async4(&xs[b][k], s.a2 + ((size_t)sel * BS + b) * 1568 + k0 + k); else xs[b][k] = 0.f;
     }
-    for (int i = tid; i < 64 * 32; i += 256) wsm[i >> 5][i & 31] = prm[F1W + (size_t)(i >> 5) * 1568 + k0 + (i & 31)];
+    for (int i = tid; i < 64 * 32; i += 256) cp_async4(&wsm[i >> 5][i & 31], prm + F1W + (size_t)(i >> 5) * 1568 + k0 + (i & 31));
+    cp_async_wait_all();
     __syncthreads();
     // dx[b][k] = sum_f dh[b][f] W1[f][k]; 1024 outputs, 4 per thread (b = tid/8 .., k = ..)
     {
@@ -449,6 +476,7 @@ __global__ void __launch_bounds__(256) conv2_dgrad_train(const Step s) {
     const size_t row = (size_t)sel * BS + b;
     copy_f4(ws, s.w2b + (size_t)sel * 12800, 12800);
     fill_padded_planes(xs, s.g2 + row * 32 * 196, 32);
+    cp_async_wait_all();
     __syncthreads();
     const int g = tid >> 6, pos = tid & 63;
     if (pos >= 49) return;
@@ -482,6 +510,7 @@ __global__ void __launch_bounds__(320) conv2_wgrad_train(const Step s) {
     const size_t row = (size_t)sel * BS + b;
     copy_f4(gs, s.g2 + row * 32 * 196, 32 * 196);
     fill_padded_planes(xs, s.a1 + row * 3136, 16);
+    cp_async_wait_all();
     __syncthreads();
     const int ky = tid % 5, c = (tid / 5) % 16, og = tid / 80;  // og in 0..3
     float acc[8][5] = {};
@@ -528,14 +557,33 @@ __global__ void __launch_bounds__(416) conv1_wgrad_train(const Step s) {
     if (b >= nb) return;  // conv_part rows of absent images were zeroed by conv2_wgrad_train
     const size_t row = (size_t)sel * BS + b;
     const float* img = s.X + (size_t)sample_index(s, lo, b) * 784;
-    for (int i = tid; i < 1024; i += 416) {
-        const int y = (i >> 5) - 2, x = (i & 31) - 2;
-        xs[(i >> 5) * XS1 + (i & 31)] = (y >= 0 && y < 28 && x >= 0 && x < 28) ? img[y * 28 + x] : 0.f;
+    for (int i = tid; i < 32 * XS1; i += 416) xs[i] = 0.f;
+    __syncthreads();
+    for (int i = tid; i < 784; i += 416) {
+        const int y = i / 28, x = i - y * 28;
+        cp_async4(xs + (y + 2) * XS1 + x + 2, img + i);
     }
-    for (int i = tid; i < 3136; i += 416) {
-        gsm[i] = s.a1[row * 3136 + i] > 0.f ? s.da1[row * 3136 + i] : 0.f;
-        ism[i] = s.i1[row * 3136 + i];
+    {
+        const float4* __restrict__ a4 = reinterpret_cast<const float4*>(s.a1 + row * 3136);
+        const float4* __restrict__ d4 = reinterpret_cast<const float4*>(s.da1 + row * 3136);
+        const uchar4* __restrict__ i4 = reinterpret_cast<const uchar4*>(s.i1 + row * 3136);
+        float4 av[2], dv[2]; uchar4 iv[2];
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            const int i = tid + r * 416;
+            if (i < 784) { av[r] = __ldg(a4 + i); dv[r] = __ldg(d4 + i); iv[r] = __ldg(i4 + i); }
+        }
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            const int i = tid + r * 416;
+            if (i < 784) {
+                gsm[4 * i] = av[r].x > 0.f ? dv[r].x : 0.f;     gsm[4 * i + 1] = av[r].y > 0.f ? dv[r].y : 0.f;
+                gsm[4 * i + 2] = av[r].z > 0.f ? dv[r].z : 0.f; gsm[4 * i + 3] = av[r].w > 0.f ? dv[r].w : 0.f;
+                ism[4 * i] = iv[r].x; ism[4 * i + 1] = iv[r].y; ism[4 * i + 2] = iv[r].z; ism[4 * i + 3] = iv[r].w;
+            }
+        }
     }
+    cp_async_wait_all();
     __syncthreads();
     float* part = s.conv_part + row * NCONV;
     if (tid < 400) {

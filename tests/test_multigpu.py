@@ -20,3 +20,10 @@ def test_fused_cross_gpu_aggregation_matches_nccl_baseline():
     n = min(torch.cuda.device_count(), 8)
     res = _torchrun(os.path.join(ROOT, "tests", "helpers", "multigpu_agg_worker.py"), n, 29617)
     assert "MULTIGPU_AGG_OK" in res.stdout, res.stdout[-3000:] + res.stderr[-3000:]
+
+
+def test_sharded_statevector_matches_single_gpu_engine():
+    n = torch.cuda.device_count()
+    n = 8 if n >= 8 else (4 if n >= 4 else 2)
+    res = _torchrun(os.path.join(ROOT, "tests", "helpers", "multigpu_sharded_worker.py"), n, 29618)
+    assert "MULTIGPU_SHARDED_OK" in res.stdout, res.stdout[-3000:] + res.stderr[-3000:]
