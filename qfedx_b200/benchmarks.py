@@ -67,6 +67,50 @@ def aggregation_latency(K=64, D=102, secagg=False):
     return {"K": K, "D": D, "secagg": secagg, "ms": ms, "bytes": K * D * 4, "gbps": K * D * 4 / ms / 1e6}
 
 
+def unitary_gemm_throughput(n=8, L=6, B=1 << 15):
+    """K2: samples/s and TFLOP/s of the tcgen05 complex GEMM (3xTF32 and plain TF32) vs the register kernel."""
+    from .ops import statevector as sv
+    from .ops.unitary_gemm import UnitaryGemm
+    dev = torch.device("cuda")
+    theta = torch.randn(1, L, n, 2, device=dev)
+    ang = torch.rand(B, n, device=dev) * math.pi
+    out = {"n_qubits": n, "batch": B}
+    m = 2 << n
+    for prec in (3, 1):
+        ug = UnitaryGemm(theta, precision=prec)
+        bp = ug._pad(B)
+        b_hi = torch.empty(bp, m, device=dev); b_lo = torch.empty_like(b_hi)
+        from .ops import _lib
+        from .ops.statevector import BASIS
+        _lib.call("qfx_unitary_pack_product_states", _lib.ptr(ang), _lib.c_int(n), _lib.c_int(BASIS["ry"]), _lib.c_int(B),
+                  _lib.c_int(bp), _lib.ptr(b_hi), _lib.ptr(b_lo), _lib.stream_ptr())
+        gemm_only = _time_ms(lambda: ug._gemm(b_hi, b_lo, bp, True, False), iters=10)
+        e2e = _time_ms(lambda: ug.expvals(ang), iters=10)
+        flops = 2.0 * m * m * bp * prec
+        out[f"tf32x{prec}"] = {"gemm_ms": gemm_only, "gemm_tflops": flops / gemm_only / 1e9,
+                               "expvals_pipeline_ms": e2e, "samples_per_s": B / e2e * 1e3}
+    reg = _time_ms(lambda: sv.sv_forward(ang, theta), iters=10)
+    out["register_kernel_ms"] = reg
+    return out
+
+
+def large_state_throughput(n=20, L=2, batch=16, tile_bits=12, low_bits=3):
+    """K5: gates/s of the pass engine on `batch` n-qubit states (config 4 shape: 16 clients x 20 qubits)."""
+    from .ops.large import LargeVQC, expvals_z
+    dev = torch.device("cuda")
+    vqc = LargeVQC(n, L, tile_bits=tile_bits, low_bits=low_bits)
+    ang = torch.rand(batch, n, device=dev) * math.pi
+    theta = torch.randn(1, vqc.n_params, device=dev)
+    ms = _time_ms(lambda: vqc.states(ang, theta), iters=5, warmup=2)
+    st = vqc.states(ang, theta)
+    ez = _time_ms(lambda: expvals_z(st, n), iters=5, warmup=1)
+    state_bytes = (1 << n) * 8 * batch
+    return {"n_qubits": n, "layers": L, "batch": batch, "tile_bits": tile_bits, "low_bits": low_bits,
+            "passes": len(vqc.passes), "gates": vqc.n_gates, "ms": ms,
+            "gates_per_s": vqc.n_gates * batch / ms * 1e3,
+            "effective_gbs": 2 * state_bytes * len(vqc.passes) / ms / 1e6, "expz_ms": ez}
+
+
 def aux_measurements(args=None, rank=0, world=1, local=0, skip=None):
     out = {}
     if rank != 0:
@@ -77,8 +121,18 @@ def aux_measurements(args=None, rank=0, world=1, local=0, skip=None):
     out["agg_vqc"] = aggregation_latency(64, 102)
     out["agg_tinycnn_dp_secagg"] = aggregation_latency(8, 113859, True)
     out["agg_1e8"] = aggregation_latency(4, 25_000_000)
+    out["unitary_gemm_8q"] = unitary_gemm_throughput(8, 6, 1 << 15)
+    out["sv20_pass_engine"] = large_state_throughput(20, 2, 16)
     return out
 
 
 if __name__ == "__main__":
-    print(json.dumps(aux_measurements(), indent=1))
+    import sys
+    if len(sys.argv) > 1 and sys.argv[1] == "tiles":
+        res = []
+        for tb, lb in [(12, 3), (12, 4), (12, 5), (11, 3), (10, 3), (12, 2)]:
+            res.append(large_state_throughput(20, 2, 16, tb, lb))
+            res.append(large_state_throughput(26, 1, 1, tb, lb))
+        print(json.dumps(res, indent=1))
+    else:
+        print(json.dumps(aux_measurements(), indent=1))

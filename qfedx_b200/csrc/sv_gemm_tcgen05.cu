@@ -129,6 +129,8 @@ unitary_gemm_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_c
     __shared__ __align__(8) uint64_t empty_bar[STAGES];
     __shared__ __align__(8) uint64_t accum_bar;
     __shared__ uint32_t tmem_base_slot;
+    __shared__ float ztile[4 * 32 * 33];   // per epilogue warp: transposed block of squared amplitudes
+    __shared__ float zacc[BN * 16];        // <Z> partial sums of this CTA: [column][qubit (<= 12, padded to 16)]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
@@ -210,7 +212,10 @@ unitary_gemm_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_c
         const int row = m0 + q * 32 + lane;  // output component index m (0 .. M-1)
         // sign table of this row for the <Z> reduction: component m = part * dim + amplitude index
         const int dim = g.m_total >> 1;
-        const int amp = row % dim;
+        if (g.expvals != nullptr) {
+            for (int e = threadIdx.x - 64; e < BN * 16; e += 128) zacc[e] = 0.f;
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+        }
 #pragma unroll 1
         for (int c0 = 0; c0 < BN; c0 += 32) {
             uint32_t r[32];
@@ -221,18 +226,41 @@ unitary_gemm_kernel(const __grid_constant__ CUtensorMap map_a_hi, const __grid_c
                     g.out[(size_t)(n0 + c0 + j) * g.m_total + row] = __uint_as_float(r[j]);
             }
             if (g.expvals != nullptr) {
-                // <Z_q> = sum_i sign_q(i) |amp_i|^2 and |amp|^2 = re^2 + im^2 is linear in the squares,
-                // so every row contributes sign * v^2 independently; reduce over the 32 rows of the warp
-                for (int qb = 0; qb < g.n_qubits; ++qb) {
-                    const float sgn = ((amp >> qb) & 1) ? -1.f : 1.f;
+                // <Z_q> = sum_i sign_q(i) |amp_i|^2, and |amp|^2 = re^2 + im^2 is linear in the squares, so
+                // every row contributes sign * v^2 on its own.  Transpose the 32x32 block of squares through
+                // shared memory: lane j then owns column j and sums it over the warp's 32 rows, once
+                // unsigned (for the qubits whose bit is the same for all 32 rows) and once per lane-bit qubit.
+                float* tp = ztile + (warp - 2) * (32 * 33);
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const float v = __uint_as_float(r[j]);
-                        float t = sgn * v * v;
-                        t = warp_sum(t);
-                        if (lane == 0) atomicAdd(g.expvals + (size_t)(n0 + c0 + j) * g.n_qubits + qb, t);
-                    }
+                for (int j = 0; j < 32; ++j) { const float v = __uint_as_float(r[j]); tp[lane * 33 + j] = v * v; }
+                __syncwarp();
+                float tot = 0.f, d0 = 0.f, d1 = 0.f, d2 = 0.f, d3 = 0.f, d4 = 0.f;
+#pragma unroll
+                for (int rr = 0; rr < 32; ++rr) {
+                    const float pv = tp[rr * 33 + lane];
+                    tot += pv;
+                    d0 += (rr & 1) ? -pv : pv;  d1 += (rr & 2) ? -pv : pv;  d2 += (rr & 4) ? -pv : pv;
+                    d3 += (rr & 8) ? -pv : pv;  d4 += (rr & 16) ? -pv : pv;
                 }
+                __syncwarp();
+                // rows of this warp: amp = base + rr with base a multiple of 32 -> qubits 0..4 follow rr,
+                // qubits >= 5 follow base
+                const int base = (m0 + q * 32) % dim;
+                float* zc = zacc + (c0 + lane) * 16;
+                const float dl[5] = {d0, d1, d2, d3, d4};
+                for (int qb = 0; qb < g.n_qubits; ++qb) {
+                    const float v = qb < 5 ? dl[qb] : (((base >> qb) & 1) ? -tot : tot);
+                    atomicAdd(zc + qb, v);
+                }
+            }
+        }
+        if (g.expvals != nullptr) {
+            // combine the four epilogue warps in shared memory, then one global atomic per (column, qubit)
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            const int t = threadIdx.x - 64;  // 0..127
+            for (int e = t; e < BN * g.n_qubits; e += 128) {
+                const int col = e / g.n_qubits, qb = e - col * g.n_qubits;
+                atomicAdd(g.expvals + (size_t)(n0 + col) * g.n_qubits + qb, zacc[col * 16 + qb]);
             }
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -268,31 +296,42 @@ __global__ void pack_unitary_kernel(const float2* __restrict__ ut, int dim, floa
     }
 }
 
-// feature-map product states straight into the GEMM's B operand: row b = [re(2^n) | im(2^n)]
-__global__ void pack_product_states_kernel(const float* __restrict__ angles, int n_qubits, int basis, int batch,
-                                           int batch_padded, float* __restrict__ b_hi, float* __restrict__ b_lo) {
+// feature-map product states straight into the GEMM's B operand: row b = [re(2^n) | im(2^n)].
+// One CTA handles PACK_SAMPLES samples: their n (cos, sin) pairs are computed once into shared
+// memory, then every thread multiplies n factors per amplitude.
+constexpr int PACK_SAMPLES = 8;
+__global__ void __launch_bounds__(256)
+pack_product_states_kernel(const float* __restrict__ angles, int n_qubits, int basis, int batch, int batch_padded,
+                           float* __restrict__ b_hi, float* __restrict__ b_lo) {
+    __shared__ float2 cs[PACK_SAMPLES][12];
     const int dim = 1 << n_qubits;
-    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < (size_t)batch_padded * dim;
-         idx += (size_t)gridDim.x * blockDim.x) {
-        const int b = (int)(idx / dim), i = (int)(idx % dim);
-        float re = 0.f, im = 0.f;
-        if (b < batch) {
-            re = 1.f;
+    for (int b0 = blockIdx.x * PACK_SAMPLES; b0 < batch_padded; b0 += gridDim.x * PACK_SAMPLES) {
+        __syncthreads();
+        if (threadIdx.x < PACK_SAMPLES * n_qubits) {
+            const int sidx = threadIdx.x / n_qubits, q = threadIdx.x - sidx * n_qubits;
+            float sn = 0.f, c = 0.f;
+            if (b0 + sidx < batch) sincosf(0.5f * angles[(size_t)(b0 + sidx) * n_qubits + q], &sn, &c);
+            cs[sidx][q] = make_float2(c, sn);
+        }
+        __syncthreads();
+        for (int e = threadIdx.x; e < PACK_SAMPLES * dim; e += 256) {
+            const int sidx = e / dim, i = e - sidx * dim, b = b0 + sidx;
+            if (b >= batch_padded) break;
+            float re = (b < batch) ? 1.f : 0.f, im = 0.f;
             for (int q = 0; q < n_qubits; ++q) {
-                float s, c;
-                sincosf(0.5f * angles[(size_t)b * n_qubits + q], &s, &c);
+                const float2 v = cs[sidx][q];
                 const bool bit = (i >> q) & 1;
                 float fr, fi;
-                if (basis == 1) { fr = bit ? s : c; fi = 0.f; }
-                else if (basis == 0) { fr = bit ? 0.f : c; fi = bit ? -s : 0.f; }
-                else { fr = bit ? 0.f : c; fi = bit ? 0.f : -s; }
+                if (basis == 1) { fr = bit ? v.y : v.x; fi = 0.f; }
+                else if (basis == 0) { fr = bit ? 0.f : v.x; fi = bit ? -v.y : 0.f; }
+                else { fr = bit ? 0.f : v.x; fi = bit ? 0.f : -v.y; }
                 const float nr = re * fr - im * fi, ni = re * fi + im * fr;
                 re = nr; im = ni;
             }
+            const size_t o = (size_t)b * 2 * dim;
+            split_tf32(re, b_hi + o + i, b_lo + o + i);
+            split_tf32(im, b_hi + o + dim + i, b_lo + o + dim + i);
         }
-        const size_t o = (size_t)b * 2 * dim;
-        split_tf32(re, b_hi + o + i, b_lo + o + i);
-        split_tf32(im, b_hi + o + dim + i, b_lo + o + dim + i);
     }
 }
 
