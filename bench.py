@@ -335,7 +335,7 @@ def main():
         line = {
             "metric": "fl_rounds_per_sec", "value": value, "unit": "rounds/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms"], "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "fp32" if args.config != "cfed" or args.impl == "reference" else "bf16",
+            "scaling": "strong", "vs_baseline": None, "dtype": "fp32",
             "data": "synthetic MNIST-shape images, random-init weights",
             "impl": args.impl,
             "config": {"name": args.config, "model": r["model"], "clients": r["clients"], "global_batch": r["samples"],

@@ -198,6 +198,18 @@ int qfx_sv_global_swap_fused(const float* const* src_table, float* dst, int n_lo
                              int n_feature, unsigned int* const* flags_table, unsigned int epoch,
                              cudaStream_t stream);
 
+/* TinyCNN conv2 on tcgen05 as a zero-copy implicit GEMM (csrc/tinycnn_umma.cu); standalone entry used by
+ * the tests: forward conv + bias + ReLU + 2x2 max-pool of n images.  a1 [n,16,14,14], weight [32,16,5,5],
+ * bias [32] fp32; a2 [n,32,7,7] fp32, i2 [n,32,7,7] u8 (argmax 0..3); scratch 51,200 bytes.
+ * Model: /root/reference/src/CFed/Classical_FL.py:25,33-34. */
+int qfx_tinycnn_conv2_fwd_umma(const float* a1, const float* weight, const float* bias, int n, float* a2,
+                               unsigned char* i2, void* scratch, cudaStream_t stream);
+/* same, backward: data gradient da1 [n,16,14,14] from g2 [n,32,14,14]; per-image weight/bias gradient
+ * partials part [n,13248] (weights at offset 416 in [o][c][tap] order, bias at 13216). */
+int qfx_tinycnn_conv2_dgrad_umma(const float* g2, const float* weight, int n, float* da1, void* scratch,
+                                 cudaStream_t stream);
+int qfx_tinycnn_conv2_wgrad_umma(const float* g2, const float* a1, int n, float* part, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -11,85 +11,11 @@
 // Flat parameter layout per client (state_dict order, matches models/tinycnn.py):
 //   conv1.w [16,1,5,5] @0 | conv1.b [16] @400 | conv2.w [32,16,5,5] @416 | conv2.b [32] @13216 |
 //   fc1.w [64,1568] @13248 | fc1.b [64] @113600 | fc2.w [C,64] @113664 | fc2.b [C] @113664+64C
-#include "common.cuh"
+#include "tinycnn.cuh"
 #include "../../include/qfedx_b200.h"
 
 namespace qfx {
 namespace cnn {
-
-constexpr int BS = 32;           // max minibatch rows handled by the fc kernels
-constexpr int C1W = 0, C1B = 400, C2W = 416, C2B = 13216, F1W = 13248, F1B = 113600, F2W = 113664;
-constexpr int NCONV = 13248;     // conv parameters (reduced from per-image partials)
-constexpr int FC1_SLICES = 14;   // split-K slices of the 1568-long fc1 reduction
-constexpr int FC1_KS = 112;      // 1568 / 14
-constexpr int MAX_CLASSES = 10;
-
-struct Step {
-    const float* X;          // [N,1,28,28] dataset
-    const int* labels;       // [N]
-    const int* offsets;      // [K+1]
-    const int* perm;         // [E,N] or null
-    const int* client_ids;   // [K_sel] rows -> client segment
-    int n_total, epoch, batch_index, batch_size;
-    float* params;           // [K_sel, ND]
-    float* moment;           // [K_sel, ND]
-    int nd;                  // row stride of params/moment
-    int n_classes;
-    float lr, momentum, p_drop;
-    unsigned long long seed;
-    int round;
-    // activations / workspaces, all [K_sel, ...]
-    float* a1; unsigned char* i1;    // [K,32,16,14,14]
-    float* a2; unsigned char* i2;    // [K,32,32,7,7]
-    float* fc1_part;                 // [K,16,32,64]
-    float* h1;                       // [K,32,64]
-    float* dh1;                      // [K,32,64]
-    float* g2;                       // [K,32,32,14,14]
-    float* da1;                      // [K,32,16,14,14]
-    float* conv_part;                // [K,32,NCONV]
-    float* w2f;                      // [K,12800] conv2 weights as [c][tap][o]      (forward operand)
-    float* w2b;                      // [K,12800] conv2 weights as [o][24-tap][c]   (data-gradient operand)
-    float* stats;                    // [K,2] running loss sum / correct count of the epoch
-};
-
-// Asynchronous global->shared copies (LDGSTS): every copy of a staging loop is in flight at once, so a
-// CTA pays one memory latency for its whole working set instead of one per loop iteration.
-__device__ __forceinline__ void cp_async4(void* smem, const void* gmem) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
-
-// padded 18x18 planes in shared memory from dense 14x14 planes in global memory (async; the caller
-// waits with cp_async_wait_all + __syncthreads)
-__device__ __forceinline__ void fill_padded_planes(float* __restrict__ xs, const float* __restrict__ src, int planes) {
-    for (int i = threadIdx.x; i < planes * 324; i += blockDim.x) xs[i] = 0.f;
-    __syncthreads();
-    for (int i = threadIdx.x; i < planes * 98; i += blockDim.x) {  // 7 float2 per 14-float row
-        const int c = i / 98, rem = i - c * 98, r = rem / 7, q2 = rem - r * 7;
-        cp_async8(xs + c * 324 + (r + 2) * 18 + 2 + 2 * q2, src + c * 196 + r * 14 + 2 * q2);
-    }
-}
-__device__ __forceinline__ void copy_f4(float* __restrict__ dst, const float* __restrict__ src, int n) {
-    for (int i = threadIdx.x * 4; i < n; i += blockDim.x * 4) cp_async16(dst + i, src + i);
-}
-
-__device__ __forceinline__ int batch_rows(const Step& s, int sel, int* seg_lo) {
-    const int client = s.client_ids[sel];
-    const int lo = s.offsets[client], n_k = s.offsets[client + 1] - lo;
-    *seg_lo = lo;
-    const int b0 = s.batch_index * s.batch_size;
-    return max(0, min(s.batch_size, n_k - b0));
-}
-__device__ __forceinline__ int sample_index(const Step& s, int seg_lo, int b) {
-    const int j = s.batch_index * s.batch_size + b;
-    return s.perm ? s.perm[(size_t)s.epoch * s.n_total + seg_lo + j] : seg_lo + j;
-}
 
 // ------------------------------------------------------------------------------------------
 // conv1 5x5 (1->16, pad 2) + bias + ReLU + 2x2 maxpool.  One CTA per image, one thread per pooled
@@ -191,7 +117,7 @@ constexpr int CONV2_SMEM = (16 * 324 + 16 * 25 * 32) * 4;  // 71,936 B
 // (a broadcast) per tap.  w2f is the pre-transposed [c][tap][o] copy kept current by sgd_conv_train.
 __device__ __forceinline__ void conv2_image(const float* __restrict__ a1, const float* __restrict__ w2f,
                                             const float* __restrict__ bias, float* __restrict__ a2,
-                                            unsigned char* __restrict__ i2, float* smem) {
+                                            unsigned char* __restrict__ i2, float* smem, int g0) {
     float* xs = smem;                 // [16][18][18]
     float* ws = smem + 16 * 324;      // [16][25][32]
     const int tid = threadIdx.x;
@@ -199,7 +125,7 @@ __device__ __forceinline__ void conv2_image(const float* __restrict__ a1, const 
     fill_padded_planes(xs, a1, 16);
     cp_async_wait_all();
     __syncthreads();
-    const int g = tid >> 6, pos = tid & 63;
+    const int g = g0 + (tid >> 6), pos = tid & 63;
     if (pos >= 49) return;
     const int py = pos / 7, px = pos % 7;
     float acc[4][8];
@@ -221,13 +147,13 @@ __global__ void __launch_bounds__(256) conv2_fwd_train(const Step s) {
     if (b >= batch_rows(s, sel, &lo)) return;
     const size_t r = (size_t)sel * BS + b;
     conv2_image(s.a1 + r * 3136, s.w2f + (size_t)sel * 12800, s.params + (size_t)sel * s.nd + C2B, s.a2 + r * 1568,
-                s.i2 + r * 1568, smem);
+                s.i2 + r * 1568, smem, blockIdx.z * (4 / s.split));
 }
 __global__ void __launch_bounds__(256) conv2_fwd_eval(const float* __restrict__ a1, const float* __restrict__ w2f,
                                                       const float* __restrict__ prm, float* a2, unsigned char* i2) {
     extern __shared__ __align__(16) float smem[];
     const size_t r = blockIdx.x;
-    conv2_image(a1 + r * 3136, w2f, prm + C2B, a2 + r * 1568, i2 + r * 1568, smem);
+    conv2_image(a1 + r * 3136, w2f, prm + C2B, a2 + r * 1568, i2 + r * 1568, smem, 0);
 }
 
 // [o][c][tap] -> forward copy [c][tap][o] and data-gradient copy [o][24-tap][c]
@@ -478,7 +404,7 @@ __global__ void __launch_bounds__(256) conv2_dgrad_train(const Step s) {
     fill_padded_planes(xs, s.g2 + row * 32 * 196, 32);
     cp_async_wait_all();
     __syncthreads();
-    const int g = tid >> 6, pos = tid & 63;
+    const int g = blockIdx.z * (4 / s.split) + (tid >> 6), pos = tid & 63;
     if (pos >= 49) return;
     const int py = pos / 7, px = pos % 7;
     float acc[4][4];
@@ -504,7 +430,7 @@ __global__ void __launch_bounds__(320) conv2_wgrad_train(const Step s) {
     const int nb = batch_rows(s, sel, &lo);
     float* part = s.conv_part + ((size_t)sel * BS + b) * NCONV;
     if (b >= nb) {  // keep the reduction in sgd_conv branch-free: absent images contribute zeros
-        if (nb > 0) for (int i = tid; i < NCONV; i += 320) part[i] = 0.f;
+        if (nb > 0 && blockIdx.z == 0) for (int i = tid; i < NCONV; i += blockDim.x) part[i] = 0.f;
         return;
     }
     const size_t row = (size_t)sel * BS + b;
@@ -512,7 +438,7 @@ __global__ void __launch_bounds__(320) conv2_wgrad_train(const Step s) {
     fill_padded_planes(xs, s.a1 + row * 3136, 16);
     cp_async_wait_all();
     __syncthreads();
-    const int ky = tid % 5, c = (tid / 5) % 16, og = tid / 80;  // og in 0..3
+    const int ky = tid % 5, c = (tid / 5) % 16, og = blockIdx.z * (4 / s.split) + tid / 80;  // og in 0..3
     float acc[8][5] = {};
     for (int y = 0; y < 14; ++y) {
         float xr[18];
@@ -535,7 +461,7 @@ __global__ void __launch_bounds__(320) conv2_wgrad_train(const Step s) {
 #pragma unroll
         for (int kx = 0; kx < 5; ++kx) part[C2W + (og * 8 + o) * 400 + c * 25 + ky * 5 + kx] = acc[o][kx];
     // conv2 bias gradient: sum of g2 over positions, one thread per output channel
-    if (tid < 32) {
+    if (blockIdx.z == 0 && tid < 32) {
         float sum = 0.f;
         for (int i = 0; i < 196; ++i) sum += gs[tid * 196 + i];
         part[C2B + tid] = sum;
@@ -749,13 +675,16 @@ extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const i
     s.lr = lr; s.momentum = momentum; s.p_drop = p_drop; s.seed = seed; s.round = round;
     carve(s, workspace, (size_t)n_selected);
     const dim3 gimg(batch_size, n_selected);
+    // few clients -> few CTAs: spread the channel groups of the conv2 kernels over up to 4 CTAs per image
+    s.split = n_selected >= 4 ? 1 : (n_selected >= 2 ? 2 : 4);
+    const dim3 gsplit(batch_size, n_selected, s.split);
     conv1_fwd_train<<<gimg, 224, 0, stream>>>(s);
-    conv2_fwd_train<<<gimg, 256, CONV2_SMEM, stream>>>(s);
+    conv2_fwd_train<<<gsplit, 256 / s.split, CONV2_SMEM, stream>>>(s);
     fc1_fwd_train<<<dim3(FC1_SLICES, n_selected), 128, 0, stream>>>(s);
     head_train<<<n_selected, 256, 0, stream>>>(s);
     fc1_bwd_train<<<dim3(49, n_selected), 256, 0, stream>>>(s);
-    conv2_dgrad_train<<<gimg, 256, DGRAD_SMEM, stream>>>(s);
-    conv2_wgrad_train<<<dim3(BS, n_selected), 320, WGRAD_SMEM, stream>>>(s);
+    conv2_dgrad_train<<<gsplit, 256 / s.split, DGRAD_SMEM, stream>>>(s);
+    conv2_wgrad_train<<<dim3(BS, n_selected, s.split), 320 / s.split, WGRAD_SMEM, stream>>>(s);
     conv1_wgrad_train<<<gimg, 416, 0, stream>>>(s);
     sgd_conv_train<<<dim3((NCONV + 255) / 256, n_selected), 256, 0, stream>>>(s);
     return check_launch("tinycnn_train_step");

@@ -1,0 +1,436 @@
+// TinyCNN conv2 (5x5, 16 -> 32 channels, pad 2) on the tcgen05 tensor cores as a ZERO-COPY implicit GEMM.
+//
+// The activation of one image is kept in shared memory as bf16 "half planes": plane h holds channels
+// 8h..8h+7 of every pixel, 16 bytes per pixel, pixels laid out row-major with a pitch of 32 and a
+// 2-pixel zero border.  Eight consecutive pixels of a plane are 128 contiguous bytes - exactly one
+// UMMA core matrix (8 rows x 16 bytes) of the un-swizzled K-major operand layout.  The im2col matrix of
+// filter tap (ky, kx) is therefore nothing but the same planes viewed through a descriptor whose start
+// address is shifted by (ky * 32 + kx) pixels: no im2col buffer is ever built.
+//
+//   forward     D[pixel, oc]  = sum_tap  A_tap[pixel, c]   W_tap[oc, c]^T     M = 4 x 128 pixels, N = 32, K = 16/tap
+//   data grad   D[pixel, c]   = sum_tap  G_tap[pixel, oc]  Wflip_tap[c, oc]^T M = 4 x 128, N = 16, K = 32/tap
+//   weight grad D_tap[oc, c]  = sum_pix  G[pix, oc]^T      A_tap[pix, c]       M = 64 (32 used), N = 16, K = 448 pixels
+//
+// (for the weight gradient both operands are read "MN-major": the 8 channels of a pixel are the
+// contiguous 16 bytes, 8 consecutive pixels form the K direction of a core matrix.)
+// Accumulators live in TMEM; one elected thread issues the MMAs; four warps run the epilogue
+// (tcgen05.ld -> bias/ReLU/2x2 max-pool, or plain stores).  Operands are bf16, accumulation fp32,
+// master weights and all other layers stay fp32 (standard mixed precision).
+//
+// Restates the conv2 part of the reference model (/root/reference/src/CFed/Classical_FL.py:25,33-34).
+#include <cuda_bf16.h>
+#include "tinycnn.cuh"
+#include "../../include/qfedx_b200.h"
+
+namespace qfx {
+namespace cnn {
+
+constexpr int PITCH = 32;                 // pixels per stored row
+constexpr int PLANE_PIX = 672;            // (14 + 4) rows x 32 + slack for the garbage rows of the last M block
+constexpr int PLANE_BYTES = PLANE_PIX * 16;
+constexpr int W2U_BYTES = 25 * 1024;      // 25 taps x (2 k-chunks x 4 oc-groups | 4 k-chunks x 2 c-groups) x 128 B
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// un-swizzled shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start >> 4 | LBO >> 4 << 16 |
+// SBO >> 4 << 32 | version 1 << 46 | layout 0 (SWIZZLE_NONE)
+__device__ __forceinline__ uint64_t desc_noswz(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    return (uint64_t)((addr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
+           ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) | (1ull << 46);
+}
+// kind::f16 instruction descriptor: fp32 accumulate, bf16 x bf16; a_mn / b_mn select MN-major operands
+__host__ __device__ constexpr uint32_t idesc_bf16(int m, int n, int a_mn, int b_mn) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
+           ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void mbar_init1(uint64_t* bar) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(bar)));
+}
+__device__ __forceinline__ void mbar_wait0(uint64_t* bar) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "CW_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n"
+        "@p bra CW_DONE;\n"
+        "bra CW_LOOP;\n"
+        "CW_DONE:\n"
+        "}\n" ::"r"(smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ void umma_commit1(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_addr(bar)) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void tmem_ld(uint32_t taddr, uint32_t (&r)[N]);
+template <>
+__device__ __forceinline__ void tmem_ld<32>(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+template <>
+__device__ __forceinline__ void tmem_ld<16>(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// planar fp32 [C][14][14] (global) -> bf16 half planes with pitch 32 and a 2-pixel zero border (shared).
+// The planes must have been zero-filled before.  One item = (pixel, half plane): 8 channel values.
+template <int C>
+__device__ __forceinline__ void fill_half_planes(uint8_t* planes, const float* __restrict__ src) {
+    for (int it = threadIdx.x; it < 196 * (C / 8); it += blockDim.x) {
+        const int h = it / 196, pix = it - h * 196, y = pix / 14, x = pix - y * 14;
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = __ldg(src + (8 * h + j) * 196 + pix);
+        uint4 packed = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+        *reinterpret_cast<uint4*>(planes + (size_t)h * PLANE_BYTES + ((y + 2) * PITCH + x + 2) * 16) = packed;
+    }
+}
+__device__ __forceinline__ void zero_bytes16(uint8_t* p, int bytes) {
+    for (int i = threadIdx.x * 16; i < bytes; i += blockDim.x * 16) *reinterpret_cast<uint4*>(p + i) = make_uint4(0, 0, 0, 0);
+}
+
+// ------------------------------------------------------------------------------------------
+// operand copies of the conv2 weights in UMMA layouts (bf16), kept current by the SGD kernel:
+//   w2uf (forward):  [tap][k-chunk h (2)][oc group (4)][8 oc][8 c]     B is [N = oc][K = c], K-major
+//   w2ub (dgrad):    [24-tap][k-chunk h (4)][c group (2)][8 c][8 oc]   B is [N = c][K = oc], K-major
+__device__ __forceinline__ void store_w2u(__nv_bfloat16* w2uf, __nv_bfloat16* w2ub, int o, int c, int tap, float v) {
+    const __nv_bfloat16 bv = __float2bfloat16_rn(v);
+    w2uf[(((tap * 2 + (c >> 3)) * 4 + (o >> 3)) * 8 + (o & 7)) * 8 + (c & 7)] = bv;
+    w2ub[((((24 - tap) * 4 + (o >> 3)) * 2 + (c >> 3)) * 8 + (c & 7)) * 8 + (o & 7)] = bv;
+}
+__global__ void __launch_bounds__(256) conv2_weight_prep_umma(const float* __restrict__ params, int nd, __nv_bfloat16* w2uf,
+                                                              __nv_bfloat16* w2ub) {
+    const int sel = blockIdx.y, i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= 12800) return;
+    const int o = i / 400, rem = i - o * 400, c = rem / 25, tap = rem - c * 25;
+    store_w2u(w2uf + (size_t)sel * 12800, w2ub + (size_t)sel * 12800, o, c, tap, params[(size_t)sel * nd + C2W + i]);
+}
+
+// ------------------------------------------------------------------------------------------
+// forward: conv + bias + ReLU + 2x2 max-pool for one image per CTA.  192 threads: warp 1 issues the MMAs,
+// warps 2..5 run the epilogue, everybody stages the operands.
+constexpr int FWD_SMEM = 2 * PLANE_BYTES + W2U_BYTES + 14 * 16 * 33 * 4 + 128;   // planes | weights | row maxima
+__device__ __forceinline__ void conv2_fwd_umma_image(const float* __restrict__ a1, const __nv_bfloat16* __restrict__ w2uf,
+                                                     const float* __restrict__ bias, float* __restrict__ a2,
+                                                     unsigned char* __restrict__ i2, uint8_t* smem) {
+    __shared__ __align__(8) uint64_t accum_bar;
+    __shared__ uint32_t tmem_slot;
+    uint8_t* planes = smem;                                   // 2 half planes
+    uint8_t* wts = smem + 2 * PLANE_BYTES;                    // 25 KB
+    float* hmax = reinterpret_cast<float*>(wts + W2U_BYTES);  // [14 rows][16 x-pairs][33]: horizontal maxima (+arg in the sign-free low bit)
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    if (warp == 1 && lane == 0) {
+        mbar_init1(&accum_bar);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 128;" ::"r"(smem_addr(&tmem_slot)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    zero_bytes16(planes, 2 * PLANE_BYTES);
+    for (int i = tid; i < W2U_BYTES / 16; i += blockDim.x) cp_async16(wts + 16 * i, reinterpret_cast<const uint8_t*>(w2uf) + 16 * i);
+    __syncthreads();
+    fill_half_planes<16>(planes, a1);
+    cp_async_wait_all();
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the tensor core
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = tmem_slot;
+
+    if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = idesc_bf16(128, 32, 0, 0);
+            const uint32_t pa = smem_addr(planes), wa = smem_addr(wts);
+#pragma unroll 1
+            for (int blk = 0; blk < 4; ++blk) {
+#pragma unroll 1
+                for (int tap = 0; tap < 25; ++tap) {
+                    const int ky = tap / 5, kx = tap - ky * 5;
+                    // A: rows = 128 consecutive pixels starting at (128 blk + ky*32 + kx); 8-row groups 128 B apart;
+                    //    second k-chunk (channels 8..15) one plane further
+                    const uint64_t ad = desc_noswz(pa + (uint32_t)(128 * blk + ky * PITCH + kx) * 16, PLANE_BYTES, 128);
+                    // B: rows = 32 oc; oc groups 128 B apart; second k-chunk 512 B further
+                    const uint64_t bd = desc_noswz(wa + (uint32_t)tap * 1024, 512, 128);
+                    umma_bf16(tmem + 32 * blk, ad, bd, idesc, tap > 0 ? 1u : 0u);
+                }
+            }
+            umma_commit1(&accum_bar);
+        }
+        __syncwarp();
+    } else if (warp >= 2) {
+        const int q = warp & 3;                  // TMEM lane quarter = image row within the block
+        mbar_wait0(&accum_bar);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll 1
+        for (int blk = 0; blk < 4; ++blk) {
+            const int y = 4 * blk + q;           // image row; lane = x
+            uint32_t r[32];
+            tmem_ld<32>(tmem + ((uint32_t)(q * 32) << 16) + 32 * blk, r);
+            if (y < 14) {
+#pragma unroll
+                for (int o = 0; o < 32; ++o) {
+                    const float v = __uint_as_float(r[o]);
+                    const float p = __shfl_xor_sync(0xffffffffu, v, 1);
+                    if (!(lane & 1) && lane < 14) {
+                        // horizontal maximum of (x, x+1); the winner's column goes into bit 0 of the payload
+                        const bool right = p > v;
+                        const float best = right ? p : v;
+                        hmax[(y * 16 + (lane >> 1)) * 33 + o] = __uint_as_float((__float_as_uint(best) & ~1u) | (right ? 1u : 0u));
+                    }
+                }
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        // vertical maximum + bias + ReLU: 32 oc x 49 pooled positions
+        for (int e = tid - 64; e < 32 * 49; e += 128) {
+            const int o = e / 49, pos = e - o * 49, py = pos / 7, px = pos - py * 7;
+            const uint32_t t0 = __float_as_uint(hmax[((2 * py) * 16 + px) * 33 + o]);
+            const uint32_t t1 = __float_as_uint(hmax[((2 * py + 1) * 16 + px) * 33 + o]);
+            const float v0 = __uint_as_float(t0 & ~1u), v1 = __uint_as_float(t1 & ~1u);
+            const bool lower = v1 > v0;
+            const float best = fmaxf((lower ? v1 : v0) + bias[o], 0.f);
+            a2[o * 49 + pos] = best;
+            i2[o * 49 + pos] = (unsigned char)(lower ? (2 + (t1 & 1u)) : (t0 & 1u));
+        }
+    }
+    __syncthreads();
+    if (warp == 2) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 128;" ::"r"(tmem) : "memory");
+}
+
+__global__ void __launch_bounds__(192) conv2_fwd_umma_debug(const float* __restrict__ a1, const __nv_bfloat16* __restrict__ w2uf,
+                                                            const float* __restrict__ bias, float* a2, unsigned char* i2) {
+    extern __shared__ __align__(128) uint8_t smem_dyn[];
+    const size_t r = blockIdx.x;
+    conv2_fwd_umma_image(a1 + r * 3136, w2uf, bias, a2 + r * 1568, i2 + r * 1568, smem_dyn);
+}
+
+// ------------------------------------------------------------------------------------------
+// data gradient: da1[c][y][x] = sum_o sum_tap g2pad[o][y+ky][x+kx] W[o][c][4-ky][4-kx]; K = 32 oc per tap
+constexpr int DGRAD_UMMA_SMEM = 4 * PLANE_BYTES + W2U_BYTES + 128;
+__device__ __forceinline__ void conv2_dgrad_umma_image(const float* __restrict__ g2, const __nv_bfloat16* __restrict__ w2ub,
+                                                       float* __restrict__ da1, uint8_t* smem) {
+    __shared__ __align__(8) uint64_t accum_bar;
+    __shared__ uint32_t tmem_slot;
+    uint8_t* planes = smem;                       // 4 half planes of g2 (32 oc)
+    uint8_t* wts = smem + 4 * PLANE_BYTES;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (warp == 1 && lane == 0) {
+        mbar_init1(&accum_bar);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 64;" ::"r"(smem_addr(&tmem_slot)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    zero_bytes16(planes, 4 * PLANE_BYTES);
+    for (int i = tid; i < W2U_BYTES / 16; i += blockDim.x) cp_async16(wts + 16 * i, reinterpret_cast<const uint8_t*>(w2ub) + 16 * i);
+    __syncthreads();
+    fill_half_planes<32>(planes, g2);
+    cp_async_wait_all();
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = tmem_slot;
+    if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = idesc_bf16(128, 16, 0, 0);
+            const uint32_t pa = smem_addr(planes), wa = smem_addr(wts);
+#pragma unroll 1
+            for (int blk = 0; blk < 4; ++blk) {
+#pragma unroll 1
+                for (int tap = 0; tap < 25; ++tap) {
+                    const int ky = tap / 5, kx = tap - ky * 5;
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) {   // K = 32 oc = two MMAs of 16 (k-chunks 2j, 2j+1)
+                        const uint64_t ad = desc_noswz(pa + (uint32_t)(2 * j) * PLANE_BYTES +
+                                                       (uint32_t)(128 * blk + ky * PITCH + kx) * 16, PLANE_BYTES, 128);
+                        const uint64_t bd = desc_noswz(wa + (uint32_t)tap * 1024 + (uint32_t)(2 * j) * 256, 256, 128);
+                        umma_bf16(tmem + 16 * blk, ad, bd, idesc, (tap | j) ? 1u : 0u);
+                    }
+                }
+            }
+            umma_commit1(&accum_bar);
+        }
+        __syncwarp();
+    } else if (warp >= 2) {
+        const int q = warp & 3;
+        mbar_wait0(&accum_bar);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll 1
+        for (int blk = 0; blk < 4; ++blk) {
+            const int y = 4 * blk + q;
+            uint32_t r[16];
+            tmem_ld<16>(tmem + ((uint32_t)(q * 32) << 16) + 16 * blk, r);
+            if (y < 14 && lane < 14) {
+#pragma unroll
+                for (int c = 0; c < 16; ++c) da1[c * 196 + y * 14 + lane] = __uint_as_float(r[c]);
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    }
+    __syncthreads();
+    if (warp == 2) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 64;" ::"r"(tmem) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------
+// weight gradient of one image: D_tap[oc, c] = sum_pixels g2[pixel, oc] * a1pad[pixel + tap shift, c].
+// Both operands are read MN-major straight from the half planes.  M is padded to 128 (16 chunks of 8 oc,
+// 4 real): chunks 4..15 alias the activation planes and a zero-filled tail, whose products land in
+// accumulator rows that are never read.
+constexpr int WG_PLANES = 16;
+constexpr int WGRAD_UMMA_SMEM = WG_PLANES * PLANE_BYTES + 128;   // 172,160 B; the fp32 staging tile reuses the tail
+__device__ __forceinline__ void conv2_wgrad_umma_image(const float* __restrict__ g2, const float* __restrict__ a1,
+                                                       float* __restrict__ part, uint8_t* smem) {
+    __shared__ __align__(8) uint64_t accum_bar;
+    __shared__ uint32_t tmem_slot;
+    uint8_t* gpl = smem;                          // planes 0..3: g2 (32 oc); 4..5: a1 (16 c); 6..15: zeros
+    uint8_t* apl = smem + 4 * PLANE_BYTES;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (warp == 1 && lane == 0) {
+        mbar_init1(&accum_bar);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_addr(&tmem_slot)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    zero_bytes16(smem, WG_PLANES * PLANE_BYTES);
+    __syncthreads();
+    fill_half_planes<32>(gpl, g2);
+    fill_half_planes<16>(apl, a1);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = tmem_slot;
+    if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = idesc_bf16(128, 16, 1, 1);
+            const uint32_t ga = smem_addr(gpl), aa = smem_addr(apl);
+            // K runs over the stored pixels 64 .. 511 (rows 2..15 of the padded g2 planes), 16 per MMA.
+            // MN-major: 16-byte channel chunks are SBO = one plane apart, 8-pixel K groups LBO = 128 B apart.
+#pragma unroll 1
+            for (int tap = 0; tap < 25; ++tap) {
+                const int ky = tap / 5, kx = tap - ky * 5;
+                const uint32_t a0 = ga + 64 * 16;
+                const uint32_t b0 = aa + (uint32_t)(64 - 66 + ky * PITCH + kx) * 16;   // may start 2 pixels before the plane: g2 is zero there
+#pragma unroll 1
+                for (int kk = 0; kk < 28; ++kk) {
+                    const uint64_t ad = desc_noswz(a0 + kk * 256, 128, PLANE_BYTES);
+                    const uint64_t bd = desc_noswz(b0 + kk * 256, 128, PLANE_BYTES);
+                    umma_bf16(tmem + 16 * tap, ad, bd, idesc, kk ? 1u : 0u);
+                }
+            }
+            umma_commit1(&accum_bar);
+        }
+        __syncwarp();
+    } else if (warp == 4) {   // rows 0..31 (the real oc) live in TMEM lane quarter 0 = warps with id % 4 == 0
+        mbar_wait0(&accum_bar);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        float* stage = reinterpret_cast<float*>(smem + 6 * PLANE_BYTES);   // [32 oc][401] fp32 = 51 KB over the zero tail
+#pragma unroll 1
+        for (int tap = 0; tap < 25; ++tap) {
+            uint32_t r[16];
+            tmem_ld<16>(tmem + 16 * tap, r);
+#pragma unroll
+            for (int c = 0; c < 16; ++c) stage[lane * 401 + c * 25 + tap] = __uint_as_float(r[c]);
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    } else if (warp == 0) {   // conv2 bias gradient in fp32 from the dense g2
+        float sum = 0.f;
+        for (int i = 0; i < 196; ++i) sum += __ldg(g2 + lane * 196 + i);
+        part[C2B + lane] = sum;
+    }
+    __syncthreads();
+    {
+        const float* stage = reinterpret_cast<const float*>(smem + 6 * PLANE_BYTES);
+        for (int e = tid; e < 12800; e += blockDim.x) part[C2W + e] = stage[(e / 400) * 401 + (e % 400)];
+    }
+    if (warp == 2) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+}
+
+__global__ void __launch_bounds__(192) conv2_dgrad_umma_debug(const float* __restrict__ g2, const __nv_bfloat16* __restrict__ w2ub,
+                                                              float* da1) {
+    extern __shared__ __align__(128) uint8_t smem_dyn[];
+    const size_t r = blockIdx.x;
+    conv2_dgrad_umma_image(g2 + r * 32 * 196, w2ub, da1 + r * 3136, smem_dyn);
+}
+__global__ void __launch_bounds__(192) conv2_wgrad_umma_debug(const float* __restrict__ g2, const float* __restrict__ a1,
+                                                              float* part) {
+    extern __shared__ __align__(128) uint8_t smem_dyn[];
+    const size_t r = blockIdx.x;
+    conv2_wgrad_umma_image(g2 + r * 32 * 196, a1 + r * 3136, part + r * NCONV, smem_dyn);
+}
+
+}  // namespace cnn
+}  // namespace qfx
+
+using namespace qfx;
+using namespace qfx::cnn;
+
+// Debug / test entry: conv2 forward (+bias, ReLU, pool) of n images with the tcgen05 kernel.
+// a1 [n,16,14,14] fp32, weights [32,16,5,5] fp32, bias [32]; a2 [n,32,7,7], i2 [n,32,7,7] u8;
+// scratch: 51,200 bytes for the operand-layout weight copies.
+extern "C" int qfx_tinycnn_conv2_fwd_umma(const float* a1, const float* weight, const float* bias, int n, float* a2,
+                                          unsigned char* i2, void* scratch, cudaStream_t stream) {
+    QFX_ARG_CHECK(n >= 1 && a1 && weight && bias && a2 && i2 && scratch, QFX_ERR_BAD_ARG, "bad arguments");
+    __nv_bfloat16* w2uf = (__nv_bfloat16*)scratch;
+    __nv_bfloat16* w2ub = w2uf + 12800;
+    // weight points at a bare [32,16,5,5] tensor: use nd = 0 and shift the base so that C2W + i lands on it
+    conv2_weight_prep_umma<<<dim3(50, 1), 256, 0, stream>>>(weight - C2W, 0, w2uf, w2ub);
+    QFX_CUDA_TRY(cudaFuncSetAttribute(conv2_fwd_umma_debug, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM));
+    conv2_fwd_umma_debug<<<n, 192, FWD_SMEM, stream>>>(a1, w2uf, bias, a2, i2);
+    return check_launch("conv2_fwd_umma");
+}
+
+// Debug / test entries for the backward kernels.  g2 [n,32,14,14] (gradient w.r.t. the conv2 output before
+// pooling), a1 [n,16,14,14]; da1 [n,16,14,14]; part [n,13248] per-image partials (conv2 weight gradient at
+// offset 416 in [o][c][tap] order, conv2 bias gradient at 13216).
+extern "C" int qfx_tinycnn_conv2_dgrad_umma(const float* g2, const float* weight, int n, float* da1, void* scratch,
+                                            cudaStream_t stream) {
+    QFX_ARG_CHECK(n >= 1 && g2 && weight && da1 && scratch, QFX_ERR_BAD_ARG, "bad arguments");
+    __nv_bfloat16* w2uf = (__nv_bfloat16*)scratch;
+    __nv_bfloat16* w2ub = w2uf + 12800;
+    conv2_weight_prep_umma<<<dim3(50, 1), 256, 0, stream>>>(weight - C2W, 0, w2uf, w2ub);
+    QFX_CUDA_TRY(cudaFuncSetAttribute(conv2_dgrad_umma_debug, cudaFuncAttributeMaxDynamicSharedMemorySize, DGRAD_UMMA_SMEM));
+    conv2_dgrad_umma_debug<<<n, 192, DGRAD_UMMA_SMEM, stream>>>(g2, w2ub, da1);
+    return check_launch("conv2_dgrad_umma");
+}
+
+extern "C" int qfx_tinycnn_conv2_wgrad_umma(const float* g2, const float* a1, int n, float* part, cudaStream_t stream) {
+    QFX_ARG_CHECK(n >= 1 && g2 && a1 && part, QFX_ERR_BAD_ARG, "bad arguments");
+    QFX_CUDA_TRY(cudaFuncSetAttribute(conv2_wgrad_umma_debug, cudaFuncAttributeMaxDynamicSharedMemorySize, WGRAD_UMMA_SMEM));
+    conv2_wgrad_umma_debug<<<n, 192, WGRAD_UMMA_SMEM, stream>>>(g2, a1, part);
+    return check_launch("conv2_wgrad_umma");
+}

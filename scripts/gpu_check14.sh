@@ -1,0 +1,7 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_gpu_tinycnn.py -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/pytest_gpu.log | cut -c1-300
+for k in 1 2 8; do
+QFX_BENCH_CLIENTS=$k timeout 600 python bench.py --config cfed --steps 4 --warmup 3 --no-aux > gpurun_out/bench_cfed_k$k.log 2>&1; echo "K=$k rc=$?"; python -c "
+import json; d=json.loads(open('gpurun_out/bench_cfed_k$k.log').read().strip().splitlines()[-1]); print(d['ms_per_step'], d['value'], d['e2e']['value'], d['final_eval'])"
+done
