@@ -229,7 +229,8 @@ def run_cfed(cfg, args, rank, world, local):
                 model="TinyCNN (113,859 params) FedAvg + DP clip/noise", clients=len(clients),
                 samples=int(all_sizes.sum()), eval=result.get("eval"),
                 extra={"local_epochs": cfg["epochs"], "batch": cfg["batch"], "optimizer": "sgd(0.01, m=0.9)",
-                       "dp": {"clip": cfg["clip"], "sigma": cfg["sigma"]}})
+                       "dp": {"clip": cfg["clip"], "sigma": cfg["sigma"]},
+                       "precision": "conv2 on tcgen05 with bf16 operands + fp32 accumulate; fp32 master weights and other layers"})
 
 
 # --------------------------------------------------------------------------------------------
@@ -335,7 +336,8 @@ def main():
         line = {
             "metric": "fl_rounds_per_sec", "value": value, "unit": "rounds/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms"], "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "fp32",
+            "scaling": "strong", "vs_baseline": None,
+            "dtype": "bf16" if (args.config == "cfed" and args.impl == "ours") else "fp32",
             "data": "synthetic MNIST-shape images, random-init weights",
             "impl": args.impl,
             "config": {"name": args.config, "model": r["model"], "clients": r["clients"], "global_batch": r["samples"],

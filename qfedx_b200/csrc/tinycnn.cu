@@ -480,7 +480,10 @@ __global__ void __launch_bounds__(416) conv1_wgrad_train(const Step s) {
     const int sel = blockIdx.y, b = blockIdx.x, tid = threadIdx.x;
     int lo;
     const int nb = batch_rows(s, sel, &lo);
-    if (b >= nb) return;  // conv_part rows of absent images were zeroed by conv2_wgrad_train
+    if (b >= nb) {  // absent image: its row of conv1 partials must read as zero in sgd_conv_train
+        if (nb > 0) s.conv_part[((size_t)sel * BS + b) * NCONV + C1W + tid] = 0.f;   // 416 threads = 400 weights + 16 biases
+        return;
+    }
     const size_t row = (size_t)sel * BS + b;
     const float* img = s.X + (size_t)sample_index(s, lo, b) * 784;
     for (int i = tid; i < 32 * XS1; i += 416) xs[i] = 0.f;
@@ -536,8 +539,10 @@ __global__ void __launch_bounds__(256) sgd_conv_train(const Step s) {
     if (batch_rows(s, sel, &lo) <= 0 || p >= NCONV) return;
     const float* part = s.conv_part + (size_t)sel * BS * NCONV + p;
     float g = 0.f;
+    // conv1 partials always have one row per image; conv2 partials have BS / wgrad_ipc rows
+    const int rows = (p >= C2W && s.conv2_mode == 1) ? BS / s.wgrad_ipc : BS;
 #pragma unroll 8
-    for (int b = 0; b < BS; ++b) g += part[(size_t)b * NCONV];
+    for (int b = 0; b < rows; ++b) g += part[(size_t)b * NCONV];
     float* prm = s.params + (size_t)sel * s.nd;
     float* mom = s.moment + (size_t)sel * s.nd;
     const float m = s.momentum * mom[p] + g;
@@ -548,6 +553,7 @@ __global__ void __launch_bounds__(256) sgd_conv_train(const Step s) {
         const int i = p - C2W, o = i / 400, rem = i - o * 400, c = rem / 25, tap = rem - c * 25;
         s.w2f[(size_t)sel * 12800 + rem * 32 + o] = w;
         s.w2b[(size_t)sel * 12800 + (o * 25 + (24 - tap)) * 16 + c] = w;
+        if (s.conv2_mode == 1) store_w2u(s.w2uf + (size_t)sel * 12800, s.w2ub + (size_t)sel * 12800, o, c, tap, w);
     }
 }
 
@@ -625,7 +631,7 @@ extern "C" int qfx_tinycnn_workspace_bytes(int n_selected, size_t* bytes) {
     auto add = [&](size_t n) { tot += (n + 255) & ~(size_t)255; };
     add(K * BS * 3136 * 4); add(K * BS * 3136); add(K * BS * 1568 * 4); add(K * BS * 1568);
     add(K * FC1_SLICES * BS * 64 * 4); add(K * BS * 64 * 4); add(K * BS * 64 * 4);
-    add(K * BS * 32 * 196 * 4); add(K * BS * 3136 * 4); add(K * BS * NCONV * 4); add(K * 12800 * 4); add(K * 12800 * 4);
+    add(K * BS * 32 * 196 * 4); add(K * BS * 3136 * 4); add(K * BS * NCONV * 4); add(K * 12800 * 4); add(K * 12800 * 4); add(K * 12800 * 2); add(K * 12800 * 2);
     add(K * 2 * 4);
     *bytes = tot;
     return 0;
@@ -640,7 +646,9 @@ static void carve(Step& s, void* workspace, size_t K) {
     s.h1 = (float*)take(K * BS * 64 * 4); s.dh1 = (float*)take(K * BS * 64 * 4);
     s.g2 = (float*)take(K * BS * 32 * 196 * 4); s.da1 = (float*)take(K * BS * 3136 * 4);
     s.conv_part = (float*)take(K * BS * NCONV * 4);
-    s.w2f = (float*)take(K * 12800 * 4); s.w2b = (float*)take(K * 12800 * 4); s.stats = (float*)take(K * 2 * 4);
+    s.w2f = (float*)take(K * 12800 * 4); s.w2b = (float*)take(K * 12800 * 4);
+    s.w2uf = (__nv_bfloat16*)take(K * 12800 * 2); s.w2ub = (__nv_bfloat16*)take(K * 12800 * 2);
+    s.stats = (float*)take(K * 2 * 4);
 }
 
 // Call once per round after the global parameters were broadcast into `params`: builds the
@@ -651,7 +659,8 @@ extern "C" int qfx_tinycnn_begin_round(const float* params, int nd, int n_select
     Step s;
     carve(s, workspace, (size_t)n_selected);
     conv2_weight_prep<<<dim3(50, n_selected), 256, 0, stream>>>(params, nd, s.w2f, s.w2b);
-    return check_launch("conv2_weight_prep");
+    if (int e = check_launch("conv2_weight_prep")) return e;
+    return launch_conv2_umma_prep(params, nd, n_selected, s.w2uf, s.w2ub, stream);
 }
 
 // One SGD step for every selected client: 9 kernels on `stream` (capture them in a CUDA graph).
@@ -661,7 +670,9 @@ extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const i
                                       int n_total, const int* client_ids, int n_selected, int epoch,
                                       int batch_index, int batch_size, float* params, float* moment, int nd,
                                       int n_classes, float lr, float momentum, float p_drop,
-                                      unsigned long long seed, int round, void* workspace, cudaStream_t stream) {
+                                      unsigned long long seed, int round, void* workspace, int conv2_mode,
+                                      cudaStream_t stream) {
+    QFX_ARG_CHECK(conv2_mode == 0 || conv2_mode == 1, QFX_ERR_BAD_ARG, "conv2_mode must be 0 (fp32) or 1 (tcgen05 bf16)");
     QFX_ARG_CHECK(batch_size >= 1 && batch_size <= BS, QFX_ERR_UNSUPPORTED,
                   "client-batched TinyCNN supports batch_size <= %d, got %d", BS, batch_size);
     QFX_ARG_CHECK(n_classes >= 2 && n_classes <= MAX_CLASSES, QFX_ERR_UNSUPPORTED, "n_classes %d not in 2..10", n_classes);
@@ -672,19 +683,27 @@ extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const i
     s.X = X; s.labels = labels; s.offsets = offsets; s.perm = perm; s.client_ids = client_ids;
     s.n_total = n_total; s.epoch = epoch; s.batch_index = batch_index; s.batch_size = batch_size;
     s.params = params; s.moment = moment; s.nd = nd; s.n_classes = n_classes;
-    s.lr = lr; s.momentum = momentum; s.p_drop = p_drop; s.seed = seed; s.round = round;
+    s.lr = lr; s.momentum = momentum; s.p_drop = p_drop; s.seed = seed; s.round = round; s.conv2_mode = conv2_mode;
+    // many clients: two images per weight-gradient CTA (one wave of CTAs, half the partial sums)
+    s.wgrad_ipc = (conv2_mode == 1 && n_selected >= 5) ? 2 : 1;
     carve(s, workspace, (size_t)n_selected);
     const dim3 gimg(batch_size, n_selected);
     // few clients -> few CTAs: spread the channel groups of the conv2 kernels over up to 4 CTAs per image
     s.split = n_selected >= 4 ? 1 : (n_selected >= 2 ? 2 : 4);
     const dim3 gsplit(batch_size, n_selected, s.split);
     conv1_fwd_train<<<gimg, 224, 0, stream>>>(s);
-    conv2_fwd_train<<<gsplit, 256 / s.split, CONV2_SMEM, stream>>>(s);
+    if (conv2_mode == 1) { if (int e = launch_conv2_umma_fwd(s, n_selected, stream)) return e; }
+    else conv2_fwd_train<<<gsplit, 256 / s.split, CONV2_SMEM, stream>>>(s);
     fc1_fwd_train<<<dim3(FC1_SLICES, n_selected), 128, 0, stream>>>(s);
     head_train<<<n_selected, 256, 0, stream>>>(s);
     fc1_bwd_train<<<dim3(49, n_selected), 256, 0, stream>>>(s);
-    conv2_dgrad_train<<<gsplit, 256 / s.split, DGRAD_SMEM, stream>>>(s);
-    conv2_wgrad_train<<<dim3(BS, n_selected, s.split), 320 / s.split, WGRAD_SMEM, stream>>>(s);
+    if (conv2_mode == 1) {
+        if (int e = launch_conv2_umma_dgrad(s, n_selected, stream)) return e;
+        if (int e = launch_conv2_umma_wgrad(s, n_selected, stream)) return e;
+    } else {
+        conv2_dgrad_train<<<gsplit, 256 / s.split, DGRAD_SMEM, stream>>>(s);
+        conv2_wgrad_train<<<dim3(BS, n_selected, s.split), 320 / s.split, WGRAD_SMEM, stream>>>(s);
+    }
     conv1_wgrad_train<<<gimg, 416, 0, stream>>>(s);
     sgd_conv_train<<<dim3((NCONV + 255) / 256, n_selected), 256, 0, stream>>>(s);
     return check_launch("tinycnn_train_step");

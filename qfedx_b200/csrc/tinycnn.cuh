@@ -1,6 +1,7 @@
 // Shared definitions of the client-batched TinyCNN kernels (tinycnn.cu: fp32 CUDA-core kernels,
 // tinycnn_umma.cu: tcgen05 implicit-GEMM conv2 kernels).
 #pragma once
+#include <cuda_bf16.h>
 #include "common.cuh"
 
 namespace qfx {
@@ -39,6 +40,10 @@ struct Step {
     float* conv_part;                // [K,32,NCONV]
     float* w2f;                      // [K,12800] conv2 weights as [c][tap][o]      (forward operand)
     float* w2b;                      // [K,12800] conv2 weights as [o][24-tap][c]   (data-gradient operand)
+    __nv_bfloat16* w2uf;             // [K,12800] bf16 UMMA forward operand  [tap][c/8][oc/8][oc%8][c%8]
+    __nv_bfloat16* w2ub;             // [K,12800] bf16 UMMA dgrad operand    [24-tap][oc/8][c/8][c%8][oc%8]
+    int conv2_mode;                  // 0: fp32 CUDA-core conv2 kernels, 1: tcgen05 bf16 implicit-GEMM kernels
+    int wgrad_ipc;                   // tcgen05 weight gradient: images accumulated per CTA; conv_part then has BS / ipc rows
     float* stats;                    // [K,2] running loss sum / correct count of the epoch
 };
 
@@ -81,6 +86,22 @@ __device__ __forceinline__ int sample_index(const Step& s, int seg_lo, int b) {
     return s.perm ? s.perm[(size_t)s.epoch * s.n_total + seg_lo + j] : seg_lo + j;
 }
 
+
+// operand copies of the conv2 weights in UMMA layouts (bf16), kept current by the SGD kernel:
+//   w2uf (forward):  [tap][k-chunk h (2)][oc group (4)][8 oc][8 c]     B is [N = oc][K = c], K-major
+//   w2ub (dgrad):    [24-tap][k-chunk h (4)][c group (2)][8 c][8 oc]   B is [N = c][K = oc], K-major
+__device__ __forceinline__ void store_w2u(__nv_bfloat16* w2uf, __nv_bfloat16* w2ub, int o, int c, int tap, float v) {
+    const __nv_bfloat16 bv = __float2bfloat16_rn(v);
+    w2uf[(((tap * 2 + (c >> 3)) * 4 + (o >> 3)) * 8 + (o & 7)) * 8 + (c & 7)] = bv;
+    w2ub[((((24 - tap) * 4 + (o >> 3)) * 2 + (c >> 3)) * 8 + (c & 7)) * 8 + (o & 7)] = bv;
+}
+
+// tcgen05 conv2 kernels for the training step (tinycnn_umma.cu)
+int launch_conv2_umma_prep(const float* params, int nd, int n_selected, __nv_bfloat16* w2uf, __nv_bfloat16* w2ub,
+                           cudaStream_t stream);
+int launch_conv2_umma_fwd(const Step& s, int n_selected, cudaStream_t stream);
+int launch_conv2_umma_dgrad(const Step& s, int n_selected, cudaStream_t stream);
+int launch_conv2_umma_wgrad(const Step& s, int n_selected, cudaStream_t stream);
 
 }  // namespace cnn
 }  // namespace qfx

@@ -65,6 +65,17 @@ __device__ __forceinline__ void mbar_wait0(uint64_t* bar) {
         "CW_DONE:\n"
         "}\n" ::"r"(smem_addr(bar)) : "memory");
 }
+__device__ __forceinline__ void mbar_wait_parity(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "CP_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra CP_DONE;\n"
+        "bra CP_LOOP;\n"
+        "CP_DONE:\n"
+        "}\n" ::"r"(smem_addr(bar)), "r"(parity) : "memory");
+}
 __device__ __forceinline__ void umma_commit1(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_addr(bar)) : "memory");
 }
@@ -103,13 +114,26 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 // The planes must have been zero-filled before.  One item = (pixel, half plane): 8 channel values.
 template <int C>
 __device__ __forceinline__ void fill_half_planes(uint8_t* planes, const float* __restrict__ src) {
-    for (int it = threadIdx.x; it < 196 * (C / 8); it += blockDim.x) {
-        const int h = it / 196, pix = it - h * 196, y = pix / 14, x = pix - y * 14;
-        float v[8];
+    constexpr int ITEMS = 196 * (C / 8);
+    for (int it0 = threadIdx.x; it0 < ITEMS; it0 += 2 * blockDim.x) {
+        float v[2][8];
+        int dst[2];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = __ldg(src + (8 * h + j) * 196 + pix);
-        uint4 packed = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
-        *reinterpret_cast<uint4*>(planes + (size_t)h * PLANE_BYTES + ((y + 2) * PITCH + x + 2) * 16) = packed;
+        for (int u = 0; u < 2; ++u) {   // issue both items' loads before converting: two L2 latencies overlap
+            const int it = it0 + u * blockDim.x;
+            dst[u] = -1;
+            if (it < ITEMS) {
+                const int h = it / 196, pix = it - h * 196, y = pix / 14, x = pix - y * 14;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[u][j] = __ldg(src + (8 * h + j) * 196 + pix);
+                dst[u] = h * PLANE_BYTES + ((y + 2) * PITCH + x + 2) * 16;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u)
+            if (dst[u] >= 0)
+                *reinterpret_cast<uint4*>(planes + dst[u]) = make_uint4(pack_bf16(v[u][0], v[u][1]), pack_bf16(v[u][2], v[u][3]),
+                                                                        pack_bf16(v[u][4], v[u][5]), pack_bf16(v[u][6], v[u][7]));
     }
 }
 __device__ __forceinline__ void zero_bytes16(uint8_t* p, int bytes) {
@@ -117,14 +141,6 @@ __device__ __forceinline__ void zero_bytes16(uint8_t* p, int bytes) {
 }
 
 // ------------------------------------------------------------------------------------------
-// operand copies of the conv2 weights in UMMA layouts (bf16), kept current by the SGD kernel:
-//   w2uf (forward):  [tap][k-chunk h (2)][oc group (4)][8 oc][8 c]     B is [N = oc][K = c], K-major
-//   w2ub (dgrad):    [24-tap][k-chunk h (4)][c group (2)][8 c][8 oc]   B is [N = c][K = oc], K-major
-__device__ __forceinline__ void store_w2u(__nv_bfloat16* w2uf, __nv_bfloat16* w2ub, int o, int c, int tap, float v) {
-    const __nv_bfloat16 bv = __float2bfloat16_rn(v);
-    w2uf[(((tap * 2 + (c >> 3)) * 4 + (o >> 3)) * 8 + (o & 7)) * 8 + (c & 7)] = bv;
-    w2ub[((((24 - tap) * 4 + (o >> 3)) * 2 + (c >> 3)) * 8 + (c & 7)) * 8 + (o & 7)] = bv;
-}
 __global__ void __launch_bounds__(256) conv2_weight_prep_umma(const float* __restrict__ params, int nd, __nv_bfloat16* w2uf,
                                                               __nv_bfloat16* w2ub) {
     const int sel = blockIdx.y, i = blockIdx.x * 256 + threadIdx.x;
@@ -311,7 +327,7 @@ __device__ __forceinline__ void conv2_dgrad_umma_image(const float* __restrict__
 constexpr int WG_PLANES = 16;
 constexpr int WGRAD_UMMA_SMEM = WG_PLANES * PLANE_BYTES + 128;   // 172,160 B; the fp32 staging tile reuses the tail
 __device__ __forceinline__ void conv2_wgrad_umma_image(const float* __restrict__ g2, const float* __restrict__ a1,
-                                                       float* __restrict__ part, uint8_t* smem) {
+                                                       float* __restrict__ part, uint8_t* smem, int n_img) {
     __shared__ __align__(8) uint64_t accum_bar;
     __shared__ uint32_t tmem_slot;
     uint8_t* gpl = smem;                          // planes 0..3: g2 (32 oc); 4..5: a1 (16 c); 6..15: zeros
@@ -326,51 +342,67 @@ __device__ __forceinline__ void conv2_wgrad_umma_image(const float* __restrict__
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     zero_bytes16(smem, WG_PLANES * PLANE_BYTES);
-    __syncthreads();
-    fill_half_planes<32>(gpl, g2);
-    fill_half_planes<16>(apl, a1);
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem = tmem_slot;
-    if (warp == 1) {
-        if (lane == 0) {
-            constexpr uint32_t idesc = idesc_bf16(128, 16, 1, 1);
+    float bias_acc = 0.f;
+    uint32_t tmem = 0;
+#pragma unroll 1
+    for (int img = 0; img < n_img; ++img) {
+        // the previous image's MMAs must have consumed the planes before they are overwritten
+        if (img > 0) { mbar_wait_parity(&accum_bar, (img - 1) & 1); }
+        __syncthreads();
+        fill_half_planes<32>(gpl, g2 + (size_t)img * 32 * 196);
+        fill_half_planes<16>(apl, a1 + (size_t)img * 3136);
+        if (warp == 0) for (int i = 0; i < 196; ++i) bias_acc += __ldg(g2 + (size_t)img * 32 * 196 + lane * 196 + i);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        tmem = tmem_slot;
+        if (warp == 1 && lane == 0) {
+            // One MMA covers all five kx taps of a filter row: the B operand is read MN-major with its
+            // 16-byte N chunks only ONE PIXEL (16 B) apart, so N chunk j is the activation shifted by j pixels.
+            // N = 48 = 6 shifts x 8 channels of half plane h (the 6th shift is padding to a multiple of 16).
+            constexpr uint32_t idesc = idesc_bf16(128, 48, 1, 1);
             const uint32_t ga = smem_addr(gpl), aa = smem_addr(apl);
-            // K runs over the stored pixels 64 .. 511 (rows 2..15 of the padded g2 planes), 16 per MMA.
-            // MN-major: 16-byte channel chunks are SBO = one plane apart, 8-pixel K groups LBO = 128 B apart.
+            // K runs over the stored pixels 64 .. 511 (rows 2..15 of the padded g2 planes), 16 per MMA;
+            // 8-pixel K groups are LBO = 128 B apart.  A: 16-byte oc chunks are SBO = one plane apart.
+            const uint64_t a_hi = desc_noswz(0, 128, PLANE_BYTES) >> 32, b_hi = desc_noswz(0, 128, 16) >> 32;
+            const uint32_t lbo_lo = (uint32_t)((128u >> 4) << 16);
 #pragma unroll 1
-            for (int tap = 0; tap < 25; ++tap) {
-                const int ky = tap / 5, kx = tap - ky * 5;
-                const uint32_t a0 = ga + 64 * 16;
-                const uint32_t b0 = aa + (uint32_t)(64 - 66 + ky * PITCH + kx) * 16;   // may start 2 pixels before the plane: g2 is zero there
-#pragma unroll 1
+            for (int kyh = 0; kyh < 10; ++kyh) {
+                const int ky = kyh >> 1, h = kyh & 1;
+                uint32_t a_lo = (((ga + 64 * 16) >> 4) & 0x3FFF) | lbo_lo;
+                // may start 2 pixels before the plane: g2 is zero for those K rows
+                uint32_t b_lo = (((aa + (uint32_t)h * PLANE_BYTES + (uint32_t)(64 - 66 + ky * PITCH) * 16) >> 4) & 0x3FFF) | lbo_lo;
+#pragma unroll 4
                 for (int kk = 0; kk < 28; ++kk) {
-                    const uint64_t ad = desc_noswz(a0 + kk * 256, 128, PLANE_BYTES);
-                    const uint64_t bd = desc_noswz(b0 + kk * 256, 128, PLANE_BYTES);
-                    umma_bf16(tmem + 16 * tap, ad, bd, idesc, kk ? 1u : 0u);
+                    umma_bf16(tmem + 48 * kyh, (a_hi << 32) | a_lo, (b_hi << 32) | b_lo, idesc, (img | kk) ? 1u : 0u);
+                    a_lo += 16; b_lo += 16;   // 16 pixels = 256 B
                 }
             }
             umma_commit1(&accum_bar);
         }
-        __syncwarp();
-    } else if (warp == 4) {   // rows 0..31 (the real oc) live in TMEM lane quarter 0 = warps with id % 4 == 0
-        mbar_wait0(&accum_bar);
+    }
+    if (warp == 4) {   // rows 0..31 (the real oc) live in TMEM lane quarter 0 = warps with id % 4 == 0
+        mbar_wait_parity(&accum_bar, (n_img - 1) & 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         float* stage = reinterpret_cast<float*>(smem + 6 * PLANE_BYTES);   // [32 oc][401] fp32 = 51 KB over the zero tail
 #pragma unroll 1
-        for (int tap = 0; tap < 25; ++tap) {
-            uint32_t r[16];
-            tmem_ld<16>(tmem + 16 * tap, r);
+        for (int kyh = 0; kyh < 10; ++kyh) {
+            const int ky = kyh >> 1, h = kyh & 1;
+#pragma unroll 1
+            for (int part3 = 0; part3 < 3; ++part3) {          // 48 columns = 3 loads of 16 = shifts (2 part3, 2 part3 + 1)
+                uint32_t r[16];
+                tmem_ld<16>(tmem + 48 * kyh + 16 * part3, r);
 #pragma unroll
-            for (int c = 0; c < 16; ++c) stage[lane * 401 + c * 25 + tap] = __uint_as_float(r[c]);
+                for (int j = 0; j < 16; ++j) {
+                    const int kx = 2 * part3 + (j >> 3), c = 8 * h + (j & 7);
+                    if (kx < 5) stage[lane * 401 + c * 25 + ky * 5 + kx] = __uint_as_float(r[j]);
+                }
+            }
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     } else if (warp == 0) {   // conv2 bias gradient in fp32 from the dense g2
-        float sum = 0.f;
-        for (int i = 0; i < 196; ++i) sum += __ldg(g2 + lane * 196 + i);
-        part[C2B + lane] = sum;
+        part[C2B + lane] = bias_acc;
     }
     __syncthreads();
     {
@@ -390,7 +422,70 @@ __global__ void __launch_bounds__(192) conv2_wgrad_umma_debug(const float* __res
                                                               float* part) {
     extern __shared__ __align__(128) uint8_t smem_dyn[];
     const size_t r = blockIdx.x;
-    conv2_wgrad_umma_image(g2 + r * 32 * 196, a1 + r * 3136, part + r * NCONV, smem_dyn);
+    conv2_wgrad_umma_image(g2 + r * 32 * 196, a1 + r * 3136, part + r * NCONV, smem_dyn, 1);
+}
+
+// ------------------------------------------------------------------------------------------
+// training-step wrappers: grid (image, client)
+__global__ void __launch_bounds__(192) conv2_fwd_umma_train(const Step s) {
+    extern __shared__ __align__(128) uint8_t smem_dyn[];
+    const int sel = blockIdx.y, b = blockIdx.x;
+    int lo;
+    if (b >= batch_rows(s, sel, &lo)) return;
+    const size_t r = (size_t)sel * BS + b;
+    conv2_fwd_umma_image(s.a1 + r * 3136, s.w2uf + (size_t)sel * 12800, s.params + (size_t)sel * s.nd + C2B,
+                         s.a2 + r * 1568, s.i2 + r * 1568, smem_dyn);
+}
+__global__ void __launch_bounds__(192) conv2_dgrad_umma_train(const Step s) {
+    extern __shared__ __align__(128) uint8_t smem_dyn[];
+    const int sel = blockIdx.y, b = blockIdx.x;
+    int lo;
+    if (b >= batch_rows(s, sel, &lo)) return;
+    const size_t r = (size_t)sel * BS + b;
+    conv2_dgrad_umma_image(s.g2 + r * 32 * 196, s.w2ub + (size_t)sel * 12800, s.da1 + r * 3136, smem_dyn);
+}
+__global__ void __launch_bounds__(192) conv2_wgrad_umma_train(const Step s) {
+    extern __shared__ __align__(128) uint8_t smem_dyn[];
+    const int sel = blockIdx.y, ipc = s.wgrad_ipc, b0 = blockIdx.x * ipc;   // this CTA sums images b0 .. b0+ipc-1
+    int lo;
+    const int nb = batch_rows(s, sel, &lo);
+    float* part = s.conv_part + ((size_t)sel * BS + blockIdx.x) * NCONV;
+    if (b0 >= nb) {  // absent images contribute zeros to the reduction in sgd_conv_train
+        if (nb > 0) for (int i = threadIdx.x; i < NCONV; i += blockDim.x) part[i] = 0.f;
+        return;
+    }
+    const size_t r = (size_t)sel * BS + b0;
+    conv2_wgrad_umma_image(s.g2 + r * 32 * 196, s.a1 + r * 3136, part, smem_dyn, min(ipc, nb - b0));
+}
+
+static bool g_umma_attr = false;
+static int umma_attrs() {
+    if (g_umma_attr) return 0;
+    QFX_CUDA_TRY(cudaFuncSetAttribute(conv2_fwd_umma_train, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM));
+    QFX_CUDA_TRY(cudaFuncSetAttribute(conv2_dgrad_umma_train, cudaFuncAttributeMaxDynamicSharedMemorySize, DGRAD_UMMA_SMEM));
+    QFX_CUDA_TRY(cudaFuncSetAttribute(conv2_wgrad_umma_train, cudaFuncAttributeMaxDynamicSharedMemorySize, WGRAD_UMMA_SMEM));
+    g_umma_attr = true;
+    return 0;
+}
+int launch_conv2_umma_prep(const float* params, int nd, int n_selected, __nv_bfloat16* w2uf, __nv_bfloat16* w2ub,
+                           cudaStream_t stream) {
+    conv2_weight_prep_umma<<<dim3(50, n_selected), 256, 0, stream>>>(params, nd, w2uf, w2ub);
+    return check_launch("conv2_weight_prep_umma");
+}
+int launch_conv2_umma_fwd(const Step& s, int n_selected, cudaStream_t stream) {
+    if (int e = umma_attrs()) return e;
+    conv2_fwd_umma_train<<<dim3(s.batch_size, n_selected), 192, FWD_SMEM, stream>>>(s);
+    return check_launch("conv2_fwd_umma_train");
+}
+int launch_conv2_umma_dgrad(const Step& s, int n_selected, cudaStream_t stream) {
+    if (int e = umma_attrs()) return e;
+    conv2_dgrad_umma_train<<<dim3(s.batch_size, n_selected), 192, DGRAD_UMMA_SMEM, stream>>>(s);
+    return check_launch("conv2_dgrad_umma_train");
+}
+int launch_conv2_umma_wgrad(const Step& s, int n_selected, cudaStream_t stream) {
+    if (int e = umma_attrs()) return e;
+    conv2_wgrad_umma_train<<<dim3(BS / s.wgrad_ipc, n_selected), 192, WGRAD_UMMA_SMEM, stream>>>(s);
+    return check_launch("conv2_wgrad_umma_train");
 }
 
 }  // namespace cnn

@@ -22,7 +22,7 @@ KERNELS_PER_STEP = 9
 class TinyCNNBatchedTrainer:
     def __init__(self, model: TinyCNN, data: FederatedDataset, epochs: int = 5, batch_size: int = 32,
                  lr: float = 0.01, momentum: float = 0.9, p_drop: float = 0.5, shuffle: bool = True, seed: int = 0,
-                 use_graph: bool = True, generator=None):
+                 use_graph: bool = True, generator=None, conv2: str = "tcgen05"):
         if data.device.type != "cuda":
             raise _lib.QfxError("TinyCNNBatchedTrainer runs on CUDA only; use TorchLocalTrainer on CPU")
         if batch_size > 32:
@@ -31,6 +31,7 @@ class TinyCNNBatchedTrainer:
         self.epochs, self.batch_size, self.lr, self.momentum, self.p_drop = epochs, batch_size, lr, momentum, p_drop
         self.shuffle, self.seed, self.use_graph, self.generator = shuffle, seed, use_graph, generator
         self.n_classes = model.num_classes
+        self.conv2_mode = {"fp32": 0, "tcgen05": 1}[conv2]   # tcgen05: bf16 operands, fp32 accumulate
         self.n_wrap = 0
         self._template = {k: v.detach().clone() for k, v in model.state_dict().items()}
         self.dim = sum(v.numel() for v in self._template.values())
@@ -105,7 +106,7 @@ class TinyCNNBatchedTrainer:
                           _lib.ptr(st["params"]), _lib.ptr(st["moment"]), _lib.c_int(self.nd),
                           _lib.c_int(self.n_classes), _lib.c_float(self.lr), _lib.c_float(self.momentum),
                           _lib.c_float(self.p_drop), _lib.c_u64(self.seed), _lib.c_int(rnd), _lib.ptr(st["ws"]),
-                          _lib.stream_ptr(), launches=KERNELS_PER_STEP)
+                          _lib.c_int(self.conv2_mode), _lib.stream_ptr(), launches=KERNELS_PER_STEP)
 
     def train(self, global_flat: torch.Tensor, selected, rnd: int):
         sel = [int(k) for k in selected]

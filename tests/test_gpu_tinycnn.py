@@ -36,9 +36,10 @@ def _torch_reference(model, flat0, clients, epochs, bs, lr, mom):
     return torch.stack(rows)
 
 
+@pytest.mark.parametrize("conv2", ["fp32", "tcgen05"])
 @pytest.mark.parametrize("sizes", [[70, 45, 32], [50], [33, 64, 40, 32, 41]])   # 1 / 3 / 5 clients: every conv2 split
 @pytest.mark.parametrize("use_graph", [False, True])
-def test_training_matches_eager_torch(use_graph, sizes):
+def test_training_matches_eager_torch(use_graph, sizes, conv2):
     from qfedx_b200.fl.trainers_cnn import TinyCNNBatchedTrainer
     torch.manual_seed(0)
     clients = _clients(sizes)
@@ -46,13 +47,14 @@ def test_training_matches_eager_torch(use_graph, sizes):
     flat0 = flatten_state(ref_model.state_dict()).float()
     data = FederatedDataset.from_clients(clients, "cuda")
     tr = TinyCNNBatchedTrainer(TinyCNN(3).cuda(), data, epochs=2, batch_size=32, lr=0.05, momentum=0.9, p_drop=0.0,
-                               shuffle=False, use_graph=use_graph)
+                               shuffle=False, use_graph=use_graph, conv2=conv2)
     ids = list(range(len(sizes)))
     out, info = tr.train(flat0.cuda(), ids, 0)
     exp = _torch_reference(ref_model, flat0.double(), [(x.double(), y) for x, y in clients], 2, 32, 0.05, 0.9)
     got = out.cpu().double()
     err = (got - exp).abs().max(dim=1).values
-    assert float(err.max()) < 2e-4, err
+    # fp32 kernels track eager fp32 closely; the tcgen05 path rounds the conv2 operands to bf16 (fp32 accumulate)
+    assert float(err.max()) < (2e-4 if conv2 == "fp32" else 4e-3), err
     # parameters really moved
     assert float((got - flat0.double()).abs().max()) > 1e-3
     # a second round from the same start reproduces the first (fresh momentum, same data order)
