@@ -476,7 +476,7 @@ constexpr int XS1 = 37;  // row stride: bank = 5*ky + kx is distinct for the 25 
 __global__ void __launch_bounds__(416) conv1_wgrad_train(const Step s) {
     __shared__ float xs[32 * XS1];
     __shared__ float gsm[16 * 196];
-    __shared__ unsigned char ism[16 * 196];
+    __shared__ unsigned short osm[16 * 196];   // offset of the arg-max pixel of every pooled element in xs
     const int sel = blockIdx.y, b = blockIdx.x, tid = threadIdx.x;
     int lo;
     const int nb = batch_rows(s, sel, &lo);
@@ -508,7 +508,12 @@ __global__ void __launch_bounds__(416) conv1_wgrad_train(const Step s) {
             if (i < 784) {
                 gsm[4 * i] = av[r].x > 0.f ? dv[r].x : 0.f;     gsm[4 * i + 1] = av[r].y > 0.f ? dv[r].y : 0.f;
                 gsm[4 * i + 2] = av[r].z > 0.f ? dv[r].z : 0.f; gsm[4 * i + 3] = av[r].w > 0.f ? dv[r].w : 0.f;
-                ism[4 * i] = iv[r].x; ism[4 * i + 1] = iv[r].y; ism[4 * i + 2] = iv[r].z; ism[4 * i + 3] = iv[r].w;
+                const unsigned char args[4] = {iv[r].x, iv[r].y, iv[r].z, iv[r].w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int p = (4 * i + j) % 196, arg = args[j];
+                    osm[4 * i + j] = (unsigned short)((2 * (p / 14) + (arg >> 1)) * XS1 + 2 * (p % 14) + (arg & 1));
+                }
             }
         }
     }
@@ -518,11 +523,9 @@ __global__ void __launch_bounds__(416) conv1_wgrad_train(const Step s) {
     if (tid < 400) {
         const int o = tid / 25, ky = (tid % 25) / 5, kx = tid % 5;
         float acc = 0.f;
-        for (int p = 0; p < 196; ++p) {
-            const int arg = ism[o * 196 + p];
-            const int y = 2 * (p / 14) + (arg >> 1), x = 2 * (p % 14) + (arg & 1);
-            acc += gsm[o * 196 + p] * xs[(y + ky) * XS1 + x + kx];
-        }
+        const float* xt = xs + ky * XS1 + kx;
+#pragma unroll 4
+        for (int p = 0; p < 196; ++p) acc += gsm[o * 196 + p] * xt[osm[o * 196 + p]];
         part[C1W + tid] = acc;
     } else {
         const int o = tid - 400;
@@ -605,6 +608,18 @@ __global__ void __launch_bounds__(256) head_eval(const float* __restrict__ a2, c
         atomicAdd(out2, m + logf(sum) - z[b][y]);
         atomicAdd(out2 + 1, arg == y ? 1.f : 0.f);
     }
+}
+
+// second stream + events for the fork/join inside a step (works eagerly and under stream capture, where
+// the cross-stream waits become graph dependencies)
+static cudaStream_t g_side_stream = nullptr;
+static cudaEvent_t g_fork_event = nullptr, g_join_event = nullptr;
+static int side_stream_init() {
+    if (g_side_stream) return 0;
+    QFX_CUDA_TRY(cudaStreamCreateWithFlags(&g_side_stream, cudaStreamNonBlocking));
+    QFX_CUDA_TRY(cudaEventCreateWithFlags(&g_fork_event, cudaEventDisableTiming));
+    QFX_CUDA_TRY(cudaEventCreateWithFlags(&g_join_event, cudaEventDisableTiming));
+    return 0;
 }
 
 static bool g_attr_set = false;
@@ -697,14 +712,20 @@ extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const i
     fc1_fwd_train<<<dim3(FC1_SLICES, n_selected), 128, 0, stream>>>(s);
     head_train<<<n_selected, 256, 0, stream>>>(s);
     fc1_bwd_train<<<dim3(49, n_selected), 256, 0, stream>>>(s);
+    // fork: the conv2 weight gradient only needs g2 and a1; it runs beside conv2 dgrad -> conv1 wgrad
+    if (int e = side_stream_init()) return e;
+    QFX_CUDA_TRY(cudaEventRecord(g_fork_event, stream));
+    QFX_CUDA_TRY(cudaStreamWaitEvent(g_side_stream, g_fork_event, 0));
     if (conv2_mode == 1) {
+        if (int e = launch_conv2_umma_wgrad(s, n_selected, g_side_stream)) return e;
         if (int e = launch_conv2_umma_dgrad(s, n_selected, stream)) return e;
-        if (int e = launch_conv2_umma_wgrad(s, n_selected, stream)) return e;
     } else {
+        conv2_wgrad_train<<<dim3(BS, n_selected, s.split), 320 / s.split, WGRAD_SMEM, g_side_stream>>>(s);
         conv2_dgrad_train<<<gsplit, 256 / s.split, DGRAD_SMEM, stream>>>(s);
-        conv2_wgrad_train<<<dim3(BS, n_selected, s.split), 320 / s.split, WGRAD_SMEM, stream>>>(s);
     }
     conv1_wgrad_train<<<gimg, 416, 0, stream>>>(s);
+    QFX_CUDA_TRY(cudaEventRecord(g_join_event, g_side_stream));
+    QFX_CUDA_TRY(cudaStreamWaitEvent(stream, g_join_event, 0));
     sgd_conv_train<<<dim3((NCONV + 255) / 256, n_selected), 256, 0, stream>>>(s);
     return check_launch("tinycnn_train_step");
 }
