@@ -135,7 +135,8 @@ int qfx_enable_peer(int dev, int peer);
  * (/root/reference/src/CFed/Classical_FL.py:56-62) for every client: 9 kernels on `stream`, meant to
  * be captured in a CUDA graph.  params/moment are [n_selected, nd] rows in state_dict order;
  * batch_size <= 32; clients whose data is exhausted at (epoch, batch_index) are skipped.
- * conv2_mode 0: fp32 CUDA-core conv2 kernels; 1: tcgen05 bf16 implicit-GEMM conv2 (fp32 accumulate, fp32 master weights).
+ * round keys the dropout masks; round_dev (nullable device int) overrides it so a captured graph can be
+ * replayed for later rounds.  conv2_mode 0: fp32 CUDA-core conv2 kernels; 1: tcgen05 bf16 implicit-GEMM conv2 (fp32 accumulate, fp32 master weights).
  * workspace: qfx_tinycnn_workspace_bytes; its tail (qfx_tinycnn_stats_offset) holds per-client
  * (loss sum, #correct) accumulators that the caller zeroes per epoch. */
 int qfx_tinycnn_workspace_bytes(int n_selected, size_t* bytes);
@@ -145,8 +146,8 @@ int qfx_tinycnn_begin_round(const float* params, int nd, int n_selected, void* w
 int qfx_tinycnn_train_step(const float* X, const int* labels, const int* offsets, const int* perm, int n_total,
                            const int* client_ids, int n_selected, int epoch, int batch_index, int batch_size,
                            float* params, float* moment, int nd, int n_classes, float lr, float momentum,
-                           float p_drop, unsigned long long seed, int round, void* workspace, int conv2_mode,
-                           cudaStream_t stream);
+                           float p_drop, unsigned long long seed, int round, const int* round_dev,
+                           void* workspace, int conv2_mode, cudaStream_t stream);
 /* Evaluation (evaluate_model, /root/reference/src/CFed/Classical_FL.py:83-102) in three launches:
  * out2 = (loss sum, #correct); scratch needs n * 23,520 + 102,400 bytes. */
 int qfx_tinycnn_eval(const float* X, const int* labels, int n, const float* params, int n_classes,

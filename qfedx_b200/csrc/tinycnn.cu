@@ -231,7 +231,8 @@ __global__ void __launch_bounds__(256) head_train(const Step s) {
     if (tid < 2) red[tid] = 0.f;
     for (int i = tid; i < NC * 64; i += 256) w2[i / 64][i % 64] = prm[F2W + i];
     // h = dropout(relu(sum of split-K partials + b1))
-    const unsigned long long dkey = key3(s.seed ^ 0x44524f50ull, (unsigned long long)s.round * 4096ull + s.client_ids[sel],
+    const int rnd = s.round_dev ? *s.round_dev : s.round;
+    const unsigned long long dkey = key3(s.seed ^ 0x44524f50ull, (unsigned long long)rnd * 4096ull + s.client_ids[sel],
                                          (unsigned long long)s.epoch * 65536ull + s.batch_index);
     const float keep_scale = s.p_drop > 0.f ? 1.f / (1.f - s.p_drop) : 1.f;
     for (int i = tid; i < BS * 64; i += 256) {
@@ -685,8 +686,8 @@ extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const i
                                       int n_total, const int* client_ids, int n_selected, int epoch,
                                       int batch_index, int batch_size, float* params, float* moment, int nd,
                                       int n_classes, float lr, float momentum, float p_drop,
-                                      unsigned long long seed, int round, void* workspace, int conv2_mode,
-                                      cudaStream_t stream) {
+                                      unsigned long long seed, int round, const int* round_dev, void* workspace,
+                                      int conv2_mode, cudaStream_t stream) {
     QFX_ARG_CHECK(conv2_mode == 0 || conv2_mode == 1, QFX_ERR_BAD_ARG, "conv2_mode must be 0 (fp32) or 1 (tcgen05 bf16)");
     QFX_ARG_CHECK(batch_size >= 1 && batch_size <= BS, QFX_ERR_UNSUPPORTED,
                   "client-batched TinyCNN supports batch_size <= %d, got %d", BS, batch_size);
@@ -698,7 +699,7 @@ extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const i
     s.X = X; s.labels = labels; s.offsets = offsets; s.perm = perm; s.client_ids = client_ids;
     s.n_total = n_total; s.epoch = epoch; s.batch_index = batch_index; s.batch_size = batch_size;
     s.params = params; s.moment = moment; s.nd = nd; s.n_classes = n_classes;
-    s.lr = lr; s.momentum = momentum; s.p_drop = p_drop; s.seed = seed; s.round = round; s.conv2_mode = conv2_mode;
+    s.lr = lr; s.momentum = momentum; s.p_drop = p_drop; s.seed = seed; s.round = round; s.round_dev = round_dev; s.conv2_mode = conv2_mode;
     // many clients: two images per weight-gradient CTA (one wave of CTAs, half the partial sums)
     s.wgrad_ipc = (conv2_mode == 1 && n_selected >= 5) ? 2 : 1;
     carve(s, workspace, (size_t)n_selected);

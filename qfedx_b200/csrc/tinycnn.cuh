@@ -29,6 +29,7 @@ struct Step {
     float lr, momentum, p_drop;
     unsigned long long seed;
     int round;
+    const int* round_dev;    // when non-null the round is read from device memory (CUDA-graph replays)
     // activations / workspaces, all [K_sel, ...]
     float* a1; unsigned char* i1;    // [K,32,16,14,14]
     float* a2; unsigned char* i2;    // [K,32,32,7,7]

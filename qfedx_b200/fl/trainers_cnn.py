@@ -44,6 +44,7 @@ class TinyCNNBatchedTrainer:
         self._perm = None
         self._eval_scratch = None
         self._stream = torch.cuda.Stream(device=dev)
+        self._round_dev = torch.zeros(1, dtype=torch.int32, device=dev)   # dropout key of the replayed graph
 
     @property
     def weights(self) -> torch.Tensor:
@@ -88,7 +89,7 @@ class TinyCNNBatchedTrainer:
         self._graphs[sel_key] = st
         return st
 
-    def _enqueue_round(self, st, rnd_tensor_unused=None, rnd=0):
+    def _enqueue_round(self, st, rnd=0):
         """Everything of one round's local training on the current stream."""
         K = st["K"]
         st["params"][:, : self.dim] = st["global"][None, :]
@@ -105,7 +106,8 @@ class TinyCNNBatchedTrainer:
                           _lib.c_int(K), _lib.c_int(e), _lib.c_int(b), _lib.c_int(self.batch_size),
                           _lib.ptr(st["params"]), _lib.ptr(st["moment"]), _lib.c_int(self.nd),
                           _lib.c_int(self.n_classes), _lib.c_float(self.lr), _lib.c_float(self.momentum),
-                          _lib.c_float(self.p_drop), _lib.c_u64(self.seed), _lib.c_int(rnd), _lib.ptr(st["ws"]),
+                          _lib.c_float(self.p_drop), _lib.c_u64(self.seed), _lib.c_int(rnd), _lib.ptr(self._round_dev),
+                          _lib.ptr(st["ws"]),
                           _lib.c_int(self.conv2_mode), _lib.stream_ptr(), launches=KERNELS_PER_STEP)
 
     def train(self, global_flat: torch.Tensor, selected, rnd: int):
@@ -118,15 +120,13 @@ class TinyCNNBatchedTrainer:
             else:
                 self._perm.copy_(new_perm)  # same storage: the captured graph keeps pointing at it
         st["global"].copy_(global_flat[: self.dim])
+        self._round_dev.fill_(int(rnd))
         if not self.use_graph:
             self._enqueue_round(st, rnd=rnd)
         else:
             if st["graph"] is None:
-                # dropout masks are keyed by (seed, round, client, epoch, batch); a captured graph bakes
-                # `round` in, so the seed is advanced per round through device memory instead: the
-                # kernels read the key from the arguments, hence one graph per distinct round value
-                # would be needed.  We capture with round = 0 and vary `self.seed`-independent masks by
-                # permuting samples each round (the mask of a slot then lands on a different sample).
+                # dropout masks are keyed by (seed, round, client, epoch, batch); the kernels read the round
+                # from device memory (self._round_dev), so one captured graph serves every round
                 torch.cuda.synchronize()
                 before = _lib.LAUNCH_COUNT
                 g = torch.cuda.CUDAGraph()
