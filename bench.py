@@ -75,12 +75,12 @@ def barrier(world):
 def timed_rounds(step_fn, steps, warmup, world, flush=True):
     """W untimed steps, then exactly K steps between CUDA events, max over ranks; returns ms/step."""
     from qfedx_b200.utils.timing import ClockSampler, flush_l2, max_over_ranks
-    for _ in range(warmup):
-        step_fn()
-    barrier(world)
     cuda = torch.cuda.is_available()
-    sampler = ClockSampler(torch.cuda.current_device() if cuda else 0)
-    with sampler:
+    sampler = ClockSampler(torch.cuda.current_device() if cuda else 0, period_s=0.05)
+    with sampler:  # sampling starts with the warm-up so that short timed regions still get samples under load
+        for _ in range(warmup):
+            step_fn()
+        barrier(world)
         if cuda:
             evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
             for s, e in evs:
