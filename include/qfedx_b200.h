@@ -132,7 +132,7 @@ int qfx_enable_peer(int dev, int peer);
 
 /* K8: TinyCNN (the reference's model, /root/reference/src/CFed/Classical_FL.py:21-38) trained for
  * all selected clients at once.  One call = one SGD-momentum step of client_update
- * (/root/reference/src/CFed/Classical_FL.py:56-62) for every client: 9 kernels on `stream`, meant to
+ * (/root/reference/src/CFed/Classical_FL.py:56-62) for every client: 8 kernels on `stream`, meant to
  * be captured in a CUDA graph.  params/moment are [n_selected, nd] rows in state_dict order;
  * batch_size <= 32; clients whose data is exhausted at (epoch, batch_index) are skipped.
  * round keys the dropout masks; round_dev (nullable device int) overrides it so a captured graph can be

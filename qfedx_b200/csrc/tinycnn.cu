@@ -215,21 +215,23 @@ __global__ void __launch_bounds__(128) fc1_fwd_train(const Step s) {
 // ------------------------------------------------------------------------------------------
 // Head: fc1 bias + ReLU + dropout, fc2, softmax cross-entropy, and everything of the backward
 // pass that lives above fc1: d logits, fc2 / fc1-bias SGD updates, dh1.  One CTA per client.
-__global__ void __launch_bounds__(256) head_train(const Step s) {
-    __shared__ float h[BS][65];
-    __shared__ float w2[MAX_CLASSES][64];
-    __shared__ float z[BS][MAX_CLASSES];
-    __shared__ float dz[BS][MAX_CLASSES];
-    __shared__ float red[2];
-    const int sel = blockIdx.x, tid = threadIdx.x, NC = s.n_classes;
-    int lo;
-    const int nb = batch_rows(s, sel, &lo);
-    if (nb <= 0) return;
-    float* prm = s.params + (size_t)sel * s.nd;
-    float* mom = s.moment + (size_t)sel * s.nd;
+struct HeadSmem {
+    float h[BS][65];
+    float w2[MAX_CLASSES][64];
+    float z[BS][MAX_CLASSES];
+    float dz[BS][MAX_CLASSES];
+    float red[2];
+};
+// Runs inside every fc1_bwd CTA of a client (redundantly - the work is tiny and it removes a kernel whose
+// single CTA per client left the GPU idle): fills dh[b][f] in shared memory.  The owner CTA (chunk 0)
+// also accumulates the epoch statistics and stores the fc2 / fc1-bias gradients for sgd_conv_train.
+__device__ __forceinline__ void head_compute(const Step& s, int sel, int nb, int lo, HeadSmem& hs, float (*dh)[64],
+                                             bool owner) {
+    const int tid = threadIdx.x, NC = s.n_classes;
+    const float* __restrict__ prm = s.params + (size_t)sel * s.nd;
     const int f2b = F2W + 64 * NC;
-    if (tid < 2) red[tid] = 0.f;
-    for (int i = tid; i < NC * 64; i += 256) w2[i / 64][i % 64] = prm[F2W + i];
+    if (tid < 2) hs.red[tid] = 0.f;
+    for (int i = tid; i < NC * 64; i += 256) hs.w2[i / 64][i % 64] = prm[F2W + i];
     // h = dropout(relu(sum of split-K partials + b1))
     const int rnd = s.round_dev ? *s.round_dev : s.round;
     const unsigned long long dkey = key3(s.seed ^ 0x44524f50ull, (unsigned long long)rnd * 4096ull + s.client_ids[sel],
@@ -252,73 +254,72 @@ __global__ void __launch_bounds__(256) head_train(const Step s) {
                 v = u < s.p_drop ? 0.f : v * keep_scale;
             }
         }
-        h[b][f] = v;
-        s.h1[((size_t)sel * BS + b) * 64 + f] = v;
+        hs.h[b][f] = v;
     }
     __syncthreads();
-    // logits
-    for (int i = tid; i < BS * NC; i += 256) {
+    for (int i = tid; i < BS * NC; i += 256) {   // logits
         const int b = i / NC, c = i % NC;
         float v = prm[f2b + c];
 #pragma unroll 8
-        for (int f = 0; f < 64; ++f) v += h[b][f] * w2[c][f];
-        z[b][c] = v;
+        for (int f = 0; f < 64; ++f) v += hs.h[b][f] * hs.w2[c][f];
+        hs.z[b][c] = v;
     }
     __syncthreads();
     if (tid < BS) {
         const int b = tid;
         if (b < nb) {
             const int y = s.labels[sample_index(s, lo, b)];
-            float m = z[b][0]; int arg = 0;
-            for (int c = 1; c < NC; ++c) if (z[b][c] > m) { m = z[b][c]; arg = c; }
+            float m = hs.z[b][0]; int arg = 0;
+            for (int c = 1; c < NC; ++c) if (hs.z[b][c] > m) { m = hs.z[b][c]; arg = c; }
             float sum = 0.f;
-            for (int c = 0; c < NC; ++c) sum += expf(z[b][c] - m);
+            for (int c = 0; c < NC; ++c) sum += expf(hs.z[b][c] - m);
             const float inv = 1.f / sum, inv_nb = 1.f / (float)nb;
-            for (int c = 0; c < NC; ++c) dz[b][c] = (expf(z[b][c] - m) * inv - (c == y ? 1.f : 0.f)) * inv_nb;
-            atomicAdd(&red[0], m + logf(sum) - z[b][y]);
-            atomicAdd(&red[1], arg == y ? 1.f : 0.f);
+            for (int c = 0; c < NC; ++c) hs.dz[b][c] = (expf(hs.z[b][c] - m) * inv - (c == y ? 1.f : 0.f)) * inv_nb;
+            if (owner) {
+                atomicAdd(&hs.red[0], m + logf(sum) - hs.z[b][y]);
+                atomicAdd(&hs.red[1], arg == y ? 1.f : 0.f);
+            }
         } else {
-            for (int c = 0; c < NC; ++c) dz[b][c] = 0.f;
+            for (int c = 0; c < NC; ++c) hs.dz[b][c] = 0.f;
         }
     }
     __syncthreads();
-    if (tid == 0) { s.stats[sel * 2] += red[0]; s.stats[sel * 2 + 1] += red[1]; }
-    // dh1 = (dz W2) masked by ReLU/dropout (h > 0 <=> kept and active)
+    // dh = (dz W2) masked by ReLU/dropout (h > 0 <=> kept and active)
     for (int i = tid; i < BS * 64; i += 256) {
         const int b = i >> 6, f = i & 63;
         float v = 0.f;
-        if (h[b][f] > 0.f) {
-            for (int c = 0; c < NC; ++c) v += dz[b][c] * w2[c][f];
+        if (hs.h[b][f] > 0.f) {
+            for (int c = 0; c < NC; ++c) v += hs.dz[b][c] * hs.w2[c][f];
             v *= keep_scale;
         }
-        s.dh1[((size_t)sel * BS + b) * 64 + f] = v;
+        dh[b][f] = v;
     }
-    // fc2 weight / bias and fc1 bias updates (their last use this step is above)
-    for (int i = tid; i < NC * 64 + NC + 64; i += 256) {
-        float g = 0.f; int p;
-        if (i < NC * 64) {
-            const int c = i / 64, f = i % 64;
-            for (int b = 0; b < nb; ++b) g += dz[b][c] * h[b][f];
-            p = F2W + i;
-        } else if (i < NC * 64 + NC) {
-            const int c = i - NC * 64;
-            for (int b = 0; b < nb; ++b) g += dz[b][c];
-            p = f2b + c;
-        } else {
-            const int f = i - NC * 64 - NC;
-            for (int b = 0; b < nb; ++b) {
-                if (h[b][f] > 0.f) {
-                    float v = 0.f;
-                    for (int c = 0; c < NC; ++c) v += dz[b][c] * w2[c][f];
-                    g += v * keep_scale;
+    if (owner) {
+        if (tid == 0) { s.stats[sel * 2] += hs.red[0]; s.stats[sel * 2 + 1] += hs.red[1]; }
+        // gradients of fc2 weights, fc2 bias, fc1 bias: applied by sgd_conv_train at the end of the step
+        float* hg = s.head_grad + (size_t)sel * HEAD_GRAD_STRIDE;
+        for (int i = tid; i < NC * 64 + NC + 64; i += 256) {
+            float g = 0.f;
+            if (i < NC * 64) {
+                const int c = i / 64, f = i % 64;
+                for (int b = 0; b < nb; ++b) g += hs.dz[b][c] * hs.h[b][f];
+            } else if (i < NC * 64 + NC) {
+                const int c = i - NC * 64;
+                for (int b = 0; b < nb; ++b) g += hs.dz[b][c];
+            } else {
+                const int f = i - NC * 64 - NC;
+                for (int b = 0; b < nb; ++b) {
+                    if (hs.h[b][f] > 0.f) {
+                        float v = 0.f;
+                        for (int c = 0; c < NC; ++c) v += hs.dz[b][c] * hs.w2[c][f];
+                        g += v * keep_scale;
+                    }
                 }
             }
-            p = F1B + f;
+            hg[i] = g;
         }
-        const float m = s.momentum * mom[p] + g;
-        mom[p] = m;
-        prm[p] -= s.lr * m;
     }
+    __syncthreads();
 }
 
 // ------------------------------------------------------------------------------------------
@@ -328,21 +329,19 @@ __global__ void __launch_bounds__(256) fc1_bwd_train(const Step s) {
     __shared__ __align__(16) float dh[BS][64];
     __shared__ float xs[BS][33];
     __shared__ float wsm[64][33];
+    __shared__ HeadSmem hs;
     const int sel = blockIdx.y, k0 = blockIdx.x * 32, tid = threadIdx.x;
     int lo;
     const int nb = batch_rows(s, sel, &lo);
     if (nb <= 0) return;
     float* prm = s.params + (size_t)sel * s.nd;
     float* mom = s.moment + (size_t)sel * s.nd;
-    for (int i = tid * 4; i < BS * 64; i += 1024) {
-        if ((i >> 6) < nb) cp_async16(&dh[0][0] + i, s.dh1 + (size_t)sel * BS * 64 + i);
-        else *reinterpret_cast<float4*>(&dh[0][0] + i) = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
     for (int i = tid; i < BS * 32; i += 256) {
         const int b = i >> 5, k = i & 31;
         if (b < nb) cp_async4(&xs[b][k], s.a2 + ((size_t)sel * BS + b) * 1568 + k0 + k); else xs[b][k] = 0.f;
     }
     for (int i = tid; i < 64 * 32; i += 256) cp_async4(&wsm[i >> 5][i & 31], prm + F1W + (size_t)(i >> 5) * 1568 + k0 + (i & 31));
+    head_compute(s, sel, nb, lo, hs, dh, blockIdx.x == 0);   // the async copies above land meanwhile
     cp_async_wait_all();
     __syncthreads();
     // dx[b][k] = sum_f dh[b][f] W1[f][k]; 1024 outputs, 4 per thread (b = tid/8 .., k = ..)
@@ -536,19 +535,31 @@ __global__ void __launch_bounds__(416) conv1_wgrad_train(const Step s) {
     }
 }
 
-// reduce the per-image partials and apply SGD-momentum to the 13,248 conv parameters
+// reduce the per-image partials and apply SGD-momentum to the 13,248 conv parameters; the same kernel applies
+// the fc2 / fc1-bias gradients that the head left in head_grad
 __global__ void __launch_bounds__(256) sgd_conv_train(const Step s) {
-    const int sel = blockIdx.y, p = blockIdx.x * 256 + threadIdx.x;
+    const int sel = blockIdx.y, p0 = blockIdx.x * 256 + threadIdx.x;
     int lo;
-    if (batch_rows(s, sel, &lo) <= 0 || p >= NCONV) return;
+    if (batch_rows(s, sel, &lo) <= 0) return;
+    float* prm = s.params + (size_t)sel * s.nd;
+    float* mom = s.moment + (size_t)sel * s.nd;
+    const int NC = s.n_classes;
+    if (p0 >= NCONV) {
+        const int i = p0 - NCONV;
+        if (i >= NC * 64 + NC + 64) return;
+        const int p = i < NC * 64 + NC ? F2W + i : F1B + (i - NC * 64 - NC);
+        const float m = s.momentum * mom[p] + s.head_grad[(size_t)sel * HEAD_GRAD_STRIDE + i];
+        mom[p] = m;
+        prm[p] -= s.lr * m;
+        return;
+    }
+    const int p = p0;
     const float* part = s.conv_part + (size_t)sel * BS * NCONV + p;
     float g = 0.f;
     // conv1 partials always have one row per image; conv2 partials have BS / wgrad_ipc rows
     const int rows = (p >= C2W && s.conv2_mode == 1) ? BS / s.wgrad_ipc : BS;
 #pragma unroll 8
     for (int b = 0; b < rows; ++b) g += part[(size_t)b * NCONV];
-    float* prm = s.params + (size_t)sel * s.nd;
-    float* mom = s.moment + (size_t)sel * s.nd;
     const float m = s.momentum * mom[p] + g;
     mom[p] = m;
     const float w = prm[p] - s.lr * m;
@@ -647,7 +658,7 @@ extern "C" int qfx_tinycnn_workspace_bytes(int n_selected, size_t* bytes) {
     auto add = [&](size_t n) { tot += (n + 255) & ~(size_t)255; };
     add(K * BS * 3136 * 4); add(K * BS * 3136); add(K * BS * 1568 * 4); add(K * BS * 1568);
     add(K * FC1_SLICES * BS * 64 * 4); add(K * BS * 64 * 4); add(K * BS * 64 * 4);
-    add(K * BS * 32 * 196 * 4); add(K * BS * 3136 * 4); add(K * BS * NCONV * 4); add(K * 12800 * 4); add(K * 12800 * 4); add(K * 12800 * 2); add(K * 12800 * 2);
+    add(K * BS * 32 * 196 * 4); add(K * BS * 3136 * 4); add(K * BS * NCONV * 4); add(K * 12800 * 4); add(K * 12800 * 4); add(K * 12800 * 2); add(K * 12800 * 2); add(K * HEAD_GRAD_STRIDE * 4);
     add(K * 2 * 4);
     *bytes = tot;
     return 0;
@@ -664,6 +675,7 @@ static void carve(Step& s, void* workspace, size_t K) {
     s.conv_part = (float*)take(K * BS * NCONV * 4);
     s.w2f = (float*)take(K * 12800 * 4); s.w2b = (float*)take(K * 12800 * 4);
     s.w2uf = (__nv_bfloat16*)take(K * 12800 * 2); s.w2ub = (__nv_bfloat16*)take(K * 12800 * 2);
+    s.head_grad = (float*)take(K * HEAD_GRAD_STRIDE * 4);
     s.stats = (float*)take(K * 2 * 4);
 }
 
@@ -679,7 +691,7 @@ extern "C" int qfx_tinycnn_begin_round(const float* params, int nd, int n_select
     return launch_conv2_umma_prep(params, nd, n_selected, s.w2uf, s.w2ub, stream);
 }
 
-// One SGD step for every selected client: 9 kernels on `stream` (capture them in a CUDA graph).
+// One SGD step for every selected client: 8 kernels on `stream` (capture them in a CUDA graph).
 // `workspace` comes from qfx_tinycnn_workspace_bytes; stats (last 2K floats of it) accumulate the
 // epoch's loss sum and correct count - the caller zeroes them per epoch.
 extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const int* offsets, const int* perm,
@@ -711,7 +723,6 @@ extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const i
     if (conv2_mode == 1) { if (int e = launch_conv2_umma_fwd(s, n_selected, stream)) return e; }
     else conv2_fwd_train<<<gsplit, 256 / s.split, CONV2_SMEM, stream>>>(s);
     fc1_fwd_train<<<dim3(FC1_SLICES, n_selected), 128, 0, stream>>>(s);
-    head_train<<<n_selected, 256, 0, stream>>>(s);
     fc1_bwd_train<<<dim3(49, n_selected), 256, 0, stream>>>(s);
     // fork: the conv2 weight gradient only needs g2 and a1; it runs beside conv2 dgrad -> conv1 wgrad
     if (int e = side_stream_init()) return e;
@@ -727,7 +738,7 @@ extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const i
     conv1_wgrad_train<<<gimg, 416, 0, stream>>>(s);
     QFX_CUDA_TRY(cudaEventRecord(g_join_event, g_side_stream));
     QFX_CUDA_TRY(cudaStreamWaitEvent(stream, g_join_event, 0));
-    sgd_conv_train<<<dim3((NCONV + 255) / 256, n_selected), 256, 0, stream>>>(s);
+    sgd_conv_train<<<dim3((NCONV + 64 + 65 * n_classes + 255) / 256, n_selected), 256, 0, stream>>>(s);
     return check_launch("tinycnn_train_step");
 }
 

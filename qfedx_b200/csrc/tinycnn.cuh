@@ -13,6 +13,7 @@ constexpr int NCONV = 13248;     // conv parameters (reduced from per-image part
 constexpr int FC1_SLICES = 14;   // split-K slices of the 1568-long fc1 reduction
 constexpr int FC1_KS = 112;      // 1568 / 14
 constexpr int MAX_CLASSES = 10;
+constexpr int HEAD_GRAD_STRIDE = 64 + 65 * MAX_CLASSES + 6;   // fc2 weights, fc2 bias, fc1 bias gradients (padded)
 
 struct Step {
     const float* X;          // [N,1,28,28] dataset
@@ -39,6 +40,7 @@ struct Step {
     float* g2;                       // [K,32,32,14,14]
     float* da1;                      // [K,32,16,14,14]
     float* conv_part;                // [K,32,NCONV]
+    float* head_grad;                // [K,HEAD_GRAD_STRIDE] fc2 / fc1-bias gradients of the step
     float* w2f;                      // [K,12800] conv2 weights as [c][tap][o]      (forward operand)
     float* w2b;                      // [K,12800] conv2 weights as [o][24-tap][c]   (data-gradient operand)
     __nv_bfloat16* w2uf;             // [K,12800] bf16 UMMA forward operand  [tap][c/8][oc/8][oc%8][c%8]

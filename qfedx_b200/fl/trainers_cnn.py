@@ -16,7 +16,7 @@ from ..models.tinycnn import TinyCNN, flatten_state, unflatten_state
 from ..ops import _lib
 from .dataset import FederatedDataset
 
-KERNELS_PER_STEP = 9
+KERNELS_PER_STEP = 8
 
 
 class TinyCNNBatchedTrainer:
