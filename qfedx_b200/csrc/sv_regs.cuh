@@ -21,6 +21,18 @@ namespace qfx {
 
 constexpr unsigned FULL_MASK = 0xffffffffu;
 
+// Lane-qubit loops of the merged sweeps: rolled (one copy of the gate code, small kernel) or unrolled
+// (static qubit indices, more scheduling freedom).  Measured on B200 for the 8-qubit training kernel.
+#ifndef QFX_ROLL_LANE_LOOPS
+#define QFX_ROLL_LANE_LOOPS 0
+#endif
+#if QFX_ROLL_LANE_LOOPS
+#define QFX_LANE_LOOP _Pragma("unroll 1")
+#else
+#define QFX_LANE_LOOP _Pragma("unroll")
+#endif
+
+
 // default lane split: favours throughput (most amplitudes per lane, fewest shuffles)
 constexpr int default_lane_bits(int nq) { return (nq <= 4) ? 0 : ((nq <= 9) ? nq - 4 : 5); }
 // latency split: as many lanes per circuit as possible (shortest instruction stream per warp)
@@ -238,12 +250,12 @@ struct Sv {
 #pragma unroll
             for (int q = 0; q + 1 < C::NL; ++q) cnot(q, q + 1, lg);
             cnot(C::NL - 1, C::NL, lg);
-#pragma unroll 1
+            QFX_LANE_LOOP
             for (int k = 0; k + 1 < C::LB; ++k) cnot_lanes_rt(k, k + 1, lg);
             cnot(NQ - 1, 0, lg);
         } else {
             cnot(NQ - 1, 0, lg);
-#pragma unroll 1
+            QFX_LANE_LOOP
             for (int k = C::LB - 2; k >= 0; --k) cnot_lanes_rt(k, k + 1, lg);
             cnot(C::NL - 1, C::NL, lg);
 #pragma unroll
@@ -464,6 +476,33 @@ __device__ __forceinline__ void ansatz_backward(Sv<NQ, LB_>& psi, Sv<NQ, LB_>& l
     }
 }
 
+// ---- many-values warp reduction ---------------------------------------------------------------
+// Sums N per-lane values over the 32 lanes of a warp with N-1 (+1) shuffles instead of 5 N: every
+// butterfly step halves the number of values a lane carries (it keeps the half selected by one of its
+// lane bits and sends the other half to its partner).  Afterwards lane L holds the total of value
+// index slot_of_lane(L) in v[0]; for N = 16 the two lanes that differ in bit 0 hold the same total.
+template <int N>
+__device__ __forceinline__ void warp_reduce_many(float (&v)[N], int lane) {
+    static_assert(N == 16 || N == 32, "warp_reduce_many handles 16 or 32 values");
+#pragma unroll
+    for (int cnt = N / 2, mask = 16; cnt >= 1; cnt >>= 1, mask >>= 1) {
+        const bool up = (lane & mask) != 0;
+#pragma unroll
+        for (int i = 0; i < cnt; ++i) {
+            const float keep = up ? v[i + cnt] : v[i];
+            const float send = up ? v[i] : v[i + cnt];
+            v[i] = keep + __shfl_xor_sync(FULL_MASK, send, mask);
+        }
+    }
+    if (N == 16) v[0] += __shfl_xor_sync(FULL_MASK, v[0], 1);
+}
+template <int N>
+__device__ __forceinline__ int slot_of_lane(int lane) {
+    // step with mask m keeps the upper half when (lane & m): the kept index gains cnt = N/2, N/4, ...
+    if (N == 32) return ((lane >> 4) & 1) * 16 + ((lane >> 3) & 1) * 8 + ((lane >> 2) & 1) * 4 + ((lane >> 1) & 1) * 2 + (lane & 1);
+    return ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+}
+
 // ---- merged-diagonal sweeps (all circuits of a CTA share theta) ---------------------------
 // Gates on different qubits commute, so a layer is [RX on every qubit][RZ on every qubit][ring].
 // The RZ block is one diagonal; it factors into a table over the local bits and a table over the
@@ -521,23 +560,34 @@ __device__ __forceinline__ void ansatz_forward_merged(Sv<NQ, LB_>& psi, const fl
             const float2 a = tab[(l * NQ + q) * 2];
             psi.rx(q, a.x, a.y, lg);
         }
-#pragma unroll 1
-        for (int k = 0; k < C::LB; ++k) {
-            const float2 a = tab[(l * NQ + C::NL + k) * 2];
-            psi.rx_lane_rt(k, a.x, a.y);
+        if (C::LB > 0) {
+            float2 a_next = tab[(l * NQ + C::NL) * 2];
+            QFX_LANE_LOOP
+            for (int k = 0; k < C::LB; ++k) {
+                const float2 a = a_next;
+                if (k + 1 < C::LB) a_next = tab[(l * NQ + C::NL + k + 1) * 2];   // prefetch the next gate's (cos, sin)
+                psi.rx_lane_rt(k, a.x, a.y);
+            }
         }
         apply_diag(psi, dt, l, lg, false);
         psi.entangle_rolled(ent, false, lg);
     }
 }
 
+// Reverse sweep with the merged diagonal.  The 2 NQ gradient shares of a layer are collected in registers
+// and handed to sink.layer(l, g) in one block (slot q = RX of qubit q, slot NQ + q = RZ of qubit q), so the
+// sink can reduce them over the warp together instead of one 5-step butterfly per parameter.
 template <int NQ, int LB_, class Sink>
 __device__ __forceinline__ void ansatz_backward_merged(Sv<NQ, LB_>& psi, Sv<NQ, LB_>& lam, const float2* tab,
                                                        const DiagTables& dt, int n_layers, int ent, int lg,
                                                        Sink& sink) {
     using C = SvCfg<NQ, LB_>;
+    constexpr int NG = (2 * NQ <= 16) ? 16 : 32;
 #pragma unroll 1
     for (int l = n_layers - 1; l >= 0; --l) {
+        float g[NG];
+#pragma unroll
+        for (int i = 0; i < NG; ++i) g[i] = 0.f;
         psi.entangle_rolled(ent, true, lg);
         lam.entangle_rolled(ent, true, lg);
         // all RZ gradients from one pass: t_i = Im(conj(lam_i) psi_i), signed sums per qubit
@@ -556,23 +606,29 @@ __device__ __forceinline__ void ansatz_backward_merged(Sv<NQ, LB_>& psi, Sv<NQ, 
                 } else {
                     v = ((lg >> (q - C::NL)) & 1) ? -tot : tot;
                 }
-                sink((l * NQ + q) * 2 + 1, v);
+                g[NQ + q] = v;
             }
         }
         apply_diag(psi, dt, l, lg, true);
         apply_diag(lam, dt, l, lg, true);
-#pragma unroll 1
-        for (int k = C::LB - 1; k >= 0; --k) {
-            const int q = C::NL + k;
-            const float2 a = tab[(l * NQ + q) * 2];
-            sink((l * NQ + q) * 2, grad_and_undo_rx_lane_rt(psi, lam, k, a.x, a.y));
+        {
+            float2 a_next = tab[(l * NQ + NQ - 1) * 2];
+            QFX_LANE_LOOP
+            for (int k = C::LB - 1; k >= 0; --k) {
+                const float2 a = a_next;
+                if (k > 0) a_next = tab[(l * NQ + C::NL + k - 1) * 2];   // prefetch the next gate's (cos, sin)
+                const float v = grad_and_undo_rx_lane_rt(psi, lam, k, a.x, a.y);
+#pragma unroll
+                for (int j = 0; j < C::LB; ++j) g[C::NL + j] += (j == k) ? v : 0.f;   // static slots, rolled loop
+            }
         }
 #pragma unroll
         for (int k = 0; k < C::NL; ++k) {
             const int q = C::NL - 1 - k;
             const float2 a = tab[(l * NQ + q) * 2];
-            sink((l * NQ + q) * 2, grad_and_undo_rx(psi, lam, q, a.x, a.y, lg));
+            g[q] = grad_and_undo_rx(psi, lam, q, a.x, a.y, lg);
         }
+        sink.template layer<NQ, NG>(l, g);
     }
 }
 

@@ -40,15 +40,32 @@ struct TrainArgs {
     int grad_mode;            // 0 adjoint, 1 parameter shift
 };
 
-// Gradient sink: reduce over the whole warp (dead circuits contribute zero), then lane 0 adds into
-// the warp's private row of the shared-memory gradient matrix - no atomics, no contention.
+// Gradient sink: reduce over the whole warp (dead circuits contribute zero) and add into the warp's private
+// row of the shared-memory gradient matrix - no atomics, no contention.  `first` marks the first pass of a
+// minibatch: the row is then stored instead of read-modified-written, which takes the shared-memory load
+// latency off the warp's in-order critical path.
 struct WarpRowSink {
     float* row;
     bool live;
     int lane;
-    __device__ __forceinline__ void operator()(int p, float v) {
+    bool first;
+    __device__ __forceinline__ void operator()(int p, float v) {   // single value (readout / statistics)
         v = warp_sum(live ? v : 0.f);
-        if (lane == 0) row[p] += v;
+        if (lane == 0) { if (first) row[p] = v; else row[p] += v; }
+    }
+    // one layer's 2 NQ gradient shares: slot q -> parameter (l NQ + q) 2, slot NQ + q -> (l NQ + q) 2 + 1
+    template <int NQ, int NG>
+    __device__ __forceinline__ void layer(int l, float (&g)[NG]) {
+        if (!live) {
+#pragma unroll
+            for (int i = 0; i < NG; ++i) g[i] = 0.f;
+        }
+        warp_reduce_many<NG>(g, lane);
+        const int slot = slot_of_lane<NG>(lane);
+        if (slot < 2 * NQ && (NG == 32 || (lane & 1) == 0)) {
+            const int p = slot < NQ ? (l * NQ + slot) * 2 : (l * NQ + slot - NQ) * 2 + 1;
+            if (first) row[p] = g[0]; else row[p] += g[0];
+        }
     }
 };
 
@@ -162,7 +179,7 @@ vqc_local_train_kernel(const TrainArgs a) {
                 for (int q = 0; q < NQ; ++q) cot[q] = (q < NC) ? dz[q] * prm[P + q] : 0.f;
                 {
                     // readout and statistics: one contribution per circuit (its lane 0)
-                    WarpRowSink once{my_row, live && lg == 0, lane};
+                    WarpRowSink once{my_row, live && lg == 0, lane, ps == 0};
 #pragma unroll
                     for (int q = 0; q < NQ; ++q)
                         if (q < NC) {
@@ -175,7 +192,7 @@ vqc_local_train_kernel(const TrainArgs a) {
                 if (a.grad_mode == 0) {
                     Sv<NQ, LB_> lam;
                     lam.set_obs_times(psi, cot, lg);
-                    WarpRowSink sink{my_row, live, lane};
+                    WarpRowSink sink{my_row, live, lane, ps == 0};
                     ansatz_backward_merged(psi, lam, tab, dt, a.n_layers, a.ent, lg, sink);
                 } else if (live && lg == 0) {
 #pragma unroll
