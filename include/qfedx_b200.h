@@ -180,6 +180,8 @@ int qfx_unitary_gemm(const float* a_hi, const float* a_lo, const float* b_hi, co
  *   array, ops_dev a DEVICE array of n_ops x 5 ints from the compiler; theta [theta_rows][n_params],
  *   angles [angle_rows][n_feature] (row = batch index modulo rows); shift_param/shift_value [batch]
  *   add a per-state shift to one parameter (parameter-shift rule, /root/reference/ROADMAP.md:130-135).
+ *   plan_dev (nullable, tile_bits == 12 only): segment plan for the register-resident engine (DEVICE ints:
+ *   n_seg, then per segment pos_to_bit[12], n_ops, n_ops x {kind, posA, posB, op index}); see ops/large.py.
  * qfx_sv_large_expz: <Z_q> for all n_total qubits -> out [batch][n_total]; qubits >= n_local are
  *   read from high_bits (the shard's rank).
  * qfx_sv_global_swap_fused: sharded state, world = 2^g_bits ranks: exchange the g global qubits with
@@ -192,7 +194,8 @@ int qfx_circuit_compile(int n_qubits, int n_gates, const int* gates_in, int tile
 int qfx_sv_large_pass(float* states, int n_qubits, int batch, int tile_bits, int low_bits,
                       const int* tile_qubits_host, const int* ops_dev, int n_ops, const float* theta, int theta_rows,
                       int n_params, const float* angles, int angle_rows, int n_feature, const int* shift_param,
-                      const float* shift_value, int init_zero_state, cudaStream_t stream);
+                      const float* shift_value, int init_zero_state, const int* plan_dev, int plan_len,
+                      cudaStream_t stream);
 int qfx_sv_large_expz(const float* states, int n_local, int n_total, unsigned int high_bits, int batch, float* out,
                       cudaStream_t stream);
 int qfx_sv_global_swap_fused(const float* const* src_table, float* dst, int n_local, int g_bits, int rank, int world,

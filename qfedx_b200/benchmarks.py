@@ -94,18 +94,18 @@ def unitary_gemm_throughput(n=8, L=6, B=1 << 15):
     return out
 
 
-def large_state_throughput(n=20, L=2, batch=16, tile_bits=12, low_bits=3):
+def large_state_throughput(n=20, L=2, batch=16, tile_bits=12, low_bits=3, register_engine=True):
     """K5: gates/s of the pass engine on `batch` n-qubit states (config 4 shape: 16 clients x 20 qubits)."""
     from .ops.large import LargeVQC, expvals_z
     dev = torch.device("cuda")
-    vqc = LargeVQC(n, L, tile_bits=tile_bits, low_bits=low_bits)
+    vqc = LargeVQC(n, L, tile_bits=tile_bits, low_bits=low_bits, register_engine=register_engine)
     ang = torch.rand(batch, n, device=dev) * math.pi
     theta = torch.randn(1, vqc.n_params, device=dev)
     ms = _time_ms(lambda: vqc.states(ang, theta), iters=5, warmup=2)
     st = vqc.states(ang, theta)
     ez = _time_ms(lambda: expvals_z(st, n), iters=5, warmup=1)
     state_bytes = (1 << n) * 8 * batch
-    return {"n_qubits": n, "layers": L, "batch": batch, "tile_bits": tile_bits, "low_bits": low_bits,
+    return {"n_qubits": n, "layers": L, "batch": batch, "tile_bits": tile_bits, "low_bits": low_bits, "register_engine": register_engine,
             "passes": len(vqc.passes), "gates": vqc.n_gates, "ms": ms,
             "gates_per_s": vqc.n_gates * batch / ms * 1e3,
             "effective_gbs": 2 * state_bytes * len(vqc.passes) / ms / 1e6, "expz_ms": ez}

@@ -36,6 +36,65 @@ class Pass:
     tile_qubits: np.ndarray   # int32 [T] host
     ops: np.ndarray           # int32 [k,5] host
     ops_dev: torch.Tensor | None = None
+    plan: np.ndarray | None = None       # segment plan for the register-resident kernel (12-qubit tiles)
+    plan_dev: torch.Tensor | None = None
+
+
+REG_TILE_BITS = 12
+
+
+def plan_segments(ops: np.ndarray) -> np.ndarray:
+    """Split a 12-bit pass into segments for the register-resident kernel (csrc/sv_large.cu, v2).
+
+    Positions: 0-4 lane bits, 5-8 register bits, 9-11 warp bits (inactive in a segment).  Tile bits 0-3
+    stay on lane positions 0-3 (conflict-free shared-memory re-layout); the other eight bits are
+    re-assigned per segment: the three whose next use is farthest become inactive (Belady), the busiest
+    four of the rest become register bits.  Returns the int32 plan: n_seg, then per segment
+    pos_to_bit[12], n_ops, n_ops x (kind, posA, posB, op index)."""
+    flexible = list(range(4, REG_TILE_BITS))
+    remaining = list(range(len(ops)))
+
+    def bits_of(i):
+        k, b0, b1 = int(ops[i][0]), int(ops[i][1]), int(ops[i][2])
+        return (b0, b1) if k in TWO_QUBIT else (b0,)
+
+    segs = []
+    while remaining:
+        next_use = {}
+        for rank, i in enumerate(remaining):
+            for b in bits_of(i):
+                next_use.setdefault(b, rank)
+        order = sorted(flexible, key=lambda b: -next_use.get(b, 1 << 30))
+        inactive = set(order[:3])
+        blocked, chosen, rest = set(), [], []
+        for i in remaining:
+            bs = set(bits_of(i))
+            if bs & inactive or bs & blocked:
+                blocked |= bs
+                rest.append(i)
+            else:
+                chosen.append(i)
+        assert chosen, "segment planner made no progress"
+        active = [b for b in flexible if b not in inactive]          # 5 bits: 4 register + 1 lane
+        use = {b: 0 for b in active}
+        for i in chosen:
+            for b in bits_of(i):
+                if b in use:
+                    use[b] += 1 if int(ops[i][0]) in TWO_QUBIT else 2      # 1q gates gain most from registers
+        by_use = sorted(active, key=lambda b: -use[b])
+        regs, lane4 = sorted(by_use[:4]), by_use[4]
+        p2b = [0, 1, 2, 3, lane4] + regs + sorted(inactive)
+        pos_of = {b: p for p, b in enumerate(p2b)}
+        seg = list(p2b) + [len(chosen)]
+        for i in chosen:
+            k, b0, b1 = int(ops[i][0]), int(ops[i][1]), int(ops[i][2])
+            seg += [k, pos_of[b0], pos_of[b1] if k in TWO_QUBIT else -1, i]
+        segs.append(seg)
+        remaining = rest
+    flat = [len(segs)]
+    for sgm in segs:
+        flat += sgm
+    return np.asarray(flat, dtype=np.int32)
 
 
 def compile_passes(n_qubits: int, gates: Sequence[Tuple[int, int, int, int]], tile_bits: int = 12,
@@ -54,11 +113,15 @@ def compile_passes(n_qubits: int, gates: Sequence[Tuple[int, int, int, int]], ti
                 _lib.c_int(max_passes), _lib.c_int(max_ops), ip(tq), ip(begin), ip(ops))
     if n_pass < 0:
         raise _lib.QfxError(f"qfx_circuit_compile failed ({n_pass}): {_lib.lib().qfx_last_error().decode()}")
-    return [Pass(tq[i].copy(), ops[begin[i]:begin[i + 1]].copy()) for i in range(n_pass)]
+    passes = [Pass(tq[i].copy(), ops[begin[i]:begin[i + 1]].copy()) for i in range(n_pass)]
+    if tile_bits == REG_TILE_BITS:
+        for p in passes:
+            p.plan = plan_segments(p.ops)
+    return passes
 
 
 def run_passes(states: torch.Tensor, n_qubits: int, passes: List[Pass], theta=None, angles=None, shift_param=None,
-               shift_value=None, init_zero: bool = False, low_bits: int = 3) -> None:
+               shift_value=None, init_zero: bool = False, low_bits: int = 3, use_register_engine: bool = True) -> None:
     """In place on ``states`` [B, 2^n] complex64 (CUDA)."""
     B = states.shape[0]
     flat = torch.view_as_real(states)
@@ -68,6 +131,8 @@ def run_passes(states: torch.Tensor, n_qubits: int, passes: List[Pass], theta=No
         if p.ops_dev is None or p.ops_dev.device != states.device:
             p.ops_dev = torch.as_tensor(p.ops, device=states.device).contiguous()
         T = len(p.tile_qubits)
+        if p.plan is not None and (p.plan_dev is None or p.plan_dev.device != states.device):
+            p.plan_dev = torch.as_tensor(p.plan, device=states.device).contiguous()
         tq = np.ascontiguousarray(p.tile_qubits, dtype=np.int32)
         low = 0                                   # leading tile qubits that are 0,1,2,.. move as contiguous runs
         while low < min(low_bits, T) and tq[low] == low:
@@ -78,7 +143,8 @@ def run_passes(states: torch.Tensor, n_qubits: int, passes: List[Pass], theta=No
                   _lib.c_int(0 if th is None else th.shape[1]), _lib.ptr(ang),
                   _lib.c_int(0 if ang is None else ang.shape[0]), _lib.c_int(0 if ang is None else ang.shape[1]),
                   _lib.ptr(shift_param), _lib.ptr(shift_value), _lib.c_int(1 if (init_zero and i == 0) else 0),
-                  _lib.stream_ptr())
+                  _lib.ptr(p.plan_dev if use_register_engine else None),
+                  _lib.c_int(0 if p.plan is None else len(p.plan)), _lib.stream_ptr())
 
 
 def expvals_z(states: torch.Tensor, n_local: int, n_total: int | None = None, high_bits: int = 0) -> torch.Tensor:
@@ -94,8 +160,10 @@ class LargeVQC:
     """n-qubit VQC on the pass engine.  ``expvals`` batches over samples, ``param_shift_grad`` batches the
     2P shifted circuits of every sample (K4b for large states)."""
 
-    def __init__(self, n_qubits: int, n_layers: int, entangler: str = "cnot", tile_bits: int = 12, low_bits: int = 3):
+    def __init__(self, n_qubits: int, n_layers: int, entangler: str = "cnot", tile_bits: int = 12, low_bits: int = 3,
+                 register_engine: bool = True):
         self.n, self.L, self.entangler = n_qubits, n_layers, entangler
+        self.register_engine = register_engine
         self.tile_bits, self.low_bits = min(tile_bits, n_qubits), min(low_bits, n_qubits)
         self.gates = ansatz_gates(n_qubits, n_layers, entangler)
         self.n_params = 2 * n_qubits * n_layers
@@ -117,7 +185,7 @@ class LargeVQC:
             return ref.vqc_state_ref(angles, th, None if th.shape[0] == 1 else torch.arange(B), "ry", self.entangler)
         st = torch.empty(B, 1 << self.n, dtype=torch.complex64, device=angles.device)
         run_passes(st, self.n, self.passes, theta, angles, shift_param, shift_value, init_zero=True,
-                   low_bits=self.low_bits)
+                   low_bits=self.low_bits, use_register_engine=self.register_engine)
         return st
 
     def expvals(self, angles: torch.Tensor, theta: torch.Tensor) -> torch.Tensor:

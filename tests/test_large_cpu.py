@@ -60,3 +60,27 @@ def test_bad_gate_is_rejected():
     from qfedx_b200.ops.large import compile_passes
     with pytest.raises(_lib.QfxError):
         compile_passes(4, [(0, 7, -1, 0)], 4, 2)
+
+
+def test_segment_plan_is_a_valid_reordering():
+    """Every op appears once, only on active positions, per-bit order preserved, bits 0-3 pinned to lanes 0-3."""
+    from qfedx_b200.ops.large import TWO_QUBIT, ansatz_gates, compile_passes
+    passes = compile_passes(20, ansatz_gates(20, 3), 12, 3)
+    for p in passes:
+        plan = p.plan.tolist()
+        n_seg, cur, seen = plan[0], 1, []
+        for _ in range(n_seg):
+            p2b, n_ops = plan[cur:cur + 12], plan[cur + 12]
+            assert sorted(p2b) == list(range(12)) and p2b[:4] == [0, 1, 2, 3]
+            for o in range(n_ops):
+                kind, pa, pb, idx = plan[cur + 13 + 4 * o: cur + 17 + 4 * o]
+                assert 0 <= pa < 9 and (kind not in TWO_QUBIT or 0 <= pb < 9)          # never a warp (inactive) bit
+                assert p2b[pa] == p.ops[idx][1] and (kind not in TWO_QUBIT or p2b[pb] == p.ops[idx][2])
+                seen.append(idx)
+            cur += 13 + 4 * n_ops
+        assert sorted(seen) == list(range(len(p.ops)))
+        # per-bit order of the ops is unchanged
+        for b in range(12):
+            touching = [i for i in range(len(p.ops)) if b in (p.ops[i][1], p.ops[i][2] if p.ops[i][0] in TWO_QUBIT else -9)]
+            assert [i for i in seen if i in touching] == touching
+        assert n_seg <= 3
