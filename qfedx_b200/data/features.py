@@ -119,7 +119,7 @@ def images_to_angles(X: torch.Tensor, n_qubits: int = 4, grid=(4, 4), scale: flo
     (/root/reference/src/QFed/testEncoder.py:94,124-125)."""
     if X.dim() == 4:
         X = X[:, 0]
-    small = downsample_images(X, grid).reshape(X.shape[0], -1)
+    small = downsample_images(X, grid).reshape(X.shape[0], grid[0] * grid[1])   # explicit size: clients may be empty
     return angle_features(small, n_qubits, scale)
 
 
@@ -129,5 +129,5 @@ def images_to_amplitudes(X: torch.Tensor, n_qubits: int = 4) -> torch.Tensor:
         X = X[:, 0]
     side_h = 1 << ((n_qubits + 1) // 2)
     side_w = 1 << (n_qubits // 2)
-    small = downsample_images(X, (side_h, side_w)).reshape(X.shape[0], -1)
+    small = downsample_images(X, (side_h, side_w)).reshape(X.shape[0], side_h * side_w)
     return amplitude_normalize(small)

@@ -21,6 +21,7 @@ from ..ops.aggregate import fedavg_aggregate
 from ..utils.checkpoint import latest_checkpoint, load_checkpoint, save_checkpoint
 from ..utils.logging import RoundLogger
 from ..utils.seed import rng_state, set_rng_state
+from ..utils.tracing import PhaseTimer
 from .accountant import RDPAccountant
 from .sampler import inject_dropouts, sample_clients
 
@@ -63,6 +64,7 @@ class FederatedRunner:
         self.accountant = RDPAccountant()
         self.history = {"accuracy": [], "loss": [], "epsilon": [], "round_ms": []}
         self.round = 0
+        self.timer = PhaseTimer()
         self.logger = RoundLogger(cfg.log_path, cfg.tensorboard_dir, cfg.print_every, cfg.quiet)
         self._weights = trainer.weights if global_weights is None else torch.as_tensor(global_weights, dtype=torch.float32)
         if cfg.resume and cfg.checkpoint_dir:
@@ -105,21 +107,25 @@ class FederatedRunner:
         common = dict(mode=cfg.mode, n_wrap=n_wrap, clip=cfg.clip, sigma=cfg.sigma, server_lr=cfg.server_lr,
                       seed=cfg.seed, rnd=rnd, secagg=cfg.secagg)
         if self.client_gids is None:
-            client_params, stats = self.trainer.train(self.global_flat, survivors, rnd)
+            with self.timer.phase("train_ms"):
+                client_params, stats = self.trainer.train(self.global_flat, survivors, rnd)
             w = self._weights[torch.as_tensor(survivors, dtype=torch.long)]
-            res = (self.aggregator or fedavg_aggregate)(client_params, self.global_flat, w, None, **common)
+            with self.timer.phase("aggregate_ms"):
+                res = (self.aggregator or fedavg_aggregate)(client_params, self.global_flat, w, None, **common)
         else:
             alive = set(int(s) for s in survivors)
             rows = [i for i, g in enumerate(self.client_gids) if g in alive]
-            if rows:
-                client_params, stats = self.trainer.train(self.global_flat, rows, rnd)
-            else:
-                client_params, stats = None, {}
+            with self.timer.phase("train_ms"):
+                if rows:
+                    client_params, stats = self.trainer.train(self.global_flat, rows, rnd)
+                else:
+                    client_params, stats = None, {}
             part = torch.zeros(K, dtype=torch.int32)
             part[torch.as_tensor(survivors, dtype=torch.long)] = 1
             w = self._weights[torch.as_tensor(survivors, dtype=torch.long)]
-            res = self.aggregator(client_params, self.global_flat, self._weights, part,
-                                  gids=[self.client_gids[i] for i in rows], **common)
+            with self.timer.phase("aggregate_ms"):
+                res = self.aggregator(client_params, self.global_flat, self._weights, part,
+                                      gids=[self.client_gids[i] for i in rows], **common)
         self.global_flat = res.new_global
         if cfg.mode == "delta" and cfg.clip > 0 and cfg.sigma > 0:
             # per-client noise sigma*C on each of m averaged updates: the aggregate carries noise of
@@ -143,7 +149,8 @@ class FederatedRunner:
             info = self.run_round()
             metrics = dict(info)
             if self.test_data is not None and (self.round % cfg.eval_every == 0 or self.round == cfg.num_rounds):
-                loss, acc = self.evaluate()
+                with self.timer.phase("eval_ms"):
+                    loss, acc = self.evaluate()
                 self.history["accuracy"].append(acc)
                 self.history["loss"].append(loss)
                 metrics.update(accuracy=acc, loss=loss)
@@ -155,6 +162,7 @@ class FederatedRunner:
             self.history["round_ms"].append(ms)
             metrics["round_ms"] = ms
             metrics["comm_mb"] = 2.0 * info["survivors"] * self.global_flat.numel() * 4 / 1e6
+            metrics.update(self.timer.summary_ms())   # device ms per phase (train / aggregate / eval)
             self.logger.log(self.round, **metrics)
             if cfg.checkpoint_every and cfg.checkpoint_dir and self.round % cfg.checkpoint_every == 0:
                 self.save()
