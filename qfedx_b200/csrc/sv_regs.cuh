@@ -263,6 +263,42 @@ struct Sv {
         }
     }
 
+    // ---- the whole CNOT ring as ONE index permutation through shared memory ---------------------
+    // CNOT(0,1) CNOT(1,2) ... CNOT(n-2,n-1) CNOT(n-1,0) maps basis index i to pi(i) with
+    //   bit_k(pi) = b_0 ^ ... ^ b_k  (k >= 1),   bit_0(pi) = b_0 ^ bit_{n-1}(pi)
+    // - a linear map over GF(2), so pi(lane bits | local bits) = pi(lane part) ^ pi(local part): the local
+    // parts are compile-time constants and the lane part is computed once per thread.  The ring then costs
+    // one shared-memory round trip (A stores + A loads of 8 bytes) instead of n dependent CNOT steps, five
+    // of which need two shuffles and two selects per amplitude.  `buf` holds the circuit's 2^n amplitudes.
+    static __device__ __forceinline__ constexpr unsigned ring_perm(unsigned i) {
+        unsigned p = i;
+        p ^= p << 1; p ^= p << 2; p ^= p << 4; p ^= p << 8;
+        p &= (1u << NQ) - 1u;
+        return p ^ ((p >> (NQ - 1)) & 1u);
+    }
+    static __device__ __forceinline__ constexpr unsigned ring_perm_inv(unsigned j) {
+        unsigned p = j ^ ((j >> (NQ - 1)) & 1u);          // undo CNOT(n-1, 0)
+        return (p ^ (p << 1)) & ((1u << NQ) - 1u);          // undo the prefix XOR
+    }
+    // physical slot of amplitude index d: XOR-fold the high nibble into the low one so that the 16 lanes of a
+    // half-warp, whose indices differ in high bits, land in different 8-byte banks (a bijection on indices)
+    static __device__ __forceinline__ constexpr unsigned ring_slot(unsigned d) { return d ^ ((d >> 4) & 0xFu); }
+    __device__ __forceinline__ void ring_via_smem(float2* buf, bool reverse, int lg) {
+        const unsigned lane_part = reverse ? ring_perm_inv((unsigned)lg << C::NL) : ring_perm((unsigned)lg << C::NL);
+#pragma unroll
+        for (int i = 0; i < C::A; ++i) {
+            const unsigned dst = lane_part ^ (reverse ? ring_perm_inv((unsigned)i) : ring_perm((unsigned)i));
+            buf[ring_slot(dst)] = make_float2(re[i], im[i]);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < C::A; ++i) {
+            const float2 v = buf[ring_slot(((unsigned)lg << C::NL) | (unsigned)i)];
+            re[i] = v.x; im[i] = v.y;
+        }
+        __syncwarp();
+    }
+
     // ---- reductions --------------------------------------------------------------------
     // <Z_q> for all qubits, reduced over the circuit's lanes; every lane gets the result
     __device__ __forceinline__ void expval_z_all(float* __restrict__ ez /*[NQ]*/, int lg) const {
@@ -549,9 +585,11 @@ __device__ __forceinline__ void apply_diag(Sv<NQ, LB_>& psi, const DiagTables& d
     }
 }
 
+// `ring_buf`: per-circuit shared-memory scratch of 2^n float2 for the permutation form of the CNOT ring
+// (nullptr: apply the CNOTs one by one).
 template <int NQ, int LB_>
 __device__ __forceinline__ void ansatz_forward_merged(Sv<NQ, LB_>& psi, const float2* tab, const DiagTables& dt,
-                                                      int n_layers, int ent, int lg) {
+                                                      int n_layers, int ent, int lg, float2* ring_buf = nullptr) {
     using C = SvCfg<NQ, LB_>;
 #pragma unroll 1
     for (int l = 0; l < n_layers; ++l) {
@@ -570,7 +608,8 @@ __device__ __forceinline__ void ansatz_forward_merged(Sv<NQ, LB_>& psi, const fl
             }
         }
         apply_diag(psi, dt, l, lg, false);
-        psi.entangle_rolled(ent, false, lg);
+        if (ring_buf != nullptr && ent == ENT_CNOT && NQ >= 3) psi.ring_via_smem(ring_buf, false, lg);
+        else psi.entangle_rolled(ent, false, lg);
     }
 }
 
@@ -580,7 +619,7 @@ __device__ __forceinline__ void ansatz_forward_merged(Sv<NQ, LB_>& psi, const fl
 template <int NQ, int LB_, class Sink>
 __device__ __forceinline__ void ansatz_backward_merged(Sv<NQ, LB_>& psi, Sv<NQ, LB_>& lam, const float2* tab,
                                                        const DiagTables& dt, int n_layers, int ent, int lg,
-                                                       Sink& sink) {
+                                                       Sink& sink, float2* ring_buf = nullptr) {
     using C = SvCfg<NQ, LB_>;
     constexpr int NG = (2 * NQ <= 16) ? 16 : 32;
 #pragma unroll 1
@@ -588,8 +627,13 @@ __device__ __forceinline__ void ansatz_backward_merged(Sv<NQ, LB_>& psi, Sv<NQ, 
         float g[NG];
 #pragma unroll
         for (int i = 0; i < NG; ++i) g[i] = 0.f;
-        psi.entangle_rolled(ent, true, lg);
-        lam.entangle_rolled(ent, true, lg);
+        if (ring_buf != nullptr && ent == ENT_CNOT && NQ >= 3) {
+            psi.ring_via_smem(ring_buf, true, lg);
+            lam.ring_via_smem(ring_buf, true, lg);
+        } else {
+            psi.entangle_rolled(ent, true, lg);
+            lam.entangle_rolled(ent, true, lg);
+        }
         // all RZ gradients from one pass: t_i = Im(conj(lam_i) psi_i), signed sums per qubit
         {
             float t[C::A];

@@ -38,6 +38,7 @@ struct TrainArgs {
     int opt;                  // 0 SGD-momentum, 1 Adam
     float lr, beta1, beta2, eps;
     int grad_mode;            // 0 adjoint, 1 parameter shift
+    int ring_offset_floats;   // where the CNOT-ring scratch starts in dynamic shared memory (set by the launcher)
 };
 
 // Gradient sink: reduce over the whole warp (dead circuits contribute zero) and add into the warp's private
@@ -121,6 +122,9 @@ vqc_local_train_kernel(const TrainArgs a) {
     float* m2 = m1 + D;
     float* sgrad = m2 + D;
     float* scot = sgrad + NW * DS;
+    // per-circuit scratch for the permutation form of the CNOT ring (8-byte aligned, after everything else)
+    float2* ring_all = reinterpret_cast<float2*>(smem + a.ring_offset_floats);
+    float2* ring_buf = ring_all + (size_t)(threadIdx.x >> C::LB) * C::DIM;
 
     const int tid = threadIdx.x;
     for (int p = tid; p < D; p += TR_THREADS) {
@@ -164,7 +168,7 @@ vqc_local_train_kernel(const TrainArgs a) {
 
                 Sv<NQ, LB_> psi;
                 psi.set_product(a.angles + (size_t)sidx * NQ, a.basis, lg);
-                ansatz_forward_merged(psi, tab, dt, a.n_layers, a.ent, lg);
+                ansatz_forward_merged(psi, tab, dt, a.n_layers, a.ent, lg, ring_buf);
                 float ez[NQ];
                 psi.expval_z_all(ez, lg);
 
@@ -193,7 +197,7 @@ vqc_local_train_kernel(const TrainArgs a) {
                     Sv<NQ, LB_> lam;
                     lam.set_obs_times(psi, cot, lg);
                     WarpRowSink sink{my_row, live, lane, ps == 0};
-                    ansatz_backward_merged(psi, lam, tab, dt, a.n_layers, a.ent, lg, sink);
+                    ansatz_backward_merged(psi, lam, tab, dt, a.n_layers, a.ent, lg, sink, ring_buf);
                 } else if (live && lg == 0) {
 #pragma unroll
                     for (int q = 0; q < NQ; ++q) scot[j * NQ + q] = cot[q];
@@ -343,8 +347,13 @@ static int launch_train(const TrainArgs& a, int n_sel, int cluster_size, cudaStr
     cfg.blockDim = dim3(TR_THREADS);
     const int P = 2 * NQ * a.n_layers, D = P + 2 * a.n_classes;
     const int DS = (D + 2 + 3) & ~3;
-    const size_t smem = sizeof(float) * (size_t)(2 * P + 2 * a.n_layers * (C::A + C::LANES) + 3 * D +
-                                                 (TR_THREADS / 32) * DS + (a.grad_mode == 1 ? a.batch_size * NQ : 0));
+    size_t floats = (size_t)(2 * P + 2 * a.n_layers * (C::A + C::LANES) + 3 * D + (TR_THREADS / 32) * DS +
+                             (a.grad_mode == 1 ? a.batch_size * NQ : 0));
+    floats = (floats + 1) & ~(size_t)1;                       // float2 alignment of the ring scratch
+    TrainArgs args = a;
+    args.ring_offset_floats = (int)floats;
+    floats += (size_t)2 * (TR_THREADS >> C::LB) * C::DIM;     // one 2^n float2 buffer per circuit slot of the CTA
+    const size_t smem = sizeof(float) * floats;
     QFX_ARG_CHECK(smem <= 200 * 1024, QFX_ERR_TOO_LARGE, "training state needs %zu bytes of shared memory", smem);
     if (smem > 48 * 1024)
         QFX_CUDA_TRY(cudaFuncSetAttribute(vqc_local_train_kernel<NQ, LB_>,
@@ -358,7 +367,7 @@ static int launch_train(const TrainArgs& a, int n_sel, int cluster_size, cudaStr
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    QFX_CUDA_TRY(cudaLaunchKernelEx(&cfg, vqc_local_train_kernel<NQ, LB_>, a));
+    QFX_CUDA_TRY(cudaLaunchKernelEx(&cfg, vqc_local_train_kernel<NQ, LB_>, args));
     return 0;
 }
 
