@@ -608,7 +608,7 @@ __device__ __forceinline__ void ansatz_forward_merged(Sv<NQ, LB_>& psi, const fl
             }
         }
         apply_diag(psi, dt, l, lg, false);
-        if (ring_buf != nullptr && ent == ENT_CNOT && NQ >= 3) psi.ring_via_smem(ring_buf, false, lg);
+        if (ring_buf != nullptr && ent == ENT_CNOT && NQ >= 3 && SvCfg<NQ, LB_>::LB >= 2) psi.ring_via_smem(ring_buf, false, lg);
         else psi.entangle_rolled(ent, false, lg);
     }
 }
@@ -627,7 +627,7 @@ __device__ __forceinline__ void ansatz_backward_merged(Sv<NQ, LB_>& psi, Sv<NQ, 
         float g[NG];
 #pragma unroll
         for (int i = 0; i < NG; ++i) g[i] = 0.f;
-        if (ring_buf != nullptr && ent == ENT_CNOT && NQ >= 3) {
+        if (ring_buf != nullptr && ent == ENT_CNOT && NQ >= 3 && SvCfg<NQ, LB_>::LB >= 2) {
             psi.ring_via_smem(ring_buf, true, lg);
             lam.ring_via_smem(ring_buf, true, lg);
         } else {

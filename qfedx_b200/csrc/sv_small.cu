@@ -35,6 +35,7 @@ sv_forward_kernel(int n_layers, int basis, int ent, const float* __restrict__ an
                   const int* __restrict__ gid, int B, float* __restrict__ expvals, float2* __restrict__ state_out) {
     using C = SvCfg<NQ>;
     __shared__ float2 tab[MAX_PARAMS_SMEM];
+    extern __shared__ __align__(16) float2 dyn[];   // merged path: diag tables | per-circuit ring scratch
     const int n_params = 2 * NQ * n_layers;
     if (gid == nullptr) fill_trig_table(tab, theta, n_params);
     const int lg = threadIdx.x & (C::LANES - 1);
@@ -45,8 +46,14 @@ sv_forward_kernel(int n_layers, int basis, int ent, const float* __restrict__ an
     Sv<NQ> psi;
     load_initial(psi, angles, init_state, basis, b, lg);
     if (gid == nullptr) {
-        TrigTable trig{tab, -1, 0.f};
-        ansatz_forward(psi, trig, n_layers, ent, lg);
+        // one parameter group per launch: merged RZ diagonal and the CNOT ring as one permutation
+        float2* dloc = dyn;
+        float2* dlane = dloc + n_layers * C::A;
+        float2* ring = dlane + n_layers * C::LANES + (size_t)(threadIdx.x >> C::LB) * C::DIM;
+        build_diag_tables<NQ, C::LB>(dloc, dlane, tab, n_layers, threadIdx.x, SV_THREADS);
+        __syncthreads();
+        const DiagTables dt{dloc, dlane};
+        ansatz_forward_merged(psi, tab, dt, n_layers, ent, lg, ring);
     } else {
         TrigDirect trig{theta + (size_t)gid[b] * n_params, -1, 0.f};
         ansatz_forward(psi, trig, n_layers, ent, lg);
@@ -78,6 +85,25 @@ struct AtomicSink {
     }
 };
 
+// Sink of the merged backward sweep: one layer's 2 NQ gradient shares are reduced over the warp together and
+// added to the CTA's shared-memory accumulator (one atomic per parameter and warp).
+struct WarpLayerSink {
+    float* dst;
+    bool live;
+    int lane;
+    template <int NQ, int NG>
+    __device__ __forceinline__ void layer(int l, float (&g)[NG]) {
+        if (!live) {
+#pragma unroll
+            for (int i = 0; i < NG; ++i) g[i] = 0.f;
+        }
+        warp_reduce_many<NG>(g, lane);
+        const int slot = slot_of_lane<NG>(lane);
+        if (slot < 2 * NQ && (NG == 32 || (lane & 1) == 0))
+            atomicAdd(dst + (slot < NQ ? (l * NQ + slot) * 2 : (l * NQ + slot - NQ) * 2 + 1), g[0]);
+    }
+};
+
 template <int NQ>
 __global__ void __launch_bounds__(SV_THREADS)
 sv_adjoint_kernel(int n_layers, int basis, int ent, const float* __restrict__ angles,
@@ -87,6 +113,7 @@ sv_adjoint_kernel(int n_layers, int basis, int ent, const float* __restrict__ an
     using C = SvCfg<NQ>;
     __shared__ float2 tab[MAX_PARAMS_SMEM];
     __shared__ float sgrad[MAX_PARAMS_SMEM];
+    extern __shared__ __align__(16) float2 dyn[];
     const int n_params = 2 * NQ * n_layers;
     if (gid == nullptr) {
         for (int p = threadIdx.x; p < n_params; p += blockDim.x) sgrad[p] = 0.f;
@@ -104,11 +131,16 @@ sv_adjoint_kernel(int n_layers, int basis, int ent, const float* __restrict__ an
     for (int q = 0; q < NQ; ++q) cq[q] = cot[(size_t)b * NQ + q];
 
     if (gid == nullptr) {
-        TrigTable trig{tab, -1, 0.f};
-        ansatz_forward(psi, trig, n_layers, ent, lg);
+        float2* dloc = dyn;
+        float2* dlane = dloc + n_layers * C::A;
+        float2* ring = dlane + n_layers * C::LANES + (size_t)(threadIdx.x >> C::LB) * C::DIM;
+        build_diag_tables<NQ, C::LB>(dloc, dlane, tab, n_layers, threadIdx.x, SV_THREADS);
+        __syncthreads();
+        const DiagTables dt{dloc, dlane};
+        ansatz_forward_merged(psi, tab, dt, n_layers, ent, lg, ring);
         lam.set_obs_times(psi, cq, lg);
-        AtomicSink<C::LANES> sink{sgrad, live, lg};
-        ansatz_backward(psi, lam, trig, n_layers, ent, lg, sink);
+        WarpLayerSink sink{sgrad, live, (int)(threadIdx.x & 31)};
+        ansatz_backward_merged(psi, lam, tab, dt, n_layers, ent, lg, sink, ring);
     } else {
         const size_t off = (size_t)gid[b] * n_params;
         TrigDirect trig{theta + off, -1, 0.f};
@@ -197,11 +229,22 @@ static inline unsigned blocks_for(long long circuits, int lanes) {
     return (unsigned)((threads + SV_THREADS - 1) / SV_THREADS);
 }
 
+// dynamic shared memory of the merged path: diag tables + one 2^n float2 ring buffer per circuit of the CTA
+template <int NQ>
+static size_t merged_smem(int L, const int* gid) {
+    using C = SvCfg<NQ>;
+    if (gid != nullptr) return 0;
+    return sizeof(float2) * ((size_t)L * (C::A + C::LANES) + (size_t)(SV_THREADS >> C::LB) * C::DIM);
+}
+
 template <int NQ>
 struct FwdLaunch {
     static int run(int L, int basis, int ent, const float* angles, const float* init, const float* theta,
                    const int* gid, int B, float* expvals, float2* state_out, cudaStream_t st) {
-        sv_forward_kernel<NQ><<<blocks_for(B, SvCfg<NQ>::LANES), SV_THREADS, 0, st>>>(
+        const size_t smem = merged_smem<NQ>(L, gid);
+        if (smem > 24 * 1024)
+            QFX_CUDA_TRY(cudaFuncSetAttribute(sv_forward_kernel<NQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        sv_forward_kernel<NQ><<<blocks_for(B, SvCfg<NQ>::LANES), SV_THREADS, smem, st>>>(
             L, basis, ent, angles, init, theta, gid, B, expvals, state_out);
         return check_launch("sv_forward_kernel");
     }
@@ -210,7 +253,10 @@ template <int NQ>
 struct AdjLaunch {
     static int run(int L, int basis, int ent, const float* angles, const float* init, const float* theta,
                    const int* gid, int B, const float* cot, float* gth, float* gang, cudaStream_t st) {
-        sv_adjoint_kernel<NQ><<<blocks_for(B, SvCfg<NQ>::LANES), SV_THREADS, 0, st>>>(
+        const size_t smem = merged_smem<NQ>(L, gid);
+        if (smem > 24 * 1024)
+            QFX_CUDA_TRY(cudaFuncSetAttribute(sv_adjoint_kernel<NQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        sv_adjoint_kernel<NQ><<<blocks_for(B, SvCfg<NQ>::LANES), SV_THREADS, smem, st>>>(
             L, basis, ent, angles, init, theta, gid, B, cot, gth, gang);
         return check_launch("sv_adjoint_kernel");
     }
