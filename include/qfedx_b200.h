@@ -36,6 +36,8 @@ extern "C" {
  * entangler: 0 CNOT ring, 1 CZ ring, 2 none (/root/reference/ROADMAP.md:127) */
 
 const char* qfx_last_error(void);
+/* out[j] = keyed Feistel permutation of [0, n) (the in-kernel sample shuffle); test hook, host + device agree. */
+int qfx_debug_feistel(int n, unsigned long long key, int* out_dev, cudaStream_t stream);
 int qfx_version(void);
 
 /* K1+K3: feature map (angles [B,n]) or amplitude-encoded real state (init_state [B,2^n]),
@@ -67,6 +69,7 @@ int qfx_sv_param_shift(int n_qubits, int n_layers, int basis, int entangler, con
  * angles [N,n], labels [N], offsets [K+1], perm [epochs,N] (nullable), client_ids [n_selected],
  * params_out [n_selected, D], stats_out [n_selected, 2] (mean loss, accuracy of the last epoch).
  * lane_mode 0 keeps most amplitudes per lane (throughput), 1 spreads a circuit over most lanes (latency).
+ * Sample order per epoch: perm if given; else a keyed Feistel permutation when shuffle_key != 0; else sequential.
  * Counterpart of client_update, /root/reference/src/CFed/Classical_FL.py:40-64, for the VQC of
  * /root/reference/ROADMAP.md:29-43. */
 int qfx_vqc_local_train(int n_qubits, int n_layers, int basis, int entangler, int n_classes,
@@ -74,7 +77,7 @@ int qfx_vqc_local_train(int n_qubits, int n_layers, int basis, int entangler, in
                         int n_total, const float* params_in, const int* client_ids, int n_selected,
                         float* params_out, float* stats_out, int epochs, int batch_size, int optimizer,
                         float lr, float beta1, float beta2, float eps, int grad_mode, int cluster_size,
-                        int lane_mode, cudaStream_t stream);
+                        int lane_mode, unsigned long long shuffle_key, cudaStream_t stream);
 
 /* Evaluation in one launch: out2[0] = sum of losses, out2[1] = number correct.
  * Counterpart of evaluate_model, /root/reference/src/CFed/Classical_FL.py:83-102. */
@@ -147,7 +150,7 @@ int qfx_tinycnn_train_step(const float* X, const int* labels, const int* offsets
                            const int* client_ids, int n_selected, int epoch, int batch_index, int batch_size,
                            float* params, float* moment, int nd, int n_classes, float lr, float momentum,
                            float p_drop, unsigned long long seed, int round, const int* round_dev,
-                           void* workspace, int conv2_mode, cudaStream_t stream);
+                           void* workspace, int conv2_mode, unsigned long long shuffle_key, cudaStream_t stream);
 /* Evaluation (evaluate_model, /root/reference/src/CFed/Classical_FL.py:83-102) in three launches:
  * out2 = (loss sum, #correct); scratch needs n * 23,520 + 102,400 bytes. */
 int qfx_tinycnn_eval(const float* X, const int* labels, int n, const float* params, int n_classes,

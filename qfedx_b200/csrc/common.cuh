@@ -63,6 +63,40 @@ __device__ __forceinline__ float uniform_from_bits(uint64_t r) {
     return ((uint32_t)(r >> 40)) * (1.0f / 16777216.0f);                     // [0,1)
 }
 
+// ---- keyed permutation of [0, n) without storage -----------------------------------------
+// Four-round (unbalanced) Feistel network on exactly ceil(log2 n) bits with cycle walking: a bijection of
+// [0, n) evaluated in O(1) per index (fewer than two walks on average), so a kernel can visit a client's
+// samples in a fresh pseudo-random order every epoch without a permutation array.  32-bit round function.
+// Mirrored bit for bit in qfedx_b200/fl/prng.py: feistel_permutation.
+__host__ __device__ __forceinline__ uint32_t feistel_round(uint32_t x, uint32_t k) {
+    x ^= k;
+    x ^= x >> 16; x *= 0x85EBCA6Bu;
+    x ^= x >> 13; x *= 0xC2B2AE35u;
+    return x ^ (x >> 16);
+}
+__host__ __device__ __forceinline__ uint32_t feistel_perm(uint32_t j, uint32_t n, uint64_t key) {
+    if (n <= 1) return 0;
+    int bits = 1;
+    while ((1u << bits) < n) ++bits;
+    const int a = bits >> 1, b = bits - a;             // |l| = a, |r| = b (b >= a, b - a <= 1)
+    const uint32_t k0 = (uint32_t)key, k1 = (uint32_t)(key >> 32);
+    uint32_t x = j;
+    do {
+        uint32_t l = x & ((1u << a) - 1u), r = x >> a;
+        int la = a, lb = b;                            // current widths of l and r
+#pragma unroll
+        for (int rnd = 0; rnd < 4; ++rnd) {
+            const uint32_t f = feistel_round(r, (rnd & 1 ? k1 : k0) + 0x9E3779B9u * (uint32_t)rnd) & ((1u << la) - 1u);
+            const uint32_t nl = r;
+            r = l ^ f;
+            l = nl;
+            const int t = la; la = lb; lb = t;
+        }
+        x = (r << la) | l;                             // after an even number of rounds the widths are (a, b) again
+    } while (x >= n);
+    return x;
+}
+
 // ---- warp helpers -----------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

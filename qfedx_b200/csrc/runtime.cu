@@ -16,3 +16,13 @@ void set_last_error(const char* fmt, ...) {
 
 extern "C" const char* qfx_last_error(void) { return qfx::g_last_error; }
 extern "C" int qfx_version(void) { return 100; }
+
+__global__ void feistel_kernel(int n, unsigned long long key, int* out) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < n) out[j] = (int)qfx::feistel_perm((uint32_t)j, (uint32_t)n, key);
+}
+extern "C" int qfx_debug_feistel(int n, unsigned long long key, int* out_dev, cudaStream_t stream) {
+    QFX_ARG_CHECK(n >= 1 && out_dev, QFX_ERR_BAD_ARG, "bad arguments");
+    feistel_kernel<<<(n + 255) / 256, 256, 0, stream>>>(n, key, out_dev);
+    return qfx::check_launch("feistel_kernel");
+}

@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(224) conv1_fwd_train(const Step s) {
     int lo;
     if (b >= batch_rows(s, sel, &lo)) return;
     const size_t off = ((size_t)sel * BS + b) * 16 * 196;
-    conv1_image(s.X + (size_t)sample_index(s, lo, b) * 784, s.params + (size_t)sel * s.nd, s.a1 + off, s.i1 + off);
+    conv1_image(s.X + (size_t)sample_index(s, sel, lo, b) * 784, s.params + (size_t)sel * s.nd, s.a1 + off, s.i1 + off);
 }
 __global__ void __launch_bounds__(224) conv1_fwd_eval(const float* __restrict__ X, const float* __restrict__ prm,
                                                       float* a1, unsigned char* i1) {
@@ -268,7 +268,7 @@ __device__ __forceinline__ void head_compute(const Step& s, int sel, int nb, int
     if (tid < BS) {
         const int b = tid;
         if (b < nb) {
-            const int y = s.labels[sample_index(s, lo, b)];
+            const int y = s.labels[sample_index(s, sel, lo, b)];
             float m = hs.z[b][0]; int arg = 0;
             for (int c = 1; c < NC; ++c) if (hs.z[b][c] > m) { m = hs.z[b][c]; arg = c; }
             float sum = 0.f;
@@ -485,7 +485,7 @@ __global__ void __launch_bounds__(416) conv1_wgrad_train(const Step s) {
         return;
     }
     const size_t row = (size_t)sel * BS + b;
-    const float* img = s.X + (size_t)sample_index(s, lo, b) * 784;
+    const float* img = s.X + (size_t)sample_index(s, sel, lo, b) * 784;
     for (int i = tid; i < 32 * XS1; i += 416) xs[i] = 0.f;
     __syncthreads();
     for (int i = tid; i < 784; i += 416) {
@@ -699,7 +699,7 @@ extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const i
                                       int batch_index, int batch_size, float* params, float* moment, int nd,
                                       int n_classes, float lr, float momentum, float p_drop,
                                       unsigned long long seed, int round, const int* round_dev, void* workspace,
-                                      int conv2_mode, cudaStream_t stream) {
+                                      int conv2_mode, unsigned long long shuffle_key, cudaStream_t stream) {
     QFX_ARG_CHECK(conv2_mode == 0 || conv2_mode == 1, QFX_ERR_BAD_ARG, "conv2_mode must be 0 (fp32) or 1 (tcgen05 bf16)");
     QFX_ARG_CHECK(batch_size >= 1 && batch_size <= BS, QFX_ERR_UNSUPPORTED,
                   "client-batched TinyCNN supports batch_size <= %d, got %d", BS, batch_size);
@@ -711,7 +711,7 @@ extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const i
     s.X = X; s.labels = labels; s.offsets = offsets; s.perm = perm; s.client_ids = client_ids;
     s.n_total = n_total; s.epoch = epoch; s.batch_index = batch_index; s.batch_size = batch_size;
     s.params = params; s.moment = moment; s.nd = nd; s.n_classes = n_classes;
-    s.lr = lr; s.momentum = momentum; s.p_drop = p_drop; s.seed = seed; s.round = round; s.round_dev = round_dev; s.conv2_mode = conv2_mode;
+    s.lr = lr; s.momentum = momentum; s.p_drop = p_drop; s.seed = seed; s.round = round; s.round_dev = round_dev; s.conv2_mode = conv2_mode; s.shuffle_key = shuffle_key;
     // many clients: two images per weight-gradient CTA (one wave of CTAs, half the partial sums)
     s.wgrad_ipc = (conv2_mode == 1 && n_selected >= 5) ? 2 : 1;
     carve(s, workspace, (size_t)n_selected);

@@ -31,6 +31,7 @@ struct Step {
     unsigned long long seed;
     int round;
     const int* round_dev;    // when non-null the round is read from device memory (CUDA-graph replays)
+    unsigned long long shuffle_key;  // non-zero and perm == null: keyed Feistel sample order
     // activations / workspaces, all [K_sel, ...]
     float* a1; unsigned char* i1;    // [K,32,16,14,14]
     float* a2; unsigned char* i2;    // [K,32,32,7,7]
@@ -84,9 +85,16 @@ __device__ __forceinline__ int batch_rows(const Step& s, int sel, int* seg_lo) {
     const int b0 = s.batch_index * s.batch_size;
     return max(0, min(s.batch_size, n_k - b0));
 }
-__device__ __forceinline__ int sample_index(const Step& s, int seg_lo, int b) {
+__device__ __forceinline__ int sample_index(const Step& s, int sel, int seg_lo, int b) {
     const int j = s.batch_index * s.batch_size + b;
-    return s.perm ? s.perm[(size_t)s.epoch * s.n_total + seg_lo + j] : seg_lo + j;
+    if (s.perm) return s.perm[(size_t)s.epoch * s.n_total + seg_lo + j];
+    if (s.shuffle_key == 0ull) return seg_lo + j;
+    // keyed Feistel order, fresh per (round, client, epoch); the round comes from device memory under graph replay
+    const int client = s.client_ids[sel];
+    const int n_k = s.offsets[client + 1] - seg_lo;
+    const unsigned long long rnd = (unsigned long long)(s.round_dev ? *s.round_dev : s.round);
+    return seg_lo + (int)feistel_perm((uint32_t)j, (uint32_t)n_k, key3(s.shuffle_key ^ (rnd << 20), (unsigned long long)client,
+                                                                      (unsigned long long)s.epoch));
 }
 
 

@@ -39,6 +39,7 @@ struct TrainArgs {
     float lr, beta1, beta2, eps;
     int grad_mode;            // 0 adjoint, 1 parameter shift
     int ring_offset_floats;   // where the CNOT-ring scratch starts in dynamic shared memory (set by the launcher)
+    unsigned long long shuffle_key;   // non-zero and perm == null: samples are visited in a keyed Feistel order
 };
 
 // Gradient sink: reduce over the whole warp (dead circuits contribute zero) and add into the warp's private
@@ -150,6 +151,7 @@ vqc_local_train_kernel(const TrainArgs a) {
     for (int e = 0; e < a.epochs; ++e) {
         epoch_loss = 0.f; epoch_correct = 0.f;
         const int* perm_e = a.perm ? a.perm + (size_t)e * a.n_total + seg_lo : nullptr;
+        const unsigned long long fkey = a.shuffle_key ? key3(a.shuffle_key, (unsigned long long)client, (unsigned long long)e) : 0ull;
         for (int bi = 0; bi < n_batches; ++bi) {
             const int b_lo = bi * a.batch_size;
             const int nb = min(a.batch_size, n_k - b_lo);
@@ -163,7 +165,8 @@ vqc_local_train_kernel(const TrainArgs a) {
                 const int j = ps * slots_all + slot;
                 const bool live = j < nb;
                 const int jj = live ? j : nb - 1;
-                const int sidx = perm_e ? perm_e[b_lo + jj] : (seg_lo + b_lo + jj);
+                const int sidx = perm_e ? perm_e[b_lo + jj]
+                                        : seg_lo + (fkey ? (int)feistel_perm((uint32_t)(b_lo + jj), (uint32_t)n_k, fkey) : b_lo + jj);
                 const int y = a.labels[sidx];
 
                 Sv<NQ, LB_> psi;
@@ -217,7 +220,8 @@ vqc_local_train_kernel(const TrainArgs a) {
                     const float sgn = (it & 1) ? -1.f : 1.f;
                     const int p = (it >> 1) % P;
                     const int j = (it >> 1) / P;
-                    const int sidx = perm_e ? perm_e[b_lo + j] : (seg_lo + b_lo + j);
+                    const int sidx = perm_e ? perm_e[b_lo + j]
+                                            : seg_lo + (fkey ? (int)feistel_perm((uint32_t)(b_lo + j), (uint32_t)n_k, fkey) : b_lo + j);
                     const int owner = (j % slots_all) / slots_cta;
                     const float* cot_src = cluster.map_shared_rank(scot, owner);
                     Sv<NQ, LB_> psi;
@@ -420,7 +424,7 @@ extern "C" int qfx_vqc_local_train(int n_qubits, int n_layers, int basis, int en
                                    int n_total, const float* params_in, const int* client_ids, int n_selected,
                                    float* params_out, float* stats_out, int epochs, int batch_size, int optimizer,
                                    float lr, float beta1, float beta2, float eps, int grad_mode, int cluster_size,
-                                   int lane_mode, cudaStream_t stream) {
+                                   int lane_mode, unsigned long long shuffle_key, cudaStream_t stream) {
     QFX_ARG_CHECK(n_qubits >= 1 && n_qubits <= 10, QFX_ERR_UNSUPPORTED, "n_qubits %d not in 1..10", n_qubits);
     QFX_ARG_CHECK(n_layers >= 1 && 2 * n_qubits * n_layers <= TR_MAX_P, QFX_ERR_TOO_LARGE, "too many parameters");
     QFX_ARG_CHECK(n_classes >= 1 && n_classes <= n_qubits && n_classes <= TR_MAX_C, QFX_ERR_BAD_ARG,
@@ -435,7 +439,7 @@ extern "C" int qfx_vqc_local_train(int n_qubits, int n_layers, int basis, int en
     a.angles = angles; a.labels = labels; a.offsets = offsets; a.perm = perm; a.n_total = n_total;
     a.params_in = params_in; a.client_ids = client_ids; a.params_out = params_out; a.stats_out = stats_out;
     a.epochs = epochs; a.batch_size = batch_size; a.opt = optimizer; a.lr = lr; a.beta1 = beta1; a.beta2 = beta2;
-    a.eps = eps; a.grad_mode = grad_mode;
+    a.eps = eps; a.grad_mode = grad_mode; a.shuffle_key = shuffle_key;
     return dispatch_nq2<TrainLaunch>(n_qubits, a, n_selected, cluster_size, lane_mode, stream);
 }
 

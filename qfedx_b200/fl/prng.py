@@ -41,3 +41,48 @@ def uniform_bits(seed: int, tag: int, a: int, b: int, n: int) -> np.ndarray:
     """float64 [n] uniforms in [0,1) from the shared stream (client sampling, dropouts)."""
     k = key3(_U(seed) ^ _U(tag), a, b)
     return (stream_at(k, np.arange(n, dtype=_U)) >> _U(11)).astype(np.float64) / float(1 << 53)
+
+
+def _feistel_round(x: int, k: int) -> int:
+    x = (x ^ k) & 0xFFFFFFFF
+    x ^= x >> 16
+    x = (x * 0x85EBCA6B) & 0xFFFFFFFF
+    x ^= x >> 13
+    x = (x * 0xC2B2AE35) & 0xFFFFFFFF
+    return x ^ (x >> 16)
+
+
+def feistel_permutation(n: int, key: int) -> np.ndarray:
+    """Host mirror of feistel_perm (csrc/common.cuh): the keyed permutation of [0, n) that the training kernels
+    use to visit a client's samples in a fresh order every epoch without storing a permutation."""
+    if n <= 1:
+        return np.zeros(n, dtype=np.int64)
+    bits = 1
+    while (1 << bits) < n:
+        bits += 1
+    a = bits >> 1
+    b = bits - a
+    key &= (1 << 64) - 1
+    k0, k1 = key & 0xFFFFFFFF, key >> 32
+    out = np.empty(n, dtype=np.int64)
+    for j in range(n):
+        x = j
+        while True:
+            l, r = x & ((1 << a) - 1), x >> a
+            la, lb = a, b
+            for rnd in range(4):
+                k = ((k1 if rnd & 1 else k0) + 0x9E3779B9 * rnd) & 0xFFFFFFFF
+                f = _feistel_round(r, k) & ((1 << la) - 1)
+                l, r = r, l ^ f
+                la, lb = lb, la
+            x = (r << la) | l
+            if x < n:
+                break
+        out[j] = x
+    return out
+
+
+def shuffle_key(seed: int, rnd: int) -> int:
+    """Non-zero 64-bit key of the sample shuffle of one round."""
+    k = int(key3(_U(seed) ^ _U(0x5348554646), rnd, 0))
+    return k or 1

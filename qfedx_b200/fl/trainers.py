@@ -115,13 +115,16 @@ class VQCFusedTrainer:
     def __init__(self, model: VQC, data: FederatedDataset, epochs: int = 5, batch_size: int = 32,
                  lr: float = 0.05, optimizer: str = "adam", momentum: float = 0.9, betas=(0.9, 0.999),
                  eps: float = 1e-8, grad_method: str = "adjoint", cluster_size: int = 0, shuffle: bool = True,
-                 generator=None, lane_mode: str = "latency"):
+                 generator=None, lane_mode: str = "latency", shuffle_mode: str = "feistel", seed: int = 0):
         if model.encoding != "angle":
             raise ValueError("the fused trainer takes angle-encoded features")
         self.model, self.data = model, data
         self.epochs, self.batch_size, self.lr = epochs, batch_size, lr
         self.optimizer, self.momentum, self.betas, self.eps = optimizer, momentum, betas, eps
         self.grad_method, self.shuffle, self.generator = grad_method, shuffle, generator
+        # 'feistel': the kernel derives each epoch's sample order from a keyed permutation (no array, no sort);
+        # 'array': one device sort per round produces explicit permutations
+        self.shuffle_mode, self.seed = shuffle_mode, seed
         self.n_wrap = model.n_angle_params
         self.cuda = data.device.type == "cuda"
         self.launches = 0
@@ -167,7 +170,10 @@ class VQCFusedTrainer:
         K = sel.numel()
         out = torch.empty(K, self.dim, device=self.angles.device, dtype=torch.float32)
         stats = torch.empty(K, 2, device=self.angles.device, dtype=torch.float32)
-        perm = self.data.epoch_permutations(self.epochs, self.generator) if self.shuffle else None
+        from .prng import shuffle_key
+        use_array = self.shuffle and self.shuffle_mode == "array"
+        perm = self.data.epoch_permutations(self.epochs, self.generator) if use_array else None
+        skey = shuffle_key(self.seed, rnd) if (self.shuffle and not use_array) else 0
         beta1 = self.momentum if self.optimizer == "sgd" else self.betas[0]
         g = global_flat.contiguous().float()
         _lib.call("qfx_vqc_local_train", _lib.c_int(m.n_qubits), _lib.c_int(m.n_layers), _lib.c_int(BASIS[m.basis]),
@@ -178,7 +184,7 @@ class VQCFusedTrainer:
                   _lib.c_int(OPTIMIZERS[self.optimizer]), _lib.c_float(self.lr), _lib.c_float(beta1),
                   _lib.c_float(self.betas[1]), _lib.c_float(self.eps),
                   _lib.c_int(0 if self.grad_method == "adjoint" else 1), _lib.c_int(self.cluster_size),
-                  _lib.c_int(self.lane_mode), _lib.stream_ptr())
+                  _lib.c_int(self.lane_mode), _lib.c_u64(skey), _lib.stream_ptr())
         self.launches += 1
         self._last_stats = stats
         return out, {"train_stats": stats}

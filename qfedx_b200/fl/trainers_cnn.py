@@ -22,7 +22,7 @@ KERNELS_PER_STEP = 8
 class TinyCNNBatchedTrainer:
     def __init__(self, model: TinyCNN, data: FederatedDataset, epochs: int = 5, batch_size: int = 32,
                  lr: float = 0.01, momentum: float = 0.9, p_drop: float = 0.5, shuffle: bool = True, seed: int = 0,
-                 use_graph: bool = True, generator=None, conv2: str = "tcgen05"):
+                 use_graph: bool = True, generator=None, conv2: str = "tcgen05", shuffle_mode: str = "array"):
         if data.device.type != "cuda":
             raise _lib.QfxError("TinyCNNBatchedTrainer runs on CUDA only; use TorchLocalTrainer on CPU")
         if batch_size > 32:
@@ -30,6 +30,9 @@ class TinyCNNBatchedTrainer:
         self.model, self.data = model, data
         self.epochs, self.batch_size, self.lr, self.momentum, self.p_drop = epochs, batch_size, lr, momentum, p_drop
         self.shuffle, self.seed, self.use_graph, self.generator = shuffle, seed, use_graph, generator
+        # 'array': one device sort per round gives explicit permutations (fastest here: a single dependent load in the
+        # kernels); 'feistel': in-kernel keyed permutation, no array and nothing outside the CUDA graph
+        self.shuffle_mode = shuffle_mode
         self.n_classes = model.num_classes
         self.conv2_mode = {"fp32": 0, "tcgen05": 1}[conv2]   # tcgen05: bf16 operands, fp32 accumulate
         self.n_wrap = 0
@@ -55,6 +58,10 @@ class TinyCNNBatchedTrainer:
 
     def load_flat(self, flat: torch.Tensor) -> None:
         self.model.load_state_dict(unflatten_state(flat[: self.dim], self._template))
+
+    def _shuffle_key(self) -> int:
+        from .prng import shuffle_key
+        return shuffle_key(self.seed, 0) if (self.shuffle and self.shuffle_mode == "feistel") else 0
 
     def upload(self, host_X: torch.Tensor, host_y: torch.Tensor) -> None:
         """Refresh the resident dataset from (pinned) host memory - the per-round host->device copy
@@ -108,12 +115,13 @@ class TinyCNNBatchedTrainer:
                           _lib.c_int(self.n_classes), _lib.c_float(self.lr), _lib.c_float(self.momentum),
                           _lib.c_float(self.p_drop), _lib.c_u64(self.seed), _lib.c_int(rnd), _lib.ptr(self._round_dev),
                           _lib.ptr(st["ws"]),
-                          _lib.c_int(self.conv2_mode), _lib.stream_ptr(), launches=KERNELS_PER_STEP)
+                          _lib.c_int(self.conv2_mode), _lib.c_u64(self._shuffle_key()), _lib.stream_ptr(),
+                          launches=KERNELS_PER_STEP)
 
     def train(self, global_flat: torch.Tensor, selected, rnd: int):
         sel = [int(k) for k in selected]
         st = self._state_for(tuple(sel), sel)
-        if self.shuffle:
+        if self.shuffle and self.shuffle_mode == "array":
             new_perm = self.data.epoch_permutations(self.epochs, self.generator)
             if self._perm is None:
                 self._perm = new_perm

@@ -189,3 +189,12 @@ def test_spsa_trainer_runs():
     tr = TorchLocalTrainer(m, data, epochs=1, batch_size=16, lr=0.05, optimizer="adam", grad_estimator="spsa")
     out, stats = tr.train(tr.global_flat(), [0, 1], 0)
     assert out.shape == (2, tr.dim) and not torch.allclose(out[0], tr.global_flat())
+
+
+def test_feistel_permutation_is_a_keyed_bijection():
+    for n in (1, 2, 3, 7, 32, 33, 100, 1106, 4190):
+        p = prng.feistel_permutation(n, 12345)
+        assert sorted(p.tolist()) == list(range(n))
+    a, b = prng.feistel_permutation(500, 1), prng.feistel_permutation(500, 2)
+    assert not np.array_equal(a, b)
+    assert np.abs(np.corrcoef(np.arange(500), a)[0, 1]) < 0.2          # looks shuffled

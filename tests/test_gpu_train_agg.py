@@ -135,3 +135,23 @@ def test_dp_noise_statistics():
     assert torch.equal(res2.new_global, upd)                                 # keyed, reproducible
     res3 = fedavg_aggregate(cp, glob, w, mode="delta", clip=C, sigma=sigma, seed=3, rnd=2)
     assert not torch.equal(res3.new_global, upd)
+
+
+def test_device_feistel_matches_host_and_fused_shuffle_uses_every_sample():
+    import ctypes
+    from qfedx_b200.fl import prng
+    from qfedx_b200.ops import _lib
+    for n, key in ((1106, 99), (33, 7), (4190, 2 ** 63 + 5)):
+        out = torch.empty(n, dtype=torch.int32, device="cuda")
+        _lib.call("qfx_debug_feistel", _lib.c_int(n), _lib.c_u64(key), _lib.ptr(out), _lib.stream_ptr())
+        np.testing.assert_array_equal(out.cpu().numpy(), prng.feistel_permutation(n, key))
+    # one epoch with batch = whole client: shuffled and unshuffled training must agree (order-independent mean)
+    clients = _clients(2, 30, 4, 2, seed=5)
+    data = FederatedDataset.from_clients(clients, "cuda")
+    m = VQC(4, 1, 2).cuda()
+    g0 = m.flat_params().cuda()
+    a = VQCFusedTrainer(m, data, 1, 64, 0.05, "sgd", shuffle=False)
+    b = VQCFusedTrainer(m, data, 1, 64, 0.05, "sgd", shuffle=True, shuffle_mode="feistel", seed=3)
+    oa, _ = a.train(g0, [0, 1], 0)
+    ob, _ = b.train(g0, [0, 1], 0)
+    np.testing.assert_allclose(oa.cpu().numpy(), ob.cpu().numpy(), atol=1e-5)
