@@ -657,7 +657,7 @@ extern "C" int qfx_tinycnn_workspace_bytes(int n_selected, size_t* bytes) {
     size_t tot = 0;
     auto add = [&](size_t n) { tot += (n + 255) & ~(size_t)255; };
     add(K * BS * 3136 * 4); add(K * BS * 3136); add(K * BS * 1568 * 4); add(K * BS * 1568);
-    add(K * FC1_SLICES * BS * 64 * 4); add(K * BS * 64 * 4); add(K * BS * 64 * 4);
+    add(K * FC1_SLICES * BS * 64 * 4);
     add(K * BS * 32 * 196 * 4); add(K * BS * 3136 * 4); add(K * BS * NCONV * 4); add(K * 12800 * 4); add(K * 12800 * 4); add(K * 12800 * 2); add(K * 12800 * 2); add(K * HEAD_GRAD_STRIDE * 4);
     add(K * 2 * 4);
     *bytes = tot;
@@ -670,7 +670,6 @@ static void carve(Step& s, void* workspace, size_t K) {
     s.a1 = (float*)take(K * BS * 3136 * 4); s.i1 = (unsigned char*)take(K * BS * 3136);
     s.a2 = (float*)take(K * BS * 1568 * 4); s.i2 = (unsigned char*)take(K * BS * 1568);
     s.fc1_part = (float*)take(K * FC1_SLICES * BS * 64 * 4);
-    s.h1 = (float*)take(K * BS * 64 * 4); s.dh1 = (float*)take(K * BS * 64 * 4);
     s.g2 = (float*)take(K * BS * 32 * 196 * 4); s.da1 = (float*)take(K * BS * 3136 * 4);
     s.conv_part = (float*)take(K * BS * NCONV * 4);
     s.w2f = (float*)take(K * 12800 * 4); s.w2b = (float*)take(K * 12800 * 4);

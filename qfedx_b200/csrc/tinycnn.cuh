@@ -36,8 +36,6 @@ struct Step {
     float* a1; unsigned char* i1;    // [K,32,16,14,14]
     float* a2; unsigned char* i2;    // [K,32,32,7,7]
     float* fc1_part;                 // [K,16,32,64]
-    float* h1;                       // [K,32,64]
-    float* dh1;                      // [K,32,64]
     float* g2;                       // [K,32,32,14,14]
     float* da1;                      // [K,32,16,14,14]
     float* conv_part;                // [K,32,NCONV]

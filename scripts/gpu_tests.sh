@@ -1,4 +1,6 @@
 #!/bin/bash
+# One-GPU validation on the B200 box: gpurun --timeout 3000 -- 'bash scripts/gpu_tests.sh'
+# full GPU test suite, smoke(), the default benchmark (both arms) - logs under gpurun_out/.
 mkdir -p gpurun_out
 timeout 1500 python -m pytest tests -m gpu -x -q --timeout 300 > gpurun_out/pytest_gpu_full.log 2>&1; echo "full rc=$?"; tail -4 gpurun_out/pytest_gpu_full.log | cut -c1-300
 timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/smoke.log | cut -c1-300
