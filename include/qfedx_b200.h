@@ -116,7 +116,8 @@ int qfx_fedavg_fused_static(const float* client_params, const float* global_in, 
  * the partial sum is pushed into slot [rank] of every rank's receive buffer with peer stores over
  * NVLink, flags are released/acquired at system scope, and every rank applies the same update.
  * recv_slots[r] / flags[r] are device-visible pointers to rank r's buffers ([world][dim] int64 and
- * [world] u32).  epoch must increase every call; alternate two slot sets between calls. */
+ * [world] u32), each slot array 16-byte aligned.  epoch must increase every call; alternate two slot sets
+ * between calls. */
 int qfx_fedavg_fused_multi(const float* client_params, const float* global_in, float* global_out,
                            const float* weights, const int* participate, const int* client_gids, int k_local,
                            int k_global, int dim, int mode, int n_wrap, float clip, float sigma, float server_lr,

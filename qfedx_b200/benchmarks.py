@@ -54,7 +54,9 @@ def torch_baseline_ratio(n=8, L=6, B=4096):
     return {"batch": B, "ours_ms": ours, "torch_ms": torch_ms, "speedup": torch_ms / ours}
 
 
-def aggregation_latency(K=64, D=102, secagg=False):
+def aggregation_latency(K=64, D=102, secagg=False, mode="delta", clip=1.0, sigma=0.5, iters=50):
+    """K7 latency and the HBM traffic it implies: weights mode reads K*D once; delta mode with a clip reads the
+    client rows twice (norm sweep, then the weighted sum) plus the global vector twice, and writes D."""
     from .ops.aggregate import fedavg_aggregate
     dev = torch.device("cuda")
     cp = torch.randn(K, D, device=dev)
@@ -62,9 +64,12 @@ def aggregation_latency(K=64, D=102, secagg=False):
     w = torch.rand(K, device=dev) + 1
     out = torch.empty_like(g)
     scratch = torch.empty(K, device=dev)
-    ms = _time_ms(lambda: fedavg_aggregate(cp, g, w, mode="delta", clip=1.0, sigma=0.5, secagg=secagg, out=out,
-                                           scratch=scratch), iters=50)
-    return {"K": K, "D": D, "secagg": secagg, "ms": ms, "bytes": K * D * 4, "gbps": K * D * 4 / ms / 1e6}
+    ms = _time_ms(lambda: fedavg_aggregate(cp, g, w, mode=mode, clip=clip, sigma=sigma, secagg=secagg, out=out,
+                                           scratch=scratch), iters=iters)
+    sweeps = 2 if (mode == "delta" and clip > 0) else 1
+    traffic = 4 * (sweeps * K * D + (sweeps if mode == "delta" else 0) * D + D)
+    return {"K": K, "D": D, "secagg": secagg, "mode": mode, "clip": clip, "sigma": sigma, "ms": ms,
+            "bytes": K * D * 4, "hbm_traffic_bytes": traffic, "hbm_gbps": traffic / ms / 1e6}
 
 
 def unitary_gemm_throughput(n=8, L=6, B=1 << 15):
@@ -120,7 +125,9 @@ def aux_measurements(args=None, rank=0, world=1, local=0, skip=None):
     out["vs_torch_baseline_8q"] = torch_baseline_ratio(8, 6, 2048)
     out["agg_vqc"] = aggregation_latency(64, 102)
     out["agg_tinycnn_dp_secagg"] = aggregation_latency(8, 113859, True)
-    out["agg_1e8"] = aggregation_latency(4, 25_000_000)
+    out["agg_1e8_dp"] = aggregation_latency(4, 25_000_000, iters=10)
+    out["agg_1e8_clip"] = aggregation_latency(4, 25_000_000, sigma=0.0, iters=10)
+    out["agg_1e8_weights"] = aggregation_latency(4, 25_000_000, mode="weights", clip=0.0, sigma=0.0, iters=10)
     out["unitary_gemm_8q"] = unitary_gemm_throughput(8, 6, 1 << 15)
     out["sv20_pass_engine"] = large_state_throughput(20, 2, 16)
     return out

@@ -63,38 +63,146 @@ __device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
     return v;
 }
 
-__device__ __forceinline__ float delta_at(const AggArgs& a, int k, int d, float g) {
-    float x = a.client_params[(size_t)k * a.dim + d];
+__device__ __forceinline__ float delta_of(const AggArgs& a, float x, int d, float g) {
     if (a.mode == 0) return x;
     x -= g;
     return d < a.n_wrap ? wrap_pi(x) : x;
 }
 
+constexpr int AGG_KCHUNK = 8;   // clients whose norms are accumulated in registers in one sweep
+
+// Dynamic shared memory: [mask keys u64 k_local*k_global (optional)] [noise keys u64 k_local]
+// [coef f32 k_local] [wnoise f32 k_local] [gid i32 k_local] [participates u8 k_global]
+__host__ __device__ inline size_t agg_smem_bytes(int k_local, int k_global, bool mask_keys) {
+    size_t b = (mask_keys ? (size_t)k_local * k_global * 8 : 0) + (size_t)k_local * (8 + 4 + 4 + 4) + (size_t)k_global;
+    return (b + 15) & ~(size_t)15;
+}
+
+// VEC consecutive floats per access: one 16-byte transaction when the row pitch allows it, else scalars.
+template <int VEC> struct VecIO;
+template <> struct VecIO<1> {
+    static __device__ __forceinline__ void ldg(const float* p, float (&x)[1]) { x[0] = __ldg(p); }
+    static __device__ __forceinline__ void ld(const float* p, float (&x)[1]) { x[0] = *p; }
+    static __device__ __forceinline__ void ldcv(const float* p, float (&x)[1]) { x[0] = __ldcv(p); }
+    static __device__ __forceinline__ void ldcv(const long long* p, long long (&x)[1]) { x[0] = __ldcv(p); }
+    static __device__ __forceinline__ void st(float* p, const float (&x)[1]) { *p = x[0]; }
+    static __device__ __forceinline__ void st(long long* p, const unsigned long long (&x)[1]) { *p = (long long)x[0]; }
+};
+template <> struct VecIO<4> {
+    static __device__ __forceinline__ void ldg(const float* p, float (&x)[4]) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(p));
+        x[0] = v.x; x[1] = v.y; x[2] = v.z; x[3] = v.w;
+    }
+    static __device__ __forceinline__ void ld(const float* p, float (&x)[4]) {
+        const float4 v = *reinterpret_cast<const float4*>(p);
+        x[0] = v.x; x[1] = v.y; x[2] = v.z; x[3] = v.w;
+    }
+    static __device__ __forceinline__ void ldcv(const float* p, float (&x)[4]) {
+        const float4 v = __ldcv(reinterpret_cast<const float4*>(p));
+        x[0] = v.x; x[1] = v.y; x[2] = v.z; x[3] = v.w;
+    }
+    static __device__ __forceinline__ void ldcv(const long long* p, long long (&x)[4]) {
+        const longlong2 a = __ldcv(reinterpret_cast<const longlong2*>(p));
+        const longlong2 b = __ldcv(reinterpret_cast<const longlong2*>(p) + 1);
+        x[0] = a.x; x[1] = a.y; x[2] = b.x; x[3] = b.y;
+    }
+    static __device__ __forceinline__ void st(float* p, const float (&x)[4]) {
+        *reinterpret_cast<float4*>(p) = make_float4(x[0], x[1], x[2], x[3]);
+    }
+    static __device__ __forceinline__ void st(long long* p, const unsigned long long (&x)[4]) {
+        reinterpret_cast<longlong2*>(p)[0] = make_longlong2((long long)x[0], (long long)x[1]);
+        reinterpret_cast<longlong2*>(p)[1] = make_longlong2((long long)x[2], (long long)x[3]);
+    }
+};
+
+// VEC: floats per access (4 needs dim % 4 == 0 and 16-byte aligned bases).  UNR: independent accesses per
+// thread per trip (with the one-client-ahead prefetch in phase 2: 2 x UNR x VEC x 4 bytes in flight).
+template <int VEC, int UNR, bool FIXED>
 __global__ void __launch_bounds__(AGG_THREADS)
-fedavg_fused_kernel(const AggArgs a) {
+fedavg_fused_kernel(const AggArgs a, const int mask_keys_in_smem) {
+    using IO = VecIO<VEC>;
     cg::grid_group grid = cg::this_grid();
-    extern __shared__ float coef[];  // [k_local] w_k/sum(w) * clip scale, 0 for non-participants
-    __shared__ float red[AGG_THREADS / 32];
+    extern __shared__ __align__(16) unsigned char agg_smem[];
+    uint64_t* mkey = reinterpret_cast<uint64_t*>(agg_smem);
+    uint64_t* nkey = mkey + (mask_keys_in_smem ? (size_t)a.k_local * a.k_global : 0);
+    float* coef = reinterpret_cast<float*>(nkey + a.k_local);   // w_k/sum(w) * clip scale, 0 for non-participants
+    float* wnoise = coef + a.k_local;                            // w_k/sum(w) * sigma * C
+    int* gid = reinterpret_cast<int*>(wnoise + a.k_local);
+    unsigned char* gpart = reinterpret_cast<unsigned char*>(gid + a.k_local);
+    __shared__ float red[AGG_KCHUNK][AGG_THREADS / 32];
     const int tid = threadIdx.x;
-    const int gstride = gridDim.x * AGG_THREADS;
+    const int nvec = a.dim / VEC;                                // VEC == 4 only when dim % 4 == 0
+    const int gstride = gridDim.x * AGG_THREADS;                 // in vectors
     const int g0 = blockIdx.x * AGG_THREADS + tid;
     const bool need_norm = a.mode == 1 && (a.clip > 0.f || a.norms_out != nullptr);
+    const float noise_std = (a.mode == 1 && a.clip > 0.f) ? a.sigma * a.clip : 0.f;
 
-    // ---- phase 1: squared norms ----------------------------------------------------------
+    // ---- per-block tables that do not depend on the norms: participation, ids, RNG keys ----------
+    for (int j = tid; j < a.k_global; j += AGG_THREADS) gpart[j] = (a.participate == nullptr || a.participate[j]) ? 1 : 0;
+    for (int k = tid; k < a.k_local; k += AGG_THREADS) {
+        const int gk = a.client_gids ? a.client_gids[k] : k;
+        gid[k] = gk;
+        nkey[k] = key3(a.seed ^ TAG_NOISE, (uint64_t)a.round, (uint64_t)gk);
+    }
+    if (FIXED && mask_keys_in_smem) {
+        for (int i = tid; i < a.k_local * a.k_global; i += AGG_THREADS) {
+            const int k = i / a.k_global, j = i - k * a.k_global;
+            const int gk = a.client_gids ? a.client_gids[k] : k;
+            const int lo = min(gk, j), hi = max(gk, j);
+            mkey[i] = key3(a.seed ^ TAG_MASK, (uint64_t)a.round, (uint64_t)lo * (uint64_t)a.k_global + (uint64_t)hi);
+        }
+    }
+
+    // ---- phase 1: squared norms, AGG_KCHUNK clients per sweep over the vector ---------------------
     if (need_norm) {
-        for (int k = 0; k < a.k_local; ++k) {
-            float acc = 0.f;
-            for (int d = g0; d < a.dim; d += gstride) {
-                const float v = delta_at(a, k, d, a.global_in[d]);
-                acc += v * v;
+        for (int kc = 0; kc < a.k_local; kc += AGG_KCHUNK) {
+            const int kn = min(AGG_KCHUNK, a.k_local - kc);
+            float acc[AGG_KCHUNK];
+#pragma unroll
+            for (int kk = 0; kk < AGG_KCHUNK; ++kk) acc[kk] = 0.f;
+            for (int v0 = g0; v0 < nvec; v0 += UNR * gstride) {
+                float g[UNR][VEC];
+#pragma unroll
+                for (int u = 0; u < UNR; ++u) {
+                    const int v = min(v0 + u * gstride, nvec - 1);   // clamped lanes re-read a valid vector
+                    IO::ld(a.global_in + (size_t)v * VEC, g[u]);
+                }
+#pragma unroll
+                for (int kk = 0; kk < AGG_KCHUNK; ++kk) {
+                    if (kk < kn) {
+                        const float* row = a.client_params + (size_t)(kc + kk) * a.dim;
+                        float x[UNR][VEC];
+#pragma unroll
+                        for (int u = 0; u < UNR; ++u) {
+                            const int v = min(v0 + u * gstride, nvec - 1);
+                            IO::ldg(row + (size_t)v * VEC, x[u]);
+                        }
+#pragma unroll
+                        for (int u = 0; u < UNR; ++u) {
+                            const int v = v0 + u * gstride;
+                            if (v < nvec) {
+#pragma unroll
+                                for (int e = 0; e < VEC; ++e) {
+                                    const float dl = delta_of(a, x[u][e], v * VEC + e, g[u][e]);
+                                    acc[kk] += dl * dl;
+                                }
+                            }
+                        }
+                    }
+                }
             }
-            acc = warp_sum(acc);
-            if ((tid & 31) == 0) red[tid >> 5] = acc;
+#pragma unroll
+            for (int kk = 0; kk < AGG_KCHUNK; ++kk) {
+                const float v = warp_sum(acc[kk]);
+                if ((tid & 31) == 0) red[kk][tid >> 5] = v;
+            }
             __syncthreads();
             if (tid < 32) {
-                float v = tid < AGG_THREADS / 32 ? red[tid] : 0.f;
-                v = warp_sum(v);
-                if (tid == 0 && v != 0.f) atomicAdd(a.scratch + k, v);
+                for (int kk = 0; kk < kn; ++kk) {
+                    float v = tid < AGG_THREADS / 32 ? red[kk][tid] : 0.f;
+                    v = warp_sum(v);
+                    if (tid == 0 && v != 0.f) atomicAdd(a.scratch + kc + kk, v);
+                }
             }
             __syncthreads();
         }
@@ -102,13 +210,15 @@ fedavg_fused_kernel(const AggArgs a) {
     }
 
     // ---- per-client coefficients -----------------------------------------------------------
+    __syncthreads();
     float wsum = 0.f;
     for (int j = 0; j < a.k_global; ++j)
-        if (a.participate == nullptr || a.participate[j]) wsum += a.weights[j];
+        if (gpart[j]) wsum += a.weights[j];
     const float inv_wsum = wsum > 0.f ? 1.f / wsum : 0.f;
     for (int k = tid; k < a.k_local; k += AGG_THREADS) {
-        const int gk = a.client_gids ? a.client_gids[k] : k;
-        float c = (a.participate == nullptr || a.participate[gk]) ? a.weights[gk] * inv_wsum : 0.f;
+        const int gk = gid[k];
+        float c = gpart[gk] ? a.weights[gk] * inv_wsum : 0.f;
+        wnoise[k] = a.weights[gk] * inv_wsum * noise_std;
         if (need_norm) {
             const float nrm = sqrtf(a.scratch[k]);
             if (blockIdx.x == 0 && a.norms_out) a.norms_out[k] = nrm;
@@ -118,47 +228,95 @@ fedavg_fused_kernel(const AggArgs a) {
     }
     __syncthreads();
 
-    const float noise_std = (a.mode == 1 && a.clip > 0.f) ? a.sigma * a.clip : 0.f;
-    const bool fixed = a.secagg != 0;
-
     // ---- phase 2: weighted, noised, masked sum per element -----------------------------------
-    for (int d = g0; d < a.dim; d += gstride) {
-        const float g = a.global_in[d];
-        float facc = 0.f;
-        unsigned long long iacc = 0ull;
-        for (int k = 0; k < a.k_local; ++k) {
-            const int gk = a.client_gids ? a.client_gids[k] : k;
-            const bool part = a.participate == nullptr || a.participate[gk];
-            if (!part) continue;
-            float v = coef[k] * delta_at(a, k, d, g);
-            if (noise_std > 0.f) {
-                const uint64_t nk = key3(a.seed ^ TAG_NOISE, (uint64_t)a.round, (uint64_t)gk);
-                v += a.weights[gk] * inv_wsum * noise_std * normal_from_bits(stream_at(nk, (uint64_t)d));
-            }
-            if (!fixed) {
-                facc += v;
-            } else {
-                unsigned long long y = (unsigned long long)__double2ll_rn((double)v * FIXED_SCALE);
-                for (int j = 0; j < a.k_global; ++j) {
-                    if (j == gk || !(a.participate == nullptr || a.participate[j])) continue;
-                    const int lo = min(gk, j), hi = max(gk, j);
-                    const uint64_t mk = key3(a.seed ^ TAG_MASK, (uint64_t)a.round,
-                                             (uint64_t)lo * (uint64_t)a.k_global + (uint64_t)hi);
-                    const uint64_t m = stream_at(mk, (uint64_t)d);
-                    y += (gk < j) ? m : (0ull - m);
-                }
-                if (a.masked_out) a.masked_out[(size_t)k * a.dim + d] = (long long)y;
-                iacc += y;
+    for (int v0 = g0; v0 < nvec; v0 += UNR * gstride) {
+        float g[UNR][VEC], facc[UNR][VEC];
+        unsigned long long iacc[UNR][VEC];
+        int vi[UNR];
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+            vi[u] = min(v0 + u * gstride, nvec - 1);
+            IO::ld(a.global_in + (size_t)vi[u] * VEC, g[u]);
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) {
+                facc[u][e] = 0.f;
+                iacc[u][e] = 0ull;
             }
         }
-        if (a.world == 1) {
-            const float upd = fixed ? (float)((double)(long long)iacc / FIXED_SCALE) : facc;
-            a.global_out[d] = (a.mode == 1) ? g + a.server_lr * upd : upd;
-        } else {
-            // push this rank's partial into slot [rank] of every rank (self included)
-            for (int r = 0; r < a.world; ++r) {
-                if (fixed) a.recv_slots[r][(size_t)a.rank * a.dim + d] = (long long)iacc;
-                else reinterpret_cast<float*>(a.recv_slots[r])[(size_t)a.rank * a.dim + d] = facc;
+        // first participating client, then a one-client-ahead prefetch of the rows
+        int k = 0;
+        while (k < a.k_local && !gpart[gid[k]]) ++k;
+        float xn[UNR][VEC];
+        if (k < a.k_local) {
+#pragma unroll
+            for (int u = 0; u < UNR; ++u) IO::ldg(a.client_params + (size_t)k * a.dim + (size_t)vi[u] * VEC, xn[u]);
+        }
+        while (k < a.k_local) {
+            float x[UNR][VEC];
+#pragma unroll
+            for (int u = 0; u < UNR; ++u)
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) x[u][e] = xn[u][e];
+            int kn = k + 1;
+            while (kn < a.k_local && !gpart[gid[kn]]) ++kn;
+            if (kn < a.k_local) {
+#pragma unroll
+                for (int u = 0; u < UNR; ++u) IO::ldg(a.client_params + (size_t)kn * a.dim + (size_t)vi[u] * VEC, xn[u]);
+            }
+            const int gk = gid[k];
+            const float ck = coef[k], wn = wnoise[k];
+            const uint64_t nk = nkey[k];
+#pragma unroll
+            for (int u = 0; u < UNR; ++u) {
+                if (v0 + u * gstride >= nvec) continue;       // clamped duplicate of the last vector: no work
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) {
+                    const int d = vi[u] * VEC + e;
+                    float v = ck * delta_of(a, x[u][e], d, g[u][e]);
+                    if (noise_std > 0.f) v += wn * normal_from_bits(stream_at(nk, (uint64_t)d));
+                    if constexpr (!FIXED) {
+                        facc[u][e] += v;
+                    } else {
+                        unsigned long long y = (unsigned long long)__double2ll_rn((double)v * FIXED_SCALE);
+                        for (int j = 0; j < a.k_global; ++j) {
+                            if (j == gk || !gpart[j]) continue;
+                            uint64_t mk;
+                            if (mask_keys_in_smem) {
+                                mk = mkey[(size_t)k * a.k_global + j];
+                            } else {
+                                const int lo = min(gk, j), hi = max(gk, j);
+                                mk = key3(a.seed ^ TAG_MASK, (uint64_t)a.round,
+                                          (uint64_t)lo * (uint64_t)a.k_global + (uint64_t)hi);
+                            }
+                            const uint64_t m = stream_at(mk, (uint64_t)d);
+                            y += (gk < j) ? m : (0ull - m);
+                        }
+                        if (a.masked_out) a.masked_out[(size_t)k * a.dim + d] = (long long)y;
+                        iacc[u][e] += y;
+                    }
+                }
+            }
+            k = kn;
+        }
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+            if (v0 + u * gstride >= nvec) continue;           // clamped duplicate: nothing to write
+            const size_t d = (size_t)vi[u] * VEC;
+            if (a.world == 1) {
+                float o[VEC];
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) {
+                    const float upd = FIXED ? (float)((double)(long long)iacc[u][e] / FIXED_SCALE)
+                                            : facc[u][e];
+                    o[e] = (a.mode == 1) ? g[u][e] + a.server_lr * upd : upd;
+                }
+                IO::st(a.global_out + d, o);
+            } else {
+                // push this rank's partial into slot [rank] of every rank (self included)
+                for (int r = 0; r < a.world; ++r) {
+                    if constexpr (FIXED) IO::st(a.recv_slots[r] + (size_t)a.rank * a.dim + d, iacc[u]);
+                    else IO::st(reinterpret_cast<float*>(a.recv_slots[r]) + (size_t)a.rank * a.dim + d, facc[u]);
+                }
             }
         }
     }
@@ -174,23 +332,41 @@ fedavg_fused_kernel(const AggArgs a) {
     }
     grid.sync();
     const long long* mine = a.recv_slots[a.rank];
-    for (int d = g0; d < a.dim; d += gstride) {
-        float upd;
-        if (fixed) {
-            unsigned long long s = 0ull;
-            for (int r = 0; r < a.world; ++r)
-                s += (unsigned long long)__ldcv(mine + (size_t)r * a.dim + d);
-            upd = (float)((double)(long long)s / FIXED_SCALE);
+    for (int v = g0; v < nvec; v += gstride) {
+        const size_t d = (size_t)v * VEC;
+        float upd[VEC];
+        if constexpr (FIXED) {
+            unsigned long long s[VEC];
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) s[e] = 0ull;
+            for (int r = 0; r < a.world; ++r) {
+                long long t[VEC];
+                IO::ldcv(mine + (size_t)r * a.dim + d, t);
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) s[e] += (unsigned long long)t[e];
+            }
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) upd[e] = (float)((double)(long long)s[e] / FIXED_SCALE);
         } else {
             const float* mf = reinterpret_cast<const float*>(mine);
-            float s = 0.f;
-            for (int r = 0; r < a.world; ++r) s += __ldcv(mf + (size_t)r * a.dim + d);
-            upd = s;
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) upd[e] = 0.f;
+            for (int r = 0; r < a.world; ++r) {
+                float t[VEC];
+                IO::ldcv(mf + (size_t)r * a.dim + d, t);
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) upd[e] += t[e];
+            }
         }
-        const float g = a.global_in[d];
-        a.global_out[d] = (a.mode == 1) ? g + a.server_lr * upd : upd;
+        float g[VEC], o[VEC];
+        IO::ld(a.global_in + d, g);
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) o[e] = (a.mode == 1) ? g[e] + a.server_lr * upd[e] : upd[e];
+        IO::st(a.global_out + d, o);
     }
 }
+
+using AggKernel = void (*)(const AggArgs, const int);
 
 static int g_num_sms = 0;
 
@@ -204,21 +380,40 @@ static int launch_fedavg(AggArgs& a, cudaStream_t stream) {
                   "bad rank/world");
     QFX_ARG_CHECK(a.world == 1 || (a.recv_slots && a.flags), QFX_ERR_BAD_ARG, "multi-GPU needs slots and flags");
     QFX_ARG_CHECK(a.scratch != nullptr, QFX_ERR_BAD_ARG, "scratch is required");
-    QFX_ARG_CHECK((size_t)a.k_local * sizeof(float) <= 160 * 1024, QFX_ERR_TOO_LARGE, "too many local clients");
     if (g_num_sms == 0) {
         int dev = 0;
         QFX_CUDA_TRY(cudaGetDevice(&dev));
         QFX_CUDA_TRY(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
     }
+    // pairwise mask keys are hashed once per block into shared memory when they fit
+    const size_t kSmemCap = 96 * 1024;
+    int mask_keys = a.secagg && agg_smem_bytes(a.k_local, a.k_global, true) <= 32 * 1024 ? 1 : 0;
+    const size_t smem = agg_smem_bytes(a.k_local, a.k_global, mask_keys != 0);
+    QFX_ARG_CHECK(smem <= kSmemCap, QFX_ERR_TOO_LARGE, "too many clients for one aggregation launch (%zu bytes of tables)", smem);
     if (a.k_local > 0) QFX_CUDA_TRY(cudaMemsetAsync(a.scratch, 0, sizeof(float) * a.k_local, stream));
-    const size_t smem = sizeof(float) * a.k_local;
-    if (smem > 48 * 1024)
-        QFX_CUDA_TRY(cudaFuncSetAttribute(fedavg_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int blocks = (a.dim + AGG_THREADS - 1) / AGG_THREADS;
-    const int cap = g_num_sms * 2;
+    // 16-byte accesses when every row starts on a 16-byte boundary
+    auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+    const bool vec4 = a.dim % 4 == 0 && al16(a.client_params) && al16(a.global_in) && al16(a.global_out);
+    const bool fixed = a.secagg != 0;
+    AggKernel kern = vec4 ? (fixed ? (AggKernel)fedavg_fused_kernel<4, 2, true> : (AggKernel)fedavg_fused_kernel<4, 2, false>)
+                          : (fixed ? (AggKernel)fedavg_fused_kernel<1, 4, true> : (AggKernel)fedavg_fused_kernel<1, 4, false>);
+    static bool attr_set[4] = {false, false, false, false};
+    const int which = (vec4 ? 2 : 0) + (fixed ? 1 : 0);
+    if (!attr_set[which]) {
+        QFX_CUDA_TRY(cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemCap));
+        attr_set[which] = true;
+    }
+    int occ = 0;
+    QFX_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)kern, AGG_THREADS, smem));
+    QFX_ARG_CHECK(occ >= 1, QFX_ERR_TOO_LARGE, "aggregation kernel does not fit on an SM");
+    // small vectors: as few CTAs as cover the vector (grid barriers get cheaper); large: fill the GPU
+    const int per_thread = vec4 ? 4 : 1;
+    long long blocks = ((long long)a.dim / per_thread + AGG_THREADS - 1) / AGG_THREADS;
+    const long long cap = (long long)g_num_sms * (occ > 6 ? 6 : occ);
     if (blocks > cap) blocks = cap;
-    void* params[] = {(void*)&a};
-    QFX_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)fedavg_fused_kernel, dim3(blocks), dim3(AGG_THREADS),
+    if (blocks < 1) blocks = 1;
+    void* params[] = {(void*)&a, (void*)&mask_keys};
+    QFX_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)kern, dim3((unsigned)blocks), dim3(AGG_THREADS),
                                              params, smem, stream));
     return 0;
 }

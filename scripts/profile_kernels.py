@@ -38,6 +38,10 @@ if which in ("all", "agg"):
     w = torch.rand(4, device=dev) + 1
     for _ in range(3):
         fedavg_aggregate(cp, g, w, mode="delta", clip=1.0)
+    for _ in range(3):
+        fedavg_aggregate(cp, g, w, mode="delta", clip=1.0, sigma=0.5)
+    for _ in range(3):
+        fedavg_aggregate(cp, g, w, mode="weights")
 if which in ("all", "large"):
     vqc = LargeVQC(20, 2)
     ang = torch.rand(16, 20, device=dev) * math.pi

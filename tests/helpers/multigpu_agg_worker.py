@@ -15,7 +15,7 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
     ok = True
-    for K, D, secagg, clip in [(16, 102, False, 0.0), (16, 113859, False, 0.7), (8, 5000, True, 0.7), (5, 300, True, 0.0)]:
+    for K, D, secagg, clip in [(16, 102, False, 0.0), (16, 4096, False, 0.7), (16, 113859, False, 0.7), (8, 5000, True, 0.7), (5, 300, True, 0.0)]:
         g = torch.Generator().manual_seed(1234 + K + D)                  # same stream on every rank
         glob = torch.randn(D, generator=g)
         cp_all = glob + 0.05 * torch.randn(K, D, generator=g) * (1 + torch.arange(K)[:, None])

@@ -93,7 +93,7 @@ def test_shuffled_permutations_are_per_client():
             assert sorted(seg.tolist()) == list(range(off[k], off[k + 1]))
 
 
-@pytest.mark.parametrize("K,D", [(4, 96), (8, 113859), (64, 102)])
+@pytest.mark.parametrize("K,D", [(4, 96), (8, 113859), (64, 102), (5, 70000), (3, 4099)])
 @pytest.mark.parametrize("mode,clip,secagg_on", [("weights", 0.0, False), ("delta", 0.0, False), ("delta", 0.7, False),
                                                  ("delta", 0.7, True)])
 def test_fused_aggregation_matches_reference(K, D, mode, clip, secagg_on):
