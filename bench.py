@@ -13,6 +13,10 @@ Configs (``--config``):
         clip + Gaussian noise inside the fused aggregation.
   vqc8  8-qubit 6-layer VQC, 64 clients, Dirichlet non-IID split (BASELINE.json config 3).
   vqc4  4-qubit 2-layer binary VQC, 4 clients (BASELINE.json config 1).
+  vqc20 20-qubit 2-layer VQC on the pass engine, 16 clients, parameter-shift gradients, secure-aggregation
+        masks (config 4); clients are spread over the GPUs.
+  vqc30 30-qubit VQC, ONE statevector sharded over all GPUs of the job (8 GiB at 1 GPU ... 1 GiB per GPU at 8),
+        8 clients, SPSA gradients (config 5); every rank walks the same clients in lockstep.
 The line's ``aux`` carries the secondary numbers measured in the same run.
 
 ``--impl reference`` runs the UNMODIFIED reference from baseline/_ref through its own
@@ -42,6 +46,12 @@ CFED = dict(clients=8, samples_per_client=4190, classes=3, epochs=5, batch=32, l
             clip=5.0, sigma=0.01)
 VQC8 = dict(clients=64, n_train=16760, classes=3, n_qubits=8, n_layers=6, epochs=5, batch=32, lr=0.05,
             alpha=0.5, test_n=3147)
+# configs 4 and 5: states too large for registers.  Sample counts are small because every optimizer step costs
+# S x (2P + 1) full statevector simulations (parameter shift) or 3 (SPSA).
+VQC20 = dict(clients=16, samples_per_client=4, classes=2, n_qubits=20, n_layers=2, epochs=1, batch=4, lr=0.05,
+             grad="param_shift", secagg=True, clip=1.0, test_n=16)
+VQC30 = dict(clients=8, samples_per_client=1, classes=2, n_qubits=30, n_layers=1, epochs=1, batch=1, lr=0.05,
+             grad="spsa", secagg=False, clip=0.0, test_n=2)
 VQC4 = dict(clients=4, n_train=11183, classes=2, n_qubits=4, n_layers=2, epochs=5, batch=32, lr=0.05, test_n=1991)
 
 
@@ -186,6 +196,75 @@ def run_vqc(cfg, name, args, rank, world, local):
                        "partition": "dirichlet(0.5)" if name == "vqc8" else "iid"})
 
 
+def run_large(cfg, name, args, rank, world, local):
+    """Configs 4 (vqc20: pass engine, clients spread over the ranks) and 5 (vqc30: one state sharded over the ranks)."""
+    from qfedx_b200.data import images_to_angles, synthetic_mnist
+    from qfedx_b200.fl import FederatedDataset, FederatedRunner, FLConfig
+    from qfedx_b200.fl.trainers_large import LargeVQCTrainer, PassBackend, ShardedBackend
+    from qfedx_b200.models import VQC
+    from qfedx_b200.ops import _lib
+    from qfedx_b200.ops.large import ansatz_gates
+    from qfedx_b200.parallel.runtime import make_aggregator
+    dev = torch.device("cuda", local)
+    n, L, K, per = cfg["n_qubits"], cfg["n_layers"], cfg["clients"], cfg["samples_per_client"]
+    X, y = synthetic_mnist(K * per, cfg["classes"], seed=0)
+    Xt, yt = synthetic_mnist(cfg["test_n"], cfg["classes"], seed=1)
+    A, At = images_to_angles(X, n), images_to_angles(Xt, n)
+    clients = [(A[k * per:(k + 1) * per], y[k * per:(k + 1) * per]) for k in range(K)]
+    sharded = name == "vqc30"
+    mine = list(range(K)) if sharded else split_clients(K, rank, world)
+    host = [(clients[k][0].float().contiguous(), clients[k][1].long().contiguous()) for k in mine]
+    data = FederatedDataset.from_clients(host, dev)
+    torch.manual_seed(0)                                   # same SPSA directions / orders on every rank
+    model = VQC(n, L, cfg["classes"]).to(dev)
+    if sharded and world > 1:
+        backend = ShardedBackend(n, L, world, rank, dev)
+    else:
+        backend = PassBackend(n, L)
+    trainer = LargeVQCTrainer(model, data, backend, cfg["epochs"], cfg["batch"], cfg["lr"], cfg["grad"])
+    all_sizes = torch.full((K,), float(per))
+    flc = FLConfig(num_rounds=10 ** 9, mode="delta", secagg=cfg["secagg"], clip=cfg["clip"], quiet=True)
+    agg = None if sharded else make_aggregator(rank, world, mine, all_sizes, trainer.dim, dev)
+    runner = FederatedRunner(trainer, flc, (At.to(dev), yt.to(dev)), aggregator=agg,
+                             client_gids=mine if agg is not None else None,
+                             global_weights=all_sizes if agg is not None else None)
+    result = {}
+
+    def step():
+        runner.run_round()
+        result["eval"] = runner.evaluate()
+
+    l0 = _lib.LAUNCH_COUNT
+    ms, clocks = timed_rounds(step, args.steps, args.warmup, world)
+    launches = (_lib.LAUNCH_COUNT - l0) // max(1, args.steps + args.warmup) * args.steps
+    hX = torch.cat([h[0] for h in host]).pin_memory()
+    hy = torch.cat([h[1] for h in host]).pin_memory()
+
+    def step_e2e():
+        data.X.copy_(hX, non_blocking=True)
+        data.y.copy_(hy, non_blocking=True)
+        runner.run_round()
+        result["eval"] = runner.evaluate()
+
+    e2e_ms, _ = timed_rounds(step_e2e, args.steps, 1, world)
+    # full-state simulations per round over the whole job, and the gate applications they contain
+    P = model.n_angle_params
+    steps_per_client = cfg["epochs"] * ((per + cfg["batch"] - 1) // cfg["batch"])
+    per_step = cfg["batch"] * ((1 + 2 * P) if cfg["grad"] == "param_shift" else 3)
+    sims = K * steps_per_client * per_step + cfg["test_n"]
+    n_gates = len(ansatz_gates(n, L))                      # feature map + ansatz
+    return dict(ms=ms, e2e_ms=e2e_ms, clocks=clocks, launches=launches,
+                h2d=(hX.numel() * 4 + hy.numel() * 8) * (1 if sharded else world), d2h=8,
+                model=f"VQC {n}q x {L} layers, {cfg['classes']} classes, "
+                      + ("state sharded over the job's GPUs (K6)" if sharded else "pass engine (K5)"),
+                clients=K, samples=K * per, eval=result.get("eval"),
+                extra={"local_epochs": cfg["epochs"], "batch": cfg["batch"], "optimizer": "adam",
+                       "gradients": cfg["grad"], "secagg": cfg["secagg"],
+                       "statevector_sims_per_round": sims, "gates_per_sim": n_gates,
+                       "state_gate_applications_per_s": sims * n_gates / ms * 1e3,
+                       "amplitude_updates_per_s": sims * n_gates * float(2 ** n) / ms * 1e3})
+
+
 def run_cfed(cfg, args, rank, world, local):
     from qfedx_b200.fl import FederatedDataset, FederatedRunner, FLConfig
     from qfedx_b200.fl.trainers_cnn import TinyCNNBatchedTrainer
@@ -297,12 +376,12 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--config", default="cfed", choices=["cfed", "vqc8", "vqc4"])
+    ap.add_argument("--config", default="cfed", choices=["cfed", "vqc8", "vqc4", "vqc20", "vqc30"])
     ap.add_argument("--no-aux", action="store_true", help="skip the secondary measurements")
     args = ap.parse_args()
     rank, world, local = dist_env()
     init_dist(world, local)
-    cfgs = {"cfed": CFED, "vqc8": VQC8, "vqc4": VQC4}
+    cfgs = {"cfed": CFED, "vqc8": VQC8, "vqc4": VQC4, "vqc20": VQC20, "vqc30": VQC30}
     cfg = dict(cfgs[args.config])
     if os.environ.get("QFX_BENCH_CLIENTS"):  # profiling aid: change the client count
         cfg["clients"] = int(os.environ["QFX_BENCH_CLIENTS"])
@@ -322,6 +401,10 @@ def main():
         if not torch.cuda.is_available():
             raise SystemExit("bench.py --config cfed needs a GPU (the client-batched CUDA path)")
         r = run_cfed(cfg, args, rank, world, local)
+    elif args.config in ("vqc20", "vqc30"):
+        if not torch.cuda.is_available():
+            raise SystemExit(f"bench.py --config {args.config} needs a GPU (pass engine / sharded state)")
+        r = run_large(cfg, args.config, args, rank, world, local)
     else:
         r = run_vqc(cfg, args.config, args, rank, world, local)
 
@@ -343,7 +426,7 @@ def main():
             "data": "synthetic MNIST-shape images, random-init weights",
             "impl": args.impl,
             "config": {"name": args.config, "model": r["model"], "clients": r["clients"], "global_batch": r["samples"],
-                       "seq_len": None, "parallelism": f"client-parallel x{world}", "l2": "flushed between rounds",
+                       "seq_len": None, "parallelism": (f"state-sharded x{world}" if args.config == "vqc30" else f"client-parallel x{world}"), "l2": "flushed between rounds",
                        **r["extra"]},
             "clocks": r["clocks"],
             "e2e": {"value": 1000.0 / r["e2e_ms"], "unit": "rounds/s", "h2d_bytes_per_step": r["h2d"],
