@@ -185,9 +185,14 @@ int qfx_unitary_gemm(const float* a_hi, const float* a_lo, const float* b_hi, co
  *   angles [angle_rows][n_feature] (row = batch index modulo rows); shift_param/shift_value [batch]
  *   add a per-state shift to one parameter (parameter-shift rule, /root/reference/ROADMAP.md:130-135).
  *   plan_dev (nullable, tile_bits == 12 only): segment plan for the register-resident engine (DEVICE ints:
- *   n_seg, then per segment pos_to_bit[12], n_ops, n_ops x {kind, posA, posB, op index}); see ops/large.py.
+ *   n_seg [| 1 << 16 when a trailer follows], then per segment pos_to_bit[12], n_ops, n_ops x {kind, posA, posB,
+ *   op index}; optional trailer: one mode per op of the pass (0 general, 1 RXRZ without its scalar phase, 2 the
+ *   carrier gate that absorbs those phases) and the carrier's op index (-1 none)); see ops/large.py.
  * qfx_sv_large_expz: <Z_q> for all n_total qubits -> out [batch][n_total]; qubits >= n_local are
  *   read from high_bits (the shard's rank).
+ * qfx_sv_large_expz_masks: parity readout out[b][q] = sum_i |psi_i|^2 (-1)^parity(idx & masks_host[q]) with
+ *   idx = high_bits << n_local | i (masks_host: HOST array of n_out <= 32 words).  <Z_q> behind a trailing CNOT
+ *   ring is such a parity in front of it, so the ring is never simulated (ops/large.py: ring_readout_masks).
  * qfx_sv_global_swap_fused: sharded state, world = 2^g_bits ranks: exchange the g global qubits with
  *   the top g local qubits by pulling slices from every peer's shard (src_table: device array of
  *   world peer pointers) and apply n_ops <= 32 gates on the swapped-in qubits (local bits 0..g-1 of the
@@ -202,6 +207,8 @@ int qfx_sv_large_pass(float* states, int n_qubits, int batch, int tile_bits, int
                       cudaStream_t stream);
 int qfx_sv_large_expz(const float* states, int n_local, int n_total, unsigned int high_bits, int batch, float* out,
                       cudaStream_t stream);
+int qfx_sv_large_expz_masks(const float* states, int n_local, int n_out, unsigned int high_bits,
+                            const unsigned long long* masks_host, int batch, float* out, cudaStream_t stream);
 int qfx_sv_global_swap_fused(const float* const* src_table, float* dst, int n_local, int g_bits, int rank, int world,
                              const int* ops_dev, int n_ops, const float* theta, int n_params, const float* angles,
                              int n_feature, unsigned int* const* flags_table, unsigned int epoch,

@@ -113,7 +113,10 @@ def large_state_throughput(n=20, L=2, batch=16, tile_bits=12, low_bits=3, regist
     return {"n_qubits": n, "layers": L, "batch": batch, "tile_bits": tile_bits, "low_bits": low_bits, "register_engine": register_engine,
             "passes": len(vqc.passes), "gates": vqc.n_gates, "ms": ms,
             "gates_per_s": vqc.n_gates * batch / ms * 1e3,
-            "effective_gbs": 2 * state_bytes * len(vqc.passes) / ms / 1e6, "expz_ms": ez}
+            "effective_gbs": 2 * state_bytes * len(vqc.passes) / ms / 1e6, "expz_ms": ez,
+            # what training uses: all <Z_q> of the circuit, final ring folded into the parity readout
+            "readout_passes": len(vqc.readout_passes),
+            "expvals_ms": _time_ms(lambda: vqc.expvals(ang, theta), iters=5, warmup=2)}
 
 
 def aux_measurements(args=None, rank=0, world=1, local=0, skip=None):

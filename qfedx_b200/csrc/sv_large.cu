@@ -40,9 +40,16 @@ struct PassArgs {
     int init_zero_state;       // 1: ignore memory contents, start from |0..0>
 };
 
-__device__ __forceinline__ void cmul_acc(float2& out, float2 m, float2 v) {
-    out.x += m.x * v.x - m.y * v.y;
-    out.y += m.x * v.y + m.y * v.x;
+__device__ __forceinline__ void cmul_acc(float2& out, float2 m, float2 v) {   // two FFMA per component
+    out.x = fmaf(-m.y, v.y, fmaf(m.x, v.x, out.x));
+    out.y = fmaf(m.y, v.x, fmaf(m.x, v.y, out.y));
+}
+// m0 * v0 + m1 * v1 without a zero accumulator: FMUL + 3 FFMA per component
+__device__ __forceinline__ float2 cmul2(float2 m0, float2 v0, float2 m1, float2 v1) {
+    float2 r;
+    r.x = fmaf(-m1.y, v1.y, fmaf(m1.x, v1.x, fmaf(-m0.y, v0.y, m0.x * v0.x)));
+    r.y = fmaf(m1.y, v1.x, fmaf(m1.x, v1.y, fmaf(m0.y, v0.x, m0.x * v0.y)));
+    return r;
 }
 
 // Global offset of tile element j0 = tid + 256 k: the deposit of j0's bits into the tile's qubit positions
@@ -157,10 +164,8 @@ sv_large_pass_kernel(const PassArgs a) {
             for (int idx = tid; idx < (tile_n >> 1); idx += PASS_THREADS) {
                 const int j0 = ((idx >> b0) << (b0 + 1)) | (idx & ((1 << b0) - 1)), j1 = j0 | (1 << b0);
                 const float2 v0 = tile[j0], v1 = tile[j1];
-                float2 r0 = make_float2(0.f, 0.f), r1 = make_float2(0.f, 0.f);
-                cmul_acc(r0, m00, v0); cmul_acc(r0, m01, v1);
-                cmul_acc(r1, m10, v0); cmul_acc(r1, m11, v1);
-                tile[j0] = r0; tile[j1] = r1;
+                tile[j0] = cmul2(m00, v0, m01, v1);
+                tile[j1] = cmul2(m10, v0, m11, v1);
             }
         }
         __syncthreads();
@@ -180,9 +185,11 @@ sv_large_pass_kernel(const PassArgs a) {
 // 4 register bits (gates are pure register arithmetic; static indexing through a switch over the bit),
 // 3 warp bits (inactive).  A pass is split by the host planner (qfedx_b200/ops/large.py) into segments,
 // each with its own assignment such that every gate of the segment only touches lane / register bits;
-// between segments the tile is re-laid-out through shared memory.  Tile bits 0..3 always sit on lane
-// bits 0..3, which keeps every shared-memory access of the re-layout conflict-free.
-// About 9 instructions per amplitude and gate instead of ~40 for the shared-memory loop of v1.
+// between segments the tile is re-laid-out through shared memory.  The planner puts one-qubit gates and CNOT
+// targets on register bits only (a lane-bit gate costs two shuffles per amplitude on top of the arithmetic);
+// the shared-memory copy of the tile is XOR-swizzled so that any lane set covering the four bit classes
+// mod 4 is bank-conflict free.  Real rotations take 4 instructions per amplitude, fused RX.RZ 6 (scalar
+// phases collected into one carrier gate), a CNOT 2 - against ~40 for the shared-memory loop of v1.
 constexpr int V2_T = 12;
 
 template <int RB>
@@ -193,10 +200,48 @@ __device__ __forceinline__ void v2_gate_reg(float2 (&a)[16], const float2* m) {
         if (!((i >> RB) & 1)) {
             const int j = i | (1 << RB);
             const float2 v0 = a[i], v1 = a[j];
-            float2 r0 = make_float2(0.f, 0.f), r1 = r0;
-            cmul_acc(r0, m00, v0); cmul_acc(r0, m01, v1);
-            cmul_acc(r1, m10, v0); cmul_acc(r1, m11, v1);
-            a[i] = r0; a[j] = r1;
+            a[i] = cmul2(m00, v0, m01, v1);
+            a[j] = cmul2(m10, v0, m11, v1);
+        }
+    }
+}
+// Real rotation (RY, feature map): v0' = c v0 - s v1, v1' = s v0 + c v1 - 4 instructions per amplitude
+template <int RB>
+__device__ __forceinline__ void v2_ry_reg(float2 (&a)[16], float c, float s) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        if (!((i >> RB) & 1)) {
+            const int j = i | (1 << RB);
+            const float2 v0 = a[i], v1 = a[j];
+            a[i] = make_float2(fmaf(-s, v1.x, c * v0.x), fmaf(-s, v1.y, c * v0.y));
+            a[j] = make_float2(fmaf(s, v0.x, c * v1.x), fmaf(s, v0.y, c * v1.y));
+        }
+    }
+}
+__device__ __forceinline__ void v2_ry_lane(float2 (&a)[16], float c, float s, int lb, int lane) {
+    const float so = ((lane >> lb) & 1) ? s : -s;    // partner coefficient: +s on the |1> side
+    const int mask = 1 << lb;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const float px = __shfl_xor_sync(0xffffffffu, a[i].x, mask);
+        const float py = __shfl_xor_sync(0xffffffffu, a[i].y, mask);
+        a[i] = make_float2(fmaf(so, px, c * a[i].x), fmaf(so, py, c * a[i].y));
+    }
+}
+// RZ(phi) RX(theta) = e^{-i phi/2} diag(1, e^{i phi}) RX(theta): the pair update without the scalar phase costs
+// 12 instructions instead of 16; the scalar phases of all such gates of a pass are folded into one carrier
+// gate's matrix (see the kernel preamble), so the state is exact.
+template <int RB>
+__device__ __forceinline__ void v2_rxrz_reg(float2 (&a)[16], const float2* m) {
+    const float c = m[0].x, s = m[0].y, cp = m[1].x, sp = m[1].y;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        if (!((i >> RB) & 1)) {
+            const int j = i | (1 << RB);
+            const float2 v0 = a[i], v1 = a[j];
+            a[i] = make_float2(fmaf(s, v1.y, c * v0.x), fmaf(-s, v1.x, c * v0.y));      // c v0 - i s v1
+            const float tx = fmaf(s, v0.y, c * v1.x), ty = fmaf(-s, v0.x, c * v1.y);    // c v1 - i s v0
+            a[j] = make_float2(fmaf(-sp, ty, cp * tx), fmaf(sp, tx, cp * ty));          // e^{i phi} t
         }
     }
 }
@@ -209,9 +254,7 @@ __device__ __forceinline__ void v2_gate_lane(float2 (&a)[16], const float2* m, i
         float2 p;
         p.x = __shfl_xor_sync(0xffffffffu, a[i].x, mask);
         p.y = __shfl_xor_sync(0xffffffffu, a[i].y, mask);
-        float2 r = make_float2(0.f, 0.f);
-        cmul_acc(r, ms, a[i]); cmul_acc(r, mo, p);
-        a[i] = r;
+        a[i] = cmul2(ms, a[i], mo, p);
     }
 }
 // 16-bit mask: bit i set when position `pos` (lane 0..4 / register 5..8) is 1 for register i of this thread
@@ -220,17 +263,39 @@ __device__ __forceinline__ unsigned v2_mask(int pos, int lane) {
     const unsigned pat[4] = {0xAAAAu, 0xCCCCu, 0xF0F0u, 0xFF00u};
     return pat[pos - 5];
 }
+__device__ __forceinline__ int v2_swz(int j) { return j ^ ((j >> 4) & 15) ^ ((j >> 8) & 15); }
+
+// CNOT with the target on register bit RB: control on a lane bit -> one predicate per thread ...
 template <int RB>
-__device__ __forceinline__ void v2_cswap_reg(float2 (&a)[16], unsigned cmask) {
+__device__ __forceinline__ void v2_cnot_lane_ctl(float2 (&a)[16], bool on) {
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
         if (!((i >> RB) & 1)) {
             const int j = i | (1 << RB);
-            const bool on = (cmask >> i) & 1;   // control bit of the pair (identical for i and j unless ctl == tgt)
             const float2 vi = a[i], vj = a[j];
             a[i] = on ? vj : vi;
             a[j] = on ? vi : vj;
         }
+    }
+}
+// ... control on register bit CB -> a fixed exchange of four register pairs
+template <int CB, int RB>
+__device__ __forceinline__ void v2_cnot_reg_ctl(float2 (&a)[16]) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        if (((i >> CB) & 1) && !((i >> RB) & 1)) {
+            const int j = i | (1 << RB);
+            const float2 t = a[i]; a[i] = a[j]; a[j] = t;
+        }
+    }
+}
+template <int CB>
+__device__ __forceinline__ void v2_cnot_reg_ctl_any(float2 (&a)[16], int rb) {
+    switch (rb) {
+        case 0: if (CB != 0) v2_cnot_reg_ctl<CB, CB == 0 ? 1 : 0>(a); break;
+        case 1: if (CB != 1) v2_cnot_reg_ctl<CB, CB == 1 ? 0 : 1>(a); break;
+        case 2: if (CB != 2) v2_cnot_reg_ctl<CB, CB == 2 ? 0 : 2>(a); break;
+        default: if (CB != 3) v2_cnot_reg_ctl<CB, CB == 3 ? 0 : 3>(a); break;
     }
 }
 
@@ -240,7 +305,9 @@ struct PassArgsV2 {
     int plan_len;
 };
 
-constexpr int V2_PLAN_MAX = 1 + 4 * (13 + 4 * MAX_OPS_PER_PASS / 2);   // ints of plan kept in shared memory
+// ints of plan kept in shared memory: header, segments, and the optional trailer (per-op mode + carrier index)
+constexpr int V2_PLAN_MAX = 1 + 4 * (13 + 4 * MAX_OPS_PER_PASS / 2) + MAX_OPS_PER_PASS + 1;
+constexpr int V2_KIND_RXRZ_STRIPPED = 7;   // plan-private op kind: RXRZ on a register bit without its scalar phase
 
 __global__ void __launch_bounds__(PASS_THREADS, 3)
 sv_large_pass_v2_kernel(const PassArgsV2 pa) {
@@ -250,8 +317,40 @@ sv_large_pass_v2_kernel(const PassArgsV2 pa) {
     __shared__ int splan[V2_PLAN_MAX];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, batch = blockIdx.y;
     float2* st = a.states + ((size_t)batch << a.n_qubits);
-    for (int i = tid; i < a.n_ops; i += PASS_THREADS) op_matrix(a, a.ops + 5 * i, batch, mats[i]);
     for (int i = tid; i < pa.plan_len; i += PASS_THREADS) splan[i] = pa.plan[i];   // op stream out of global memory
+    // plan[0] = n_seg | has_trailer << 16; trailer = n_ops op modes (0 general, 1 stripped RXRZ, 2 carrier) + carrier
+    const bool has_modes = (pa.plan[0] >> 16) & 1;
+    const int* gmodes = pa.plan + pa.plan_len - a.n_ops - 1;
+    for (int i = tid; i < a.n_ops; i += PASS_THREADS) {
+        if (has_modes && gmodes[i] == 1) {
+            const int* op = a.ops + 5 * i;
+            const float* th = a.theta + (size_t)(batch % a.theta_rows) * a.n_params;
+            float t0 = th[op[3]], t1 = th[op[4]];
+            if (a.shift_param && a.shift_param[batch] == op[3]) t0 += a.shift_value[batch];
+            if (a.shift_param && a.shift_param[batch] == op[4]) t1 += a.shift_value[batch];
+            float sn, cs, sp, cp;
+            sincosf(0.5f * t0, &sn, &cs);
+            sincosf(t1, &sp, &cp);
+            mats[i][0] = make_float2(cs, sn); mats[i][1] = make_float2(cp, sp);
+            mats[i][2] = make_float2(0.5f * t1, 0.f); mats[i][3] = make_float2(0.f, 0.f);
+        } else {
+            op_matrix(a, a.ops + 5 * i, batch, mats[i]);
+        }
+    }
+    __syncthreads();
+    if (has_modes && tid < 32) {   // scalar phases of the stripped gates -> the carrier's matrix
+        const int carrier = splan[pa.plan_len - 1];
+        float ph = 0.f;
+        for (int i = tid; i < a.n_ops; i += 32)
+            if (splan[pa.plan_len - a.n_ops - 1 + i] == 1) ph -= mats[i][2].x;
+        ph = warp_sum(ph);
+        if (carrier >= 0 && tid < 4) {
+            float sg, cg;
+            sincosf(ph, &sg, &cg);
+            const float2 v = mats[carrier][tid];
+            mats[carrier][tid] = make_float2(cg * v.x - sg * v.y, cg * v.y + sg * v.x);
+        }
+    }
     unsigned long long tile_mask = 0ull;
     for (int b = 0; b < V2_T; ++b) tile_mask |= 1ull << a.tile_q[b];
     unsigned long long base = 0ull;
@@ -264,15 +363,18 @@ sv_large_pass_v2_kernel(const PassArgsV2 pa) {
     if (tid < 16) koff[tid] = deposit_bits((unsigned)tid, 8, V2_T - 8, a.tile_q);
     const unsigned long long toff = base | deposit_bits((unsigned)tid, 0, 8, a.tile_q);
     __syncthreads();
+    // tile element j lives at v2_swz(j): low nibble XOR-ed with the two higher nibbles (linear over GF(2), so the
+    // address of a union of disjoint bit sets is the XOR of their addresses).  Any segment whose lane bits cover
+    // the four classes mod 4 then reads and writes its layout without bank conflicts.
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
         const unsigned long long off = toff | koff[k];
-        tile[tid + 256 * k] = a.init_zero_state ? make_float2((off == 0ull) ? 1.f : 0.f, 0.f) : st[off];
+        tile[v2_swz(tid + 256 * k)] = a.init_zero_state ? make_float2((off == 0ull) ? 1.f : 0.f, 0.f) : st[off];
     }
     __syncthreads();
 
     const int* plan = splan;
-    const int n_seg = plan[0];
+    const int n_seg = plan[0] & 0xFFFF;
     int cur = 1;
     for (int sg = 0; sg < n_seg; ++sg) {
         const int* p2b = plan + cur;          // position -> tile bit
@@ -285,22 +387,32 @@ sv_large_pass_v2_kernel(const PassArgsV2 pa) {
         for (int p = 0; p < 5; ++p) bwl |= ((lane >> p) & 1) << p2b[p];
 #pragma unroll
         for (int p = 0; p < 3; ++p) bwl |= ((warp >> p) & 1) << p2b[9 + p];
-        const int rb0 = 1 << p2b[5], rb1 = 1 << p2b[6], rb2 = 1 << p2b[7], rb3 = 1 << p2b[8];
+        bwl = v2_swz(bwl);
+        const int rb0 = v2_swz(1 << p2b[5]), rb1 = v2_swz(1 << p2b[6]), rb2 = v2_swz(1 << p2b[7]),
+                  rb3 = v2_swz(1 << p2b[8]);
         float2 r[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i)
-            r[i] = tile[bwl | ((i & 1) ? rb0 : 0) | ((i & 2) ? rb1 : 0) | ((i & 4) ? rb2 : 0) | ((i & 8) ? rb3 : 0)];
+            r[i] = tile[bwl ^ ((i & 1) ? rb0 : 0) ^ ((i & 2) ? rb1 : 0) ^ ((i & 4) ? rb2 : 0) ^ ((i & 8) ? rb3 : 0)];
         for (int o = 0; o < n_ops; ++o) {
             const int kind = ops[4 * o], pA = ops[4 * o + 1], pB = ops[4 * o + 2];
             const float2* m = mats[ops[4 * o + 3]];
             if (kind == QFX_GATE_CNOT) {
                 const unsigned cm = v2_mask(pA, lane);
-                if (pB >= 5) {
+                if (pB >= 5 && pA < 5) {
+                    const bool on = (lane >> pA) & 1;
                     switch (pB - 5) {
-                        case 0: v2_cswap_reg<0>(r, cm); break;
-                        case 1: v2_cswap_reg<1>(r, cm); break;
-                        case 2: v2_cswap_reg<2>(r, cm); break;
-                        default: v2_cswap_reg<3>(r, cm); break;
+                        case 0: v2_cnot_lane_ctl<0>(r, on); break;
+                        case 1: v2_cnot_lane_ctl<1>(r, on); break;
+                        case 2: v2_cnot_lane_ctl<2>(r, on); break;
+                        default: v2_cnot_lane_ctl<3>(r, on); break;
+                    }
+                } else if (pB >= 5) {
+                    switch (pA - 5) {
+                        case 0: v2_cnot_reg_ctl_any<0>(r, pB - 5); break;
+                        case 1: v2_cnot_reg_ctl_any<1>(r, pB - 5); break;
+                        case 2: v2_cnot_reg_ctl_any<2>(r, pB - 5); break;
+                        default: v2_cnot_reg_ctl_any<3>(r, pB - 5); break;
                     }
                 } else {
                     const int mask = 1 << pB;
@@ -316,6 +428,25 @@ sv_large_pass_v2_kernel(const PassArgsV2 pa) {
 #pragma unroll
                 for (int i = 0; i < 16; ++i)
                     if ((cm >> i) & 1) r[i] = make_float2(-r[i].x, -r[i].y);
+            } else if (kind == QFX_GATE_RY || kind == QFX_GATE_RY_FEATURE) {
+                const float c = m[0].x, sn = m[2].x;
+                if (pA >= 5) {
+                    switch (pA - 5) {
+                        case 0: v2_ry_reg<0>(r, c, sn); break;
+                        case 1: v2_ry_reg<1>(r, c, sn); break;
+                        case 2: v2_ry_reg<2>(r, c, sn); break;
+                        default: v2_ry_reg<3>(r, c, sn); break;
+                    }
+                } else {
+                    v2_ry_lane(r, c, sn, pA, lane);
+                }
+            } else if (kind == V2_KIND_RXRZ_STRIPPED) {
+                switch (pA - 5) {
+                    case 0: v2_rxrz_reg<0>(r, m); break;
+                    case 1: v2_rxrz_reg<1>(r, m); break;
+                    case 2: v2_rxrz_reg<2>(r, m); break;
+                    default: v2_rxrz_reg<3>(r, m); break;
+                }
             } else if (pA >= 5) {
                 switch (pA - 5) {
                     case 0: v2_gate_reg<0>(r, m); break;
@@ -330,11 +461,11 @@ sv_large_pass_v2_kernel(const PassArgsV2 pa) {
         __syncthreads();   // every thread has read its amplitudes of this layout
 #pragma unroll
         for (int i = 0; i < 16; ++i)
-            tile[bwl | ((i & 1) ? rb0 : 0) | ((i & 2) ? rb1 : 0) | ((i & 4) ? rb2 : 0) | ((i & 8) ? rb3 : 0)] = r[i];
+            tile[bwl ^ ((i & 1) ? rb0 : 0) ^ ((i & 2) ? rb1 : 0) ^ ((i & 4) ? rb2 : 0) ^ ((i & 8) ? rb3 : 0)] = r[i];
         __syncthreads();
     }
 #pragma unroll
-    for (int k = 0; k < 16; ++k) st[toff | koff[k]] = tile[tid + 256 * k];
+    for (int k = 0; k < 16; ++k) st[toff | koff[k]] = tile[v2_swz(tid + 256 * k)];
 }
 
 // <Z_q> for q < n_local taken from the index bits, for q >= n_local from `high_bits` (the rank)
@@ -369,6 +500,43 @@ sv_large_expz_kernel(const float2* __restrict__ states, int n_local, int n_total
     }
     __syncthreads();
     if (tid < n_total) atomicAdd(out + (size_t)batch * n_total + tid, red[tid]);
+}
+
+// <Z-string> readout: out[q] = sum_i |psi_i|^2 (-1)^{parity(idx & masks[q])} with idx = high_bits << n_local | i.
+// A trailing CNOT ring only permutes basis states, so <Z_q> after it equals a parity readout before it
+// (Z_t -> Z_c Z_t under CNOT(c,t)): the ring's passes - and for a sharded state its swaps - are never run.
+struct MaskArgs { unsigned long long m[32]; };
+__global__ void __launch_bounds__(256)
+sv_large_expz_masks_kernel(const float2* __restrict__ states, int n_local, int n_out, unsigned int high_bits,
+                           const MaskArgs masks, float* __restrict__ out /*[batch][n_out]*/) {
+    __shared__ float red[32];
+    const int batch = blockIdx.y, tid = threadIdx.x;
+    const float2* st = states + ((size_t)batch << n_local);
+    const size_t N = (size_t)1 << n_local;
+    const unsigned long long hi = (unsigned long long)high_bits << n_local;
+    float acc[32];
+#pragma unroll
+    for (int q = 0; q < 32; ++q) acc[q] = 0.f;
+    for (size_t i = (size_t)blockIdx.x * 256 + tid; i < N; i += (size_t)gridDim.x * 256) {
+        const float2 v = st[i];
+        const float p = v.x * v.x + v.y * v.y;
+        const unsigned long long idx = hi | i;
+#pragma unroll
+        for (int q = 0; q < 32; ++q)
+            if (q < n_out)                                       // uniform; sign bit of p flipped by the parity
+                acc[q] += __uint_as_float(__float_as_uint(p) ^ ((unsigned)(__popcll(idx & masks.m[q]) & 1) << 31));
+    }
+    if (tid < 32) red[tid] = 0.f;
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < 32; ++q) {
+        if (q < n_out) {
+            const float v = warp_sum(acc[q]);
+            if ((tid & 31) == 0) atomicAdd(&red[q], v);
+        }
+    }
+    __syncthreads();
+    if (tid < n_out) atomicAdd(out + (size_t)batch * n_out + tid, red[tid]);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -525,6 +693,22 @@ extern "C" int qfx_sv_large_expz(const float* states, int n_local, int n_total, 
     sv_large_expz_kernel<<<dim3((unsigned)blocks, batch), 256, 0, stream>>>(reinterpret_cast<const float2*>(states),
                                                                           n_local, n_total, high_bits, out);
     return check_launch("sv_large_expz_kernel");
+}
+
+extern "C" int qfx_sv_large_expz_masks(const float* states, int n_local, int n_out, unsigned int high_bits,
+                                       const unsigned long long* masks_host, int batch, float* out,
+                                       cudaStream_t stream) {
+    QFX_ARG_CHECK(n_local >= 1 && n_local <= 34 && n_out >= 1 && n_out <= 32, QFX_ERR_BAD_ARG, "bad qubit counts");
+    QFX_ARG_CHECK(masks_host != nullptr && batch >= 1 && batch <= 65535, QFX_ERR_BAD_ARG, "bad masks / batch");
+    MaskArgs m = {};
+    for (int q = 0; q < n_out; ++q) m.m[q] = masks_host[q];
+    QFX_CUDA_TRY(cudaMemsetAsync(out, 0, sizeof(float) * (size_t)batch * n_out, stream));
+    size_t blocks = (((size_t)1 << n_local) + 256 * 8 - 1) / (256 * 8);
+    const size_t cap = (size_t)num_sms() * 8 / (batch > 8 ? 8 : batch) + 1;
+    if (blocks > cap) blocks = cap;
+    sv_large_expz_masks_kernel<<<dim3((unsigned)blocks, batch), 256, 0, stream>>>(
+        reinterpret_cast<const float2*>(states), n_local, n_out, high_bits, m, out);
+    return check_launch("sv_large_expz_masks_kernel");
 }
 
 // src_table: device array of `world` pointers (every rank's source shard, symmetric heap);

@@ -15,12 +15,14 @@ import torch
 import torch.nn.functional as F
 
 from ..models.vqc import VQC
-from ..ops.large import LargeVQC, ansatz_gates
+from ..ops.large import LargeVQC, ansatz_gates, ring_readout_masks
 from .dataset import FederatedDataset
 
 
 class _ExpvalBackend:
-    def expvals(self, angles, theta):  # [S,n], [P] -> [S,n]
+    n_out = None   # qubits read out (None: all); the trainer sets it to the model's logit count
+
+    def expvals(self, angles, theta):  # [S,n], [P] -> [S,n_out]
         raise NotImplementedError
 
     def shift_grad(self, angles, theta, cot):  # -> [P]
@@ -32,7 +34,7 @@ class PassBackend(_ExpvalBackend):
         self.vqc, self.max_states = LargeVQC(n, L, entangler), max_states
 
     def expvals(self, angles, theta):
-        return self.vqc.expvals(angles, theta.reshape(1, -1))
+        return self.vqc.expvals(angles, theta.reshape(1, -1), self.n_out)
 
     def shift_grad(self, angles, theta, cot):
         return self.vqc.param_shift_grad(angles, theta, cot, self.max_states)
@@ -44,13 +46,15 @@ class ShardedBackend(_ExpvalBackend):
     def __init__(self, n, L, world, rank, device, entangler="cnot", loopback=False):
         from ..parallel.sharded import ShardedState, plan_sharded
         self.n, self.L = n, L
-        self.plan = plan_sharded(n, int(math.log2(world)), ansatz_gates(n, L, entangler))
+        # the last ring is folded into the parity readout: its cross-shard CNOTs would cost another swap
+        self.plan = plan_sharded(n, int(math.log2(world)), ansatz_gates(n, L, entangler, final_ring=False))
+        self.masks = ring_readout_masks(n, entangler if L > 0 else "none")
         self.state = ShardedState(n, world, rank, device, loopback=loopback)
 
     def _one(self, ang, theta):
         self.state.reset_zero_state()
         self.state.run(self.plan, theta, ang.reshape(1, -1))
-        return self.state.expvals(self.plan)
+        return self.state.expvals_parity(self.plan, self.masks[:self.n_out or self.n])
 
     def expvals(self, angles, theta):
         return torch.stack([self._one(angles[s], theta) for s in range(angles.shape[0])])
@@ -74,6 +78,7 @@ class LargeVQCTrainer:
         self.grad_method, self.spsa_c, self.generator = grad_method, spsa_c, generator
         self.n_wrap = model.n_angle_params
         self.launches = 0
+        backend.n_out = model.n_logits
 
     @property
     def dim(self):

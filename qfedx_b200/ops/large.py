@@ -17,8 +17,10 @@ GATE = {"rx": 0, "ry": 1, "rz": 2, "cnot": 3, "cz": 4, "rxrz": 5, "ry_feature": 
 TWO_QUBIT = (GATE["cnot"], GATE["cz"])
 
 
-def ansatz_gates(n: int, n_layers: int, entangler: str = "cnot", feature_map: bool = True) -> List[Tuple[int, int, int, int]]:
-    """(kind, q0, q1, param) list of the VQC: RY feature map + L x [RX RZ per qubit, ring]."""
+def ansatz_gates(n: int, n_layers: int, entangler: str = "cnot", feature_map: bool = True,
+                 final_ring: bool = True) -> List[Tuple[int, int, int, int]]:
+    """(kind, q0, q1, param) list of the VQC: RY feature map + L x [RX RZ per qubit, ring].  With
+    ``final_ring=False`` the last layer's ring is left out (read <Z> through ``ring_readout_masks``)."""
     gates = []
     if feature_map:
         gates += [(GATE["ry_feature"], q, -1, q) for q in range(n)]
@@ -26,9 +28,22 @@ def ansatz_gates(n: int, n_layers: int, entangler: str = "cnot", feature_map: bo
         for q in range(n):
             gates.append((GATE["rx"], q, -1, (l * n + q) * 2))
             gates.append((GATE["rz"], q, -1, (l * n + q) * 2 + 1))
-        if entangler != "none":
+        if entangler != "none" and (final_ring or l < n_layers - 1):
             gates += [(GATE[entangler], c, t, -1) for c, t in ring_pairs(n)]
     return gates
+
+
+def ring_readout_masks(n: int, entangler: str = "cnot") -> List[int]:
+    """Bit masks m_q with <Z_q>(ring |psi>) = sum_i |psi_i|^2 (-1)^parity(i & m_q).
+
+    A CNOT ring permutes basis states; in the Heisenberg picture CNOT(c,t) maps Z_t -> Z_c Z_t and leaves
+    Z_c alone, so pulling Z_q back through the ring (last gate first) gives a Z-string.  CZ is diagonal: the
+    masks stay single bits.  The readout of a VQC therefore never needs the final ring to be simulated."""
+    masks = [1 << q for q in range(n)]
+    if entangler == "cnot":
+        for c, t in reversed(ring_pairs(n)):
+            masks = [m ^ (1 << c) if (m >> t) & 1 else m for m in masks]
+    return masks
 
 
 @dataclass
@@ -41,59 +56,106 @@ class Pass:
 
 
 REG_TILE_BITS = 12
+PLAN_KIND_RXRZ_STRIPPED = 7   # plan-private op kind (csrc/sv_large.cu: V2_KIND_RXRZ_STRIPPED)
 
 
 def plan_segments(ops: np.ndarray) -> np.ndarray:
     """Split a 12-bit pass into segments for the register-resident kernel (csrc/sv_large.cu, v2).
 
-    Positions: 0-4 lane bits, 5-8 register bits, 9-11 warp bits (inactive in a segment).  Tile bits 0-3
-    stay on lane positions 0-3 (conflict-free shared-memory re-layout); the other eight bits are
-    re-assigned per segment: the three whose next use is farthest become inactive (Belady), the busiest
-    four of the rest become register bits.  Returns the int32 plan: n_seg, then per segment
-    pos_to_bit[12], n_ops, n_ops x (kind, posA, posB, op index)."""
-    flexible = list(range(4, REG_TILE_BITS))
-    remaining = list(range(len(ops)))
+    Positions: 0-4 lane bits, 5-8 register bits, 9-11 warp bits (inactive in a segment).  Arithmetic on a
+    register bit is plain FMAs; on a lane bit every amplitude costs two warp shuffles more, so within a segment
+    one-qubit gates and CNOT targets are only executed on REGISTER bits - anything else waits for a later
+    segment whose register set holds its bit (controls and CZ operands may sit on lane bits).  Each segment
+    picks, among the bits whose gates are due next, the register set that lets the most work run.
+
+    The tile lives in shared memory with its low index nibble XOR-ed with the two higher nibbles, so a segment's
+    re-layout is bank-conflict free whenever four of the five lane bits fall into distinct classes mod 4; the
+    planner keeps one bit of every class out of the register set for that.
+
+    Returns the int32 plan: n_seg | 1 << 16, then per segment pos_to_bit[12], n_ops, n_ops x (kind, posA, posB,
+    op index), then the trailer described below."""
+    from itertools import combinations
+    T = REG_TILE_BITS
+    cnot, cz = GATE["cnot"], GATE["cz"]
+    kinds = [int(o[0]) for o in ops]
+    b0s, b1s = [int(o[1]) for o in ops], [int(o[2]) for o in ops]
 
     def bits_of(i):
-        k, b0, b1 = int(ops[i][0]), int(ops[i][1]), int(ops[i][2])
-        return (b0, b1) if k in TWO_QUBIT else (b0,)
+        return (b0s[i], b1s[i]) if kinds[i] in TWO_QUBIT else (b0s[i],)
 
-    segs = []
-    while remaining:
-        next_use = {}
-        for rank, i in enumerate(remaining):
-            for b in bits_of(i):
-                next_use.setdefault(b, rank)
-        order = sorted(flexible, key=lambda b: -next_use.get(b, 1 << 30))
-        inactive = set(order[:3])
-        blocked, chosen, rest = set(), [], []
+    def reg_bits(i):        # bits that must be register bits for op i to run
+        return () if kinds[i] == cz else ((b1s[i],) if kinds[i] == cnot else (b0s[i],))
+
+    def run(remaining, regs, active):
+        blocked, chosen, rest, score = set(), [], [], 0
         for i in remaining:
-            bs = set(bits_of(i))
-            if bs & inactive or bs & blocked:
-                blocked |= bs
+            bs = bits_of(i)
+            if any(b in blocked or b not in active for b in bs) or any(b not in regs for b in reg_bits(i)):
+                blocked.update(bs)
                 rest.append(i)
             else:
                 chosen.append(i)
-        assert chosen, "segment planner made no progress"
-        active = [b for b in flexible if b not in inactive]          # 5 bits: 4 register + 1 lane
-        use = {b: 0 for b in active}
-        for i in chosen:
+                score += 1 if kinds[i] in TWO_QUBIT else 3
+        return chosen, rest, score
+
+    remaining = list(range(len(ops)))
+    segs = []
+    while remaining:
+        next_use, due = {}, []                     # first use of every bit; bits in the order their gates fall due
+        for rank, i in enumerate(remaining):
             for b in bits_of(i):
-                if b in use:
-                    use[b] += 1 if int(ops[i][0]) in TWO_QUBIT else 2      # 1q gates gain most from registers
-        by_use = sorted(active, key=lambda b: -use[b])
-        regs, lane4 = sorted(by_use[:4]), by_use[4]
-        p2b = [0, 1, 2, 3, lane4] + regs + sorted(inactive)
+                next_use.setdefault(b, rank)
+            for b in reg_bits(i):
+                if b not in due:
+                    due.append(b)
+        first = remaining[0]
+        must_reg, must_active = set(reg_bits(first)), set(bits_of(first))
+        pool = due[:7] + [b for b in sorted(range(T), key=lambda b: next_use.get(b, 1 << 30)) if b not in due[:7]]
+        pool = pool[:max(7, 4)]
+        best = None
+        for regs in combinations(pool, 4):
+            regs = set(regs)
+            if not must_reg <= regs or any(all(b in regs for b in range(c, T, 4)) for c in range(4)):
+                continue
+            free = [b for b in range(T) if b not in regs]
+            by_need = sorted(free, key=lambda b: (b not in must_active, next_use.get(b, 1 << 30)))
+            lanes = []
+            for b in by_need:                      # one lane bit per class mod 4, most urgent first
+                if all(b % 4 != l % 4 for l in lanes):
+                    lanes.append(b)
+            lanes = lanes[:4]
+            lanes.append(next(b for b in by_need if b not in lanes))
+            if not must_active <= regs | set(lanes):
+                continue
+            chosen, rest, score = run(remaining, regs, regs | set(lanes))
+            if best is None or score > best[0]:
+                best = (score, sorted(regs), lanes, chosen, rest)
+        assert best is not None and best[3], "segment planner made no progress"
+        _, regs, lanes, chosen, rest = best
+        warps = sorted(b for b in range(T) if b not in regs and b not in lanes)
+        p2b = lanes + regs + warps
         pos_of = {b: p for p, b in enumerate(p2b)}
         seg = list(p2b) + [len(chosen)]
         for i in chosen:
-            k, b0, b1 = int(ops[i][0]), int(ops[i][1]), int(ops[i][2])
-            seg += [k, pos_of[b0], pos_of[b1] if k in TWO_QUBIT else -1, i]
+            seg += [kinds[i], pos_of[b0s[i]], pos_of[b1s[i]] if kinds[i] in TWO_QUBIT else -1, i]
         segs.append(seg)
         remaining = rest
-    flat = [len(segs)]
+    # RXRZ gates on register bits run without their scalar phase e^{-i phi/2} (12 instead of 16 instructions per
+    # amplitude pair); the kernel folds the product of those phases into one carrier gate of the pass, which keeps
+    # its full matrix.  Trailer: mode per op (0 general, 1 stripped, 2 carrier), then the carrier's op index.
+    modes, carrier = [0] * len(ops), -1
+    for sgm in segs:
+        for e in range(13, len(sgm), 4):
+            kind, pos_a, op_i = sgm[e], sgm[e + 1], sgm[e + 3]
+            if kind == GATE["rxrz"] and pos_a >= 5:
+                if carrier < 0:
+                    carrier, modes[op_i] = op_i, 2
+                else:
+                    modes[op_i], sgm[e] = 1, PLAN_KIND_RXRZ_STRIPPED
+    flat = [len(segs) | (1 << 16)]
     for sgm in segs:
         flat += sgm
+    flat += modes + [carrier]
     return np.asarray(flat, dtype=np.int32)
 
 
@@ -147,6 +209,15 @@ def run_passes(states: torch.Tensor, n_qubits: int, passes: List[Pass], theta=No
                   _lib.c_int(0 if p.plan is None else len(p.plan)), _lib.stream_ptr())
 
 
+def expvals_parity(states: torch.Tensor, n_local: int, masks: Sequence[int], high_bits: int = 0) -> torch.Tensor:
+    """out[b, q] = sum_i |psi_i|^2 (-1)^parity((high_bits << n_local | i) & masks[q]); states [B, 2^n_local]."""
+    B, m = states.shape[0], np.asarray(masks, dtype=np.uint64)
+    out = torch.empty(B, len(m), device=states.device, dtype=torch.float32)
+    _lib.call("qfx_sv_large_expz_masks", _lib.ptr(torch.view_as_real(states)), _lib.c_int(n_local), _lib.c_int(len(m)),
+              _lib.c_u32(high_bits), m.ctypes.data_as(ctypes.c_void_p), _lib.c_int(B), _lib.ptr(out), _lib.stream_ptr())
+    return out
+
+
 def expvals_z(states: torch.Tensor, n_local: int, n_total: int | None = None, high_bits: int = 0) -> torch.Tensor:
     n_total = n_total or n_local
     B = states.shape[0]
@@ -169,9 +240,14 @@ class LargeVQC:
         self.n_params = 2 * n_qubits * n_layers
         self.passes = compile_passes(n_qubits, self.gates, self.tile_bits, self.low_bits) if _lib.available() else None
         self.n_gates = len(self.gates)
+        # readout path: the final ring is folded into parity masks instead of being simulated
+        self.readout_gates = ansatz_gates(n_qubits, n_layers, entangler, final_ring=False)
+        self.readout_masks = ring_readout_masks(n_qubits, entangler if n_layers > 0 else "none")
+        self.readout_passes = (compile_passes(n_qubits, self.readout_gates, self.tile_bits, self.low_bits)
+                               if _lib.available() else None)
 
     def states(self, angles: torch.Tensor, theta: torch.Tensor, shift_param=None, shift_value=None,
-               batch: int | None = None) -> torch.Tensor:
+               batch: int | None = None, before_final_ring: bool = False) -> torch.Tensor:
         B = batch or angles.shape[0]
         if not angles.is_cuda:
             th = theta.reshape(-1, self.L, self.n, 2)
@@ -184,17 +260,28 @@ class LargeVQC:
                 return ref.vqc_state_ref(ang, th, torch.arange(B), "ry", self.entangler)
             return ref.vqc_state_ref(angles, th, None if th.shape[0] == 1 else torch.arange(B), "ry", self.entangler)
         st = torch.empty(B, 1 << self.n, dtype=torch.complex64, device=angles.device)
-        run_passes(st, self.n, self.passes, theta, angles, shift_param, shift_value, init_zero=True,
-                   low_bits=self.low_bits, use_register_engine=self.register_engine)
+        run_passes(st, self.n, self.readout_passes if before_final_ring else self.passes, theta, angles, shift_param,
+                   shift_value, init_zero=True, low_bits=self.low_bits, use_register_engine=self.register_engine)
         return st
 
-    def expvals(self, angles: torch.Tensor, theta: torch.Tensor) -> torch.Tensor:
-        st = self.states(angles, theta)
-        return expvals_z(st, self.n) if st.is_cuda else ref.expval_z_all(st).float()
+    def _readout(self, angles, theta, shift_param=None, shift_value=None, batch=None, n_out=None) -> torch.Tensor:
+        """<Z_q>, q < n_out (default: every qubit), of the full circuit for every state of the batch."""
+        n_out = n_out or self.n
+        if not angles.is_cuda:
+            return ref.expval_z_all(self.states(angles, theta, shift_param, shift_value, batch)).float()[:, :n_out]
+        st = self.states(angles, theta, shift_param, shift_value, batch, before_final_ring=True)
+        return expvals_parity(st, self.n, self.readout_masks[:n_out])
+
+    def expvals(self, angles: torch.Tensor, theta: torch.Tensor, n_out: int | None = None) -> torch.Tensor:
+        """A classifier reads only its first n_logits qubits: pass ``n_out`` and the readout kernel stays
+        bandwidth-bound instead of evaluating n parities per amplitude."""
+        return self._readout(angles, theta, n_out=n_out)
 
     def param_shift_grad(self, angles: torch.Tensor, theta: torch.Tensor, cot: torch.Tensor,
                          max_states: int = 256) -> torch.Tensor:
-        """d sum_s cot[s] . <Z>(angles[s]) / d theta by the two-term shift rule; theta is [P]."""
+        """d sum_s cot[s] . <Z>(angles[s]) / d theta by the two-term shift rule; theta is [P]; cot is
+        [S, n_out] - only the first n_out = cot.shape[1] qubits are read out."""
+        n_out = cot.shape[1]
         S, P, dev = angles.shape[0], self.n_params, angles.device
         grad = torch.zeros(P, device=dev)
         per_chunk = max(1, max_states // (2 * S))          # parameters per chunk
@@ -203,8 +290,7 @@ class LargeVQC:
             # item order (param, sign, sample): row -> sample = row % S keeps angle_rows = S valid
             sp = ps.repeat_interleave(2 * S).to(torch.int32)
             sv = torch.tensor([np.pi / 2, -np.pi / 2], device=dev).repeat_interleave(S).repeat(len(ps)).float()
-            st = self.states(angles, theta.reshape(1, P), sp, sv, batch=len(sp))
-            E = expvals_z(st, self.n) if st.is_cuda else ref.expval_z_all(st).float()
-            val = (E.reshape(len(ps), 2, S, self.n) * cot[None, None]).sum(dim=(2, 3))
+            E = self._readout(angles, theta.reshape(1, P), sp, sv, batch=len(sp), n_out=n_out)
+            val = (E.reshape(len(ps), 2, S, n_out) * cot[None, None]).sum(dim=(2, 3))
             grad[ps] = 0.5 * (val[:, 0] - val[:, 1])
         return grad

@@ -189,6 +189,19 @@ class ShardedState:
         phys = torch.as_tensor(plan.final_phys_of, device=self.device, dtype=torch.long)
         return tot[phys]
 
+    def expvals_parity(self, plan: Plan, masks: Sequence[int]) -> torch.Tensor:
+        """sum_i |psi_i|^2 (-1)^parity(i & masks[q]) with masks over LOGICAL qubits (ops/large.py:
+        ring_readout_masks): the readout of a circuit whose final CNOT ring was not simulated."""
+        from ..ops.large import expvals_parity
+        phys = [sum(1 << plan.final_phys_of[l] for l in range(self.n) if (m >> l) & 1) for m in masks]
+        tot = torch.zeros(len(masks), device=self.device)
+        for r in self._ranks():
+            tot += expvals_parity(self.shard(r)[None], self.n_local, phys, r)[0]
+        if not self.loopback and self.world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(tot)
+        return tot
+
     def gather_logical(self, plan: Plan) -> torch.Tensor:
         """Full state in logical qubit order (loopback / small states only; for tests)."""
         assert self.loopback

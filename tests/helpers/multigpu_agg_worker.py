@@ -41,6 +41,20 @@ def main():
             if err > 3e-5 or not same:
                 ok = False
                 print(f"rank {rank}: K={K} D={D} secagg={secagg} round {rnd}: err={err:.3e} identical={same}", flush=True)
+        # back-to-back rounds with every rank delayed by a different random amount before each launch: a fast
+        # rank runs ahead into the next epoch while a slow one is still reducing the previous slots
+        skew = torch.Generator().manual_seed(99 + rank)
+        outs = []
+        for rnd in range(3, 11):
+            torch.cuda._sleep(int(torch.randint(0, 3_000_000, (1,), generator=skew)))
+            outs.append(fused(cp, glob.to(dev), w, part, mode="delta", n_wrap=D // 2, clip=clip, server_lr=0.8,
+                              seed=5, rnd=rnd, secagg=secagg, gids=rows).new_global.clone())
+        torch.cuda.synchronize()
+        for i, a in enumerate(outs):
+            err = float((a - b).abs().max())
+            if err > 3e-5:
+                ok = False
+                print(f"rank {rank}: K={K} D={D} secagg={secagg} skewed round {i}: err={err:.3e}", flush=True)
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:
