@@ -237,24 +237,35 @@ __device__ __forceinline__ void head_compute(const Step& s, int sel, int nb, int
     const unsigned long long dkey = key3(s.seed ^ 0x44524f50ull, (unsigned long long)rnd * 4096ull + s.client_ids[sel],
                                          (unsigned long long)s.epoch * 65536ull + s.batch_index);
     const float keep_scale = s.p_drop > 0.f ? 1.f / (1.f - s.p_drop) : 1.f;
-    for (int i = tid; i < BS * 64; i += 256) {
-        const int b = i >> 6, f = i & 63;
-        float v = 0.f;
-        if (b < nb) {
-            v = prm[F1B + f];
+    // 8 outputs per thread, 14 split-K partials each: the loads of four outputs (56) are issued before any is
+    // used - the sum otherwise waits for L2 eight times in a row
+    constexpr int HG = 4;
+#pragma unroll
+    for (int i0 = 0; i0 < BS * 64; i0 += 256 * HG) {
+        float pv[HG][FC1_SLICES];
+#pragma unroll
+        for (int g = 0; g < HG; ++g) {
+            const int i = i0 + g * 256 + tid, b = i >> 6, f = i & 63;
             const float* __restrict__ part = s.fc1_part + ((size_t)sel * FC1_SLICES * BS + b) * 64 + f;
-            float pv[FC1_SLICES];
 #pragma unroll
-            for (int sl = 0; sl < FC1_SLICES; ++sl) pv[sl] = __ldg(part + (size_t)sl * BS * 64);
-#pragma unroll
-            for (int sl = 0; sl < FC1_SLICES; ++sl) v += pv[sl];
-            v = fmaxf(v, 0.f);
-            if (s.p_drop > 0.f) {
-                const float u = uniform_from_bits(stream_at(dkey, (unsigned long long)i));
-                v = u < s.p_drop ? 0.f : v * keep_scale;
-            }
+            for (int sl = 0; sl < FC1_SLICES; ++sl) pv[g][sl] = b < nb ? __ldg(part + (size_t)sl * BS * 64) : 0.f;
         }
-        hs.h[b][f] = v;
+#pragma unroll
+        for (int g = 0; g < HG; ++g) {
+            const int i = i0 + g * 256 + tid, b = i >> 6, f = i & 63;
+            float v = 0.f;
+            if (b < nb) {
+                v = prm[F1B + f];
+#pragma unroll
+                for (int sl = 0; sl < FC1_SLICES; ++sl) v += pv[g][sl];
+                v = fmaxf(v, 0.f);
+                if (s.p_drop > 0.f) {
+                    const float u = uniform_from_bits(stream_at(dkey, (unsigned long long)i));
+                    v = u < s.p_drop ? 0.f : v * keep_scale;
+                }
+            }
+            hs.h[b][f] = v;
+        }
     }
     __syncthreads();
     for (int i = tid; i < BS * NC; i += 256) {   // logits
@@ -341,6 +352,13 @@ __global__ void __launch_bounds__(256) fc1_bwd_train(const Step s) {
         if (b < nb) cp_async4(&xs[b][k], s.a2 + ((size_t)sel * BS + b) * 1568 + k0 + k); else xs[b][k] = 0.f;
     }
     for (int i = tid; i < 64 * 32; i += 256) cp_async4(&wsm[i >> 5][i & 31], prm + F1W + (size_t)(i >> 5) * 1568 + k0 + (i & 31));
+    // momentum of this thread's eight weights: fetched now, needed only by the update at the very end
+    float mprev[8];
+    {
+        const int k = tid & 31, fg = (tid >> 5) * 8;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) mprev[j] = mom[F1W + (size_t)(fg + j) * 1568 + k0 + k];
+    }
     head_compute(s, sel, nb, lo, hs, dh, blockIdx.x == 0);   // the async copies above land meanwhile
     cp_async_wait_all();
     __syncthreads();
@@ -382,7 +400,7 @@ __global__ void __launch_bounds__(256) fc1_bwd_train(const Step s) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const size_t p = F1W + (size_t)(fg + j) * 1568 + k0 + k;
-            const float m = s.momentum * mom[p] + acc[j];
+            const float m = s.momentum * mprev[j] + acc[j];
             mom[p] = m;
             prm[p] = wsm[fg + j][k] - s.lr * m;
         }
