@@ -50,7 +50,8 @@ VQC8 = dict(clients=64, n_train=16760, classes=3, n_qubits=8, n_layers=6, epochs
 # S x (2P + 1) full statevector simulations (parameter shift) or 3 (SPSA).
 VQC20 = dict(clients=16, samples_per_client=4, classes=2, n_qubits=20, n_layers=2, epochs=1, batch=4, lr=0.05,
              grad="param_shift", secagg=True, clip=1.0, test_n=16)
-VQC30 = dict(clients=8, samples_per_client=1, classes=2, n_qubits=30, n_layers=1, epochs=1, batch=1, lr=0.05,
+# two layers: the last ring is folded into the readout, so one layer would leave no entangler to simulate (and no swap)
+VQC30 = dict(clients=8, samples_per_client=1, classes=2, n_qubits=30, n_layers=2, epochs=1, batch=1, lr=0.05,
              grad="spsa", secagg=False, clip=0.0, test_n=2)
 VQC4 = dict(clients=4, n_train=11183, classes=2, n_qubits=4, n_layers=2, epochs=5, batch=32, lr=0.05, test_n=1991)
 
