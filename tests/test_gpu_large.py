@@ -98,3 +98,38 @@ def test_sharded_backend_loopback_trainer_runs():
     a = ShardedBackend(n, 1, 4, 0, torch.device("cuda"), loopback=True).expvals(x, theta)
     b = PassBackend(n, 1).expvals(x, theta)
     np.testing.assert_allclose(a.cpu().numpy(), b.cpu().numpy(), atol=3e-5)
+
+
+def test_parity_readout_kernel_matches_torch():
+    """qfx_sv_large_expz_masks on random states, arbitrary masks, with rank bits above the shard."""
+    from qfedx_b200.ops.large import expvals_parity
+    n_local, B, high = 14, 3, 5
+    g = torch.Generator().manual_seed(7)
+    st = torch.complex(torch.randn(B, 1 << n_local, generator=g), torch.randn(B, 1 << n_local, generator=g)).cuda()
+    masks = [int(m) for m in torch.randint(1, 1 << 17, (9,), generator=g)]
+    got = expvals_parity(st.to(torch.complex64), n_local, masks, high_bits=high).cpu().double().numpy()
+    idx = (high << n_local) | np.arange(1 << n_local, dtype=np.int64)
+    p = (st.abs() ** 2).cpu().double().numpy()
+    for j, m in enumerate(masks):
+        par = np.zeros_like(idx)
+        v = idx & m
+        while v.any():
+            par ^= v & 1
+            v >>= 1
+        np.testing.assert_allclose(got[:, j], (p * (1 - 2 * par)).sum(1), rtol=2e-5)
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_sharded_parity_readout_replaces_final_ring(world):
+    """Two layers: the first ring is simulated (swaps), the second only changes the readout masks."""
+    from qfedx_b200.fl.trainers_large import ShardedBackend
+    n, L = 14, 2
+    g = torch.Generator().manual_seed(world)
+    ang = (torch.rand(2, n, generator=g) * math.pi).cuda()
+    theta = torch.randn(L * n * 2, generator=g).cuda()
+    be = ShardedBackend(n, L, world, 0, torch.device("cuda"), loopback=True)
+    assert be.plan.n_swaps >= 1
+    st_ref = ref.vqc_state_ref(ang.cpu().double(), theta.cpu().double().reshape(1, L, n, 2))
+    np.testing.assert_allclose(be.expvals(ang, theta).cpu().numpy(), ref.expval_z_all(st_ref).numpy(), atol=3e-5)
+    be.n_out = 3
+    np.testing.assert_allclose(be.expvals(ang, theta).cpu().numpy(), ref.expval_z_all(st_ref).numpy()[:, :3], atol=3e-5)
