@@ -251,7 +251,8 @@ def run_large(cfg, name, args, rank, world, local):
     # full-state simulations per round over the whole job, and the gate applications they contain
     P = model.n_angle_params
     steps_per_client = cfg["epochs"] * ((per + cfg["batch"] - 1) // cfg["batch"])
-    per_step = cfg["batch"] * ((1 + 2 * P) if cfg["grad"] == "param_shift" else 3)
+    # parameter shift: the last layer's n RZ angles have an exactly zero gradient for a Z-basis readout and are skipped
+    per_step = cfg["batch"] * ((1 + 2 * (P - n)) if cfg["grad"] == "param_shift" else 3)
     sims = K * steps_per_client * per_step + cfg["test_n"]
     n_gates = len(ansatz_gates(n, L))                      # feature map + ansatz
     return dict(ms=ms, e2e_ms=e2e_ms, clocks=clocks, launches=launches,

@@ -285,8 +285,13 @@ class LargeVQC:
         S, P, dev = angles.shape[0], self.n_params, angles.device
         grad = torch.zeros(P, device=dev)
         per_chunk = max(1, max_states // (2 * S))          # parameters per chunk
-        for p0 in range(0, P, per_chunk):
-            ps = torch.arange(p0, min(P, p0 + per_chunk), device=dev)
+        # The last layer's RZ angles cannot move a Z-basis readout: RZ is diagonal and what follows it (the final
+        # ring) only permutes or re-phases basis states, so |psi_i|^2 is unchanged - their gradient is exactly 0
+        # and their 2n shifted circuits are not simulated.
+        last_rz = {(self.L - 1) * self.n * 2 + 2 * q + 1 for q in range(self.n)} if self.L > 0 else set()
+        live = [p for p in range(P) if p not in last_rz]
+        for c0 in range(0, len(live), per_chunk):
+            ps = torch.tensor(live[c0:c0 + per_chunk], device=dev)
             # item order (param, sign, sample): row -> sample = row % S keeps angle_rows = S valid
             sp = ps.repeat_interleave(2 * S).to(torch.int32)
             sv = torch.tensor([np.pi / 2, -np.pi / 2], device=dev).repeat_interleave(S).repeat(len(ps)).float()
