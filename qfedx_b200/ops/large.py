@@ -290,12 +290,45 @@ class LargeVQC:
         # and their 2n shifted circuits are not simulated.
         last_rz = {(self.L - 1) * self.n * 2 + 2 * q + 1 for q in range(self.n)} if self.L > 0 else set()
         live = [p for p in range(P) if p not in last_rz]
-        for c0 in range(0, len(live), per_chunk):
-            ps = torch.tensor(live[c0:c0 + per_chunk], device=dev)
-            # item order (param, sign, sample): row -> sample = row % S keeps angle_rows = S valid
-            sp = ps.repeat_interleave(2 * S).to(torch.int32)
-            sv = torch.tensor([np.pi / 2, -np.pi / 2], device=dev).repeat_interleave(S).repeat(len(ps)).float()
-            E = self._readout(angles, theta.reshape(1, P), sp, sv, batch=len(sp), n_out=n_out)
-            val = (E.reshape(len(ps), 2, S, n_out) * cot[None, None]).sum(dim=(2, 3))
-            grad[ps] = 0.5 * (val[:, 0] - val[:, 1])
+        # A shifted angle that first appears in pass k leaves passes 0..k-1 untouched: those run once per
+        # minibatch on the unshifted circuit and every shifted state of the group starts from a copy.
+        groups = {}
+        for p in live:
+            groups.setdefault(self._first_pass_of_param().get(p, 0) if angles.is_cuda else 0, []).append(p)
+        th = theta.reshape(1, P)
+        prefix, prefix_k = None, 0
+        for k in sorted(groups):
+            if k > 0:
+                if prefix is None:
+                    prefix = torch.empty(S, 1 << self.n, dtype=torch.complex64, device=dev)
+                run_passes(prefix, self.n, self.readout_passes[prefix_k:k], th, angles, init_zero=(prefix_k == 0),
+                           low_bits=self.low_bits, use_register_engine=self.register_engine)
+                prefix_k = k
+            for c0 in range(0, len(groups[k]), per_chunk):
+                ps = torch.tensor(groups[k][c0:c0 + per_chunk], device=dev)
+                # item order (param, sign, sample): row -> sample = row % S keeps angle_rows = S valid
+                sp = ps.repeat_interleave(2 * S).to(torch.int32)
+                sv = torch.tensor([np.pi / 2, -np.pi / 2], device=dev).repeat_interleave(S).repeat(len(ps)).float()
+                if k == 0:
+                    E = self._readout(angles, th, sp, sv, batch=len(sp), n_out=n_out)
+                else:
+                    st = prefix.repeat(2 * len(ps), 1)
+                    run_passes(st, self.n, self.readout_passes[k:], th, angles, sp, sv, init_zero=False,
+                               low_bits=self.low_bits, use_register_engine=self.register_engine)
+                    E = expvals_parity(st, self.n, self.readout_masks[:n_out])
+                val = (E.reshape(len(ps), 2, S, n_out) * cot[None, None]).sum(dim=(2, 3))
+                grad[ps] = 0.5 * (val[:, 0] - val[:, 1])
         return grad
+
+    def _first_pass_of_param(self) -> dict:
+        """parameter index -> index of the (only) readout pass whose gates use it."""
+        if getattr(self, "_param_pass", None) is None:
+            self._param_pass = {}
+            for k, p in enumerate(self.readout_passes):
+                for op in p.ops:
+                    kind = int(op[0])
+                    if kind in (GATE["rx"], GATE["ry"], GATE["rz"], GATE["rxrz"]):
+                        self._param_pass.setdefault(int(op[3]), k)
+                    if kind == GATE["rxrz"]:
+                        self._param_pass.setdefault(int(op[4]), k)
+        return self._param_pass

@@ -133,3 +133,37 @@ def test_sharded_parity_readout_replaces_final_ring(world):
     np.testing.assert_allclose(be.expvals(ang, theta).cpu().numpy(), ref.expval_z_all(st_ref).numpy(), atol=3e-5)
     be.n_out = 3
     np.testing.assert_allclose(be.expvals(ang, theta).cpu().numpy(), ref.expval_z_all(st_ref).numpy()[:, :3], atol=3e-5)
+
+
+def test_param_shift_prefix_sharing_multi_pass():
+    """Shifted angles that first appear in a later pass start from the shared unshifted prefix; the last layer's RZ
+    angles are skipped (zero gradient).  Checked against the adjoint kernel (small tiles force several passes) and
+    against explicit shifts of the full circuit on the 12-qubit-tile engine."""
+    from qfedx_b200.ops.large import LargeVQC
+    n, L, S = 10, 2, 3
+    g = torch.Generator().manual_seed(5)
+    ang = (torch.rand(S, n, generator=g) * math.pi).cuda()
+    theta = torch.randn(L * n * 2, generator=g).cuda()
+    cot = torch.randn(S, n, generator=g).cuda()
+    vqc = LargeVQC(n, L, tile_bits=6)
+    assert len(vqc.readout_passes) >= 3 and len(set(vqc._first_pass_of_param().values())) >= 3
+    grad = vqc.param_shift_grad(ang, theta, cot, max_states=32)
+    gadj, _ = svop.sv_backward(ang, theta.reshape(1, L, n, 2), cot)
+    np.testing.assert_allclose(grad.cpu().numpy(), gadj.reshape(-1).cpu().numpy(), atol=3e-4)
+
+    n, L, S = 14, 2, 2
+    ang = (torch.rand(S, n, generator=g) * math.pi).cuda()
+    theta = torch.randn(L * n * 2, generator=g).cuda()
+    cot = torch.randn(S, 3, generator=g).cuda()                      # three logit qubits read out
+    vqc = LargeVQC(n, L)
+    fp = vqc._first_pass_of_param()
+    assert len(vqc.readout_passes) >= 2 and max(fp.values()) >= 1
+    grad = vqc.param_shift_grad(ang, theta, cot, max_states=64)
+    later = [p for p, k in fp.items() if k >= 1][:3]
+    for p in [0, 5, 2 * n + 4, 2 * n + 1] + later:                   # incl. a last-layer RZ angle (index 2n+1)
+        tp, tm = theta.clone(), theta.clone()
+        tp[p] += math.pi / 2
+        tm[p] -= math.pi / 2
+        d = vqc.expvals(ang, tp.reshape(1, -1), 3) - vqc.expvals(ang, tm.reshape(1, -1), 3)
+        assert float(grad[p]) == pytest.approx(0.5 * float((d * cot).sum()), abs=3e-4)
+    assert float(grad[2 * n + 1]) == 0.0
