@@ -282,7 +282,8 @@ def run_cfed(cfg, args, rank, world, local):
     model = TinyCNN(cfg["classes"]).to(dev)
     trainer = TinyCNNBatchedTrainer(model, data, cfg["epochs"], cfg["batch"], cfg["lr"],
                                     shuffle_mode=os.environ.get("QFX_SHUFFLE", "array"),
-                                    conv2=os.environ.get("QFX_CONV2", "tcgen05"))
+                                    conv2=os.environ.get("QFX_CONV2", "tcgen05"),
+                                    overlap_steps=os.environ.get("QFX_OVERLAP", "1") == "1")
     all_sizes = torch.tensor([len(c[0]) for c in clients], dtype=torch.float32)
     flc = FLConfig(num_rounds=10 ** 9, mode="delta", clip=cfg["clip"], sigma=cfg["sigma"], quiet=True)
     agg = make_aggregator(rank, world, mine, all_sizes, trainer.dim, dev)

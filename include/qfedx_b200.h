@@ -152,6 +152,16 @@ int qfx_tinycnn_train_step(const float* X, const int* labels, const int* offsets
                            float* params, float* moment, int nd, int n_classes, float lr, float momentum,
                            float p_drop, unsigned long long seed, int round, const int* round_dev,
                            void* workspace, int conv2_mode, unsigned long long shuffle_key, cudaStream_t stream);
+/* Same step, pipelined across steps: the conv2 parameter update stays on the library's side stream behind the conv2
+ * weight gradient, and the NEXT call's conv1 forward runs beside it (conv1 output alternates between two buffers);
+ * the owed work is joined in front of the next conv2 forward.  Call qfx_tinycnn_finish_steps(stream) after the last
+ * step of a sequence - before reading parameters or statistics, and before ending a stream capture. */
+int qfx_tinycnn_train_step_overlapped(const float* X, const int* labels, const int* offsets, const int* perm, int n_total,
+                           const int* client_ids, int n_selected, int epoch, int batch_index, int batch_size,
+                           float* params, float* moment, int nd, int n_classes, float lr, float momentum,
+                           float p_drop, unsigned long long seed, int round, const int* round_dev,
+                           void* workspace, int conv2_mode, unsigned long long shuffle_key, cudaStream_t stream);
+int qfx_tinycnn_finish_steps(cudaStream_t stream);
 /* Evaluation (evaluate_model, /root/reference/src/CFed/Classical_FL.py:83-102) in three launches:
  * out2 = (loss sum, #correct); scratch needs n * 23,520 + 102,400 bytes. */
 int qfx_tinycnn_eval(const float* X, const int* labels, int n, const float* params, int n_classes,

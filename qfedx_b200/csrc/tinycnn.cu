@@ -564,7 +564,7 @@ __global__ void __launch_bounds__(256) sgd_conv_train(const Step s) {
     const int NC = s.n_classes;
     if (p0 >= NCONV) {
         const int i = p0 - NCONV;
-        if (i >= NC * 64 + NC + 64) return;
+        if (i >= NC * 64 + NC + 64 || s.sgd_part == 2) return;
         const int p = i < NC * 64 + NC ? F2W + i : F1B + (i - NC * 64 - NC);
         const float m = s.momentum * mom[p] + s.head_grad[(size_t)sel * HEAD_GRAD_STRIDE + i];
         mom[p] = m;
@@ -572,6 +572,7 @@ __global__ void __launch_bounds__(256) sgd_conv_train(const Step s) {
         return;
     }
     const int p = p0;
+    if ((s.sgd_part == 1 && p >= C2W) || (s.sgd_part == 2 && p < C2W)) return;
     const float* part = s.conv_part + (size_t)sel * BS * NCONV + p;
     float g = 0.f;
     // conv1 partials always have one row per image; conv2 partials have BS / wgrad_ipc rows
@@ -670,13 +671,14 @@ using namespace qfx;
 using namespace qfx::cnn;
 
 extern "C" int qfx_tinycnn_workspace_bytes(int n_selected, size_t* bytes) {
-    // a1,i1,a2,i2,fc1_part,h1,dh1,g2,da1,conv_part,stats  (256-byte aligned pieces)
+    // a1,i1,a2,i2,fc1_part,g2,da1,conv_part,operand copies,head_grad,a1_alt,stats  (256-byte aligned pieces)
     const size_t K = (size_t)n_selected;
     size_t tot = 0;
     auto add = [&](size_t n) { tot += (n + 255) & ~(size_t)255; };
     add(K * BS * 3136 * 4); add(K * BS * 3136); add(K * BS * 1568 * 4); add(K * BS * 1568);
     add(K * FC1_SLICES * BS * 64 * 4);
     add(K * BS * 32 * 196 * 4); add(K * BS * 3136 * 4); add(K * BS * NCONV * 4); add(K * 12800 * 4); add(K * 12800 * 4); add(K * 12800 * 2); add(K * 12800 * 2); add(K * HEAD_GRAD_STRIDE * 4);
+    add(K * BS * 3136 * 4);   // a1_alt
     add(K * 2 * 4);
     *bytes = tot;
     return 0;
@@ -693,7 +695,9 @@ static void carve(Step& s, void* workspace, size_t K) {
     s.w2f = (float*)take(K * 12800 * 4); s.w2b = (float*)take(K * 12800 * 4);
     s.w2uf = (__nv_bfloat16*)take(K * 12800 * 2); s.w2ub = (__nv_bfloat16*)take(K * 12800 * 2);
     s.head_grad = (float*)take(K * HEAD_GRAD_STRIDE * 4);
+    s.a1_alt = (float*)take(K * BS * 3136 * 4);
     s.stats = (float*)take(K * 2 * 4);
+    s.sgd_part = 0;
 }
 
 // Call once per round after the global parameters were broadcast into `params`: builds the
@@ -711,12 +715,17 @@ extern "C" int qfx_tinycnn_begin_round(const float* params, int nd, int n_select
 // One SGD step for every selected client: 8 kernels on `stream` (capture them in a CUDA graph).
 // `workspace` comes from qfx_tinycnn_workspace_bytes; stats (last 2K floats of it) accumulate the
 // epoch's loss sum and correct count - the caller zeroes them per epoch.
-extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const int* offsets, const int* perm,
-                                      int n_total, const int* client_ids, int n_selected, int epoch,
-                                      int batch_index, int batch_size, float* params, float* moment, int nd,
-                                      int n_classes, float lr, float momentum, float p_drop,
-                                      unsigned long long seed, int round, const int* round_dev, void* workspace,
-                                      int conv2_mode, unsigned long long shuffle_key, cudaStream_t stream) {
+// Overlapped steps: the side stream still owes the conv2 update of the previous step; the owed work is joined in
+// front of the next conv2 forward (or by qfx_tinycnn_finish_steps).  a1 alternates between two buffers.
+static bool g_side_pending = false;
+static int g_a1_parity = 0;
+
+static int train_step_impl(const float* X, const int* labels, const int* offsets, const int* perm,
+                           int n_total, const int* client_ids, int n_selected, int epoch,
+                           int batch_index, int batch_size, float* params, float* moment, int nd,
+                           int n_classes, float lr, float momentum, float p_drop,
+                           unsigned long long seed, int round, const int* round_dev, void* workspace,
+                           int conv2_mode, unsigned long long shuffle_key, cudaStream_t stream, bool overlap) {
     QFX_ARG_CHECK(conv2_mode == 0 || conv2_mode == 1, QFX_ERR_BAD_ARG, "conv2_mode must be 0 (fp32) or 1 (tcgen05 bf16)");
     QFX_ARG_CHECK(batch_size >= 1 && batch_size <= BS, QFX_ERR_UNSUPPORTED,
                   "client-batched TinyCNN supports batch_size <= %d, got %d", BS, batch_size);
@@ -736,13 +745,21 @@ extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const i
     // few clients -> few CTAs: spread the channel groups of the conv2 kernels over up to 4 CTAs per image
     s.split = n_selected >= 4 ? 1 : (n_selected >= 2 ? 2 : 4);
     const dim3 gsplit(batch_size, n_selected, s.split);
-    conv1_fwd_train<<<gimg, 224, 0, stream>>>(s);
+    if (int e = side_stream_init()) return e;
+    if (overlap) {
+        g_a1_parity ^= 1;
+        if (g_a1_parity) { float* t = s.a1; s.a1 = s.a1_alt; s.a1_alt = t; }
+    }
+    conv1_fwd_train<<<gimg, 224, 0, stream>>>(s);   // overlapped mode: beside the previous step's conv2 wgrad + update
+    if (g_side_pending) {
+        QFX_CUDA_TRY(cudaStreamWaitEvent(stream, g_join_event, 0));
+        g_side_pending = false;
+    }
     if (conv2_mode == 1) { if (int e = launch_conv2_umma_fwd(s, n_selected, stream)) return e; }
     else conv2_fwd_train<<<gsplit, 256 / s.split, CONV2_SMEM, stream>>>(s);
     fc1_fwd_train<<<dim3(FC1_SLICES, n_selected), 128, 0, stream>>>(s);
     fc1_bwd_train<<<dim3(49, n_selected), 256, 0, stream>>>(s);
     // fork: the conv2 weight gradient only needs g2 and a1; it runs beside conv2 dgrad -> conv1 wgrad
-    if (int e = side_stream_init()) return e;
     QFX_CUDA_TRY(cudaEventRecord(g_fork_event, stream));
     QFX_CUDA_TRY(cudaStreamWaitEvent(g_side_stream, g_fork_event, 0));
     if (conv2_mode == 1) {
@@ -753,10 +770,54 @@ extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const i
         conv2_dgrad_train<<<gsplit, 256 / s.split, DGRAD_SMEM, stream>>>(s);
     }
     conv1_wgrad_train<<<gimg, 416, 0, stream>>>(s);
-    QFX_CUDA_TRY(cudaEventRecord(g_join_event, g_side_stream));
-    QFX_CUDA_TRY(cudaStreamWaitEvent(stream, g_join_event, 0));
-    sgd_conv_train<<<dim3((NCONV + 64 + 65 * n_classes + 255) / 256, n_selected), 256, 0, stream>>>(s);
+    const dim3 gsgd((NCONV + 64 + 65 * n_classes + 255) / 256, n_selected);
+    if (!overlap) {
+        QFX_CUDA_TRY(cudaEventRecord(g_join_event, g_side_stream));
+        QFX_CUDA_TRY(cudaStreamWaitEvent(stream, g_join_event, 0));
+        sgd_conv_train<<<gsgd, 256, 0, stream>>>(s);
+    } else {
+        // the conv2 parameters are updated on the side stream right behind their gradient; this stream only
+        // updates conv1 + head and goes on to the next step's conv1 forward
+        Step sb = s;
+        sb.sgd_part = 2;
+        sgd_conv_train<<<gsgd, 256, 0, g_side_stream>>>(sb);
+        QFX_CUDA_TRY(cudaEventRecord(g_join_event, g_side_stream));
+        g_side_pending = true;
+        s.sgd_part = 1;
+        sgd_conv_train<<<gsgd, 256, 0, stream>>>(s);
+    }
     return check_launch("tinycnn_train_step");
+}
+
+extern "C" int qfx_tinycnn_train_step(const float* X, const int* labels, const int* offsets, const int* perm,
+                                      int n_total, const int* client_ids, int n_selected, int epoch,
+                                      int batch_index, int batch_size, float* params, float* moment, int nd,
+                                      int n_classes, float lr, float momentum, float p_drop,
+                                      unsigned long long seed, int round, const int* round_dev, void* workspace,
+                                      int conv2_mode, unsigned long long shuffle_key, cudaStream_t stream) {
+    return train_step_impl(X, labels, offsets, perm, n_total, client_ids, n_selected, epoch, batch_index, batch_size,
+                           params, moment, nd, n_classes, lr, momentum, p_drop, seed, round, round_dev, workspace,
+                           conv2_mode, shuffle_key, stream, false);
+}
+
+extern "C" int qfx_tinycnn_train_step_overlapped(const float* X, const int* labels, const int* offsets,
+                                                 const int* perm, int n_total, const int* client_ids, int n_selected,
+                                                 int epoch, int batch_index, int batch_size, float* params,
+                                                 float* moment, int nd, int n_classes, float lr, float momentum,
+                                                 float p_drop, unsigned long long seed, int round,
+                                                 const int* round_dev, void* workspace, int conv2_mode,
+                                                 unsigned long long shuffle_key, cudaStream_t stream) {
+    return train_step_impl(X, labels, offsets, perm, n_total, client_ids, n_selected, epoch, batch_index, batch_size,
+                           params, moment, nd, n_classes, lr, momentum, p_drop, seed, round, round_dev, workspace,
+                           conv2_mode, shuffle_key, stream, true);
+}
+
+extern "C" int qfx_tinycnn_finish_steps(cudaStream_t stream) {
+    if (g_side_pending) {
+        QFX_CUDA_TRY(cudaStreamWaitEvent(stream, g_join_event, 0));
+        g_side_pending = false;
+    }
+    return 0;
 }
 
 extern "C" int qfx_tinycnn_stats_offset(int n_selected, size_t* offset) {

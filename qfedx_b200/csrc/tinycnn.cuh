@@ -34,6 +34,9 @@ struct Step {
     unsigned long long shuffle_key;  // non-zero and perm == null: keyed Feistel sample order
     // activations / workspaces, all [K_sel, ...]
     float* a1; unsigned char* i1;    // [K,32,16,14,14]
+    float* a1_alt;                   // second a1 buffer: overlapped steps alternate, so the next step's conv1 forward
+                                     // may run while this step's conv2 weight gradient still reads a1
+    int sgd_part;                    // sgd_conv_train: 0 everything, 1 conv1 + head only, 2 conv2 only
     float* a2; unsigned char* i2;    // [K,32,32,7,7]
     float* fc1_part;                 // [K,16,32,64]
     float* g2;                       // [K,32,32,14,14]

@@ -22,7 +22,8 @@ KERNELS_PER_STEP = 8
 class TinyCNNBatchedTrainer:
     def __init__(self, model: TinyCNN, data: FederatedDataset, epochs: int = 5, batch_size: int = 32,
                  lr: float = 0.01, momentum: float = 0.9, p_drop: float = 0.5, shuffle: bool = True, seed: int = 0,
-                 use_graph: bool = True, generator=None, conv2: str = "tcgen05", shuffle_mode: str = "array"):
+                 use_graph: bool = True, generator=None, conv2: str = "tcgen05", shuffle_mode: str = "array",
+                 overlap_steps: bool = True):
         if data.device.type != "cuda":
             raise _lib.QfxError("TinyCNNBatchedTrainer runs on CUDA only; use TorchLocalTrainer on CPU")
         if batch_size > 32:
@@ -35,6 +36,9 @@ class TinyCNNBatchedTrainer:
         self.shuffle_mode = shuffle_mode
         self.n_classes = model.num_classes
         self.conv2_mode = {"fp32": 0, "tcgen05": 1}[conv2]   # tcgen05: bf16 operands, fp32 accumulate
+        # pipelined steps: the conv2 update of step k runs beside conv1 forward of step k+1 (one more launch per step)
+        self.overlap_steps = bool(overlap_steps)
+        self.kernels_per_step = KERNELS_PER_STEP + (1 if self.overlap_steps else 0)
         self.n_wrap = 0
         self._template = {k: v.detach().clone() for k, v in model.state_dict().items()}
         self.dim = sum(v.numel() for v in self._template.values())
@@ -108,7 +112,8 @@ class TinyCNNBatchedTrainer:
         for e in range(self.epochs):
             st["stats"].zero_()
             for b in range(n_batches):
-                _lib.call("qfx_tinycnn_train_step", _lib.ptr(self.X), _lib.ptr(self.labels),
+                _lib.call("qfx_tinycnn_train_step_overlapped" if self.overlap_steps else "qfx_tinycnn_train_step",
+                          _lib.ptr(self.X), _lib.ptr(self.labels),
                           _lib.ptr(self.data.offsets), perm_ptr, _lib.c_int(self.X.shape[0]), _lib.ptr(st["sel"]),
                           _lib.c_int(K), _lib.c_int(e), _lib.c_int(b), _lib.c_int(self.batch_size),
                           _lib.ptr(st["params"]), _lib.ptr(st["moment"]), _lib.c_int(self.nd),
@@ -116,7 +121,9 @@ class TinyCNNBatchedTrainer:
                           _lib.c_float(self.p_drop), _lib.c_u64(self.seed), _lib.c_int(rnd), _lib.ptr(self._round_dev),
                           _lib.ptr(st["ws"]),
                           _lib.c_int(self.conv2_mode), _lib.c_u64(self._shuffle_key()), _lib.stream_ptr(),
-                          launches=KERNELS_PER_STEP)
+                          launches=self.kernels_per_step)
+        if self.overlap_steps:   # join the side stream's last conv2 update (also required before a capture ends)
+            _lib.call("qfx_tinycnn_finish_steps", _lib.stream_ptr(), launches=0)
 
     def train(self, global_flat: torch.Tensor, selected, rnd: int):
         sel = [int(k) for k in selected]
@@ -145,7 +152,7 @@ class TinyCNNBatchedTrainer:
                 _lib.LAUNCH_COUNT = before
             st["graph"].replay()
             _lib.LAUNCH_COUNT += st["graph_launches"]
-        self.launches += st["steps"] * KERNELS_PER_STEP
+        self.launches += st["steps"] * self.kernels_per_step
         out = st["params"][:, : self.dim]
         return out, {"train_stats": st["stats"]}
 

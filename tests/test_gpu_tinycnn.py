@@ -39,7 +39,8 @@ def _torch_reference(model, flat0, clients, epochs, bs, lr, mom):
 @pytest.mark.parametrize("conv2", ["fp32", "tcgen05"])
 @pytest.mark.parametrize("sizes", [[70, 45, 32], [50], [33, 64, 40, 32, 41]])   # 1 / 3 / 5 clients: every conv2 split
 @pytest.mark.parametrize("use_graph", [False, True])
-def test_training_matches_eager_torch(use_graph, sizes, conv2):
+@pytest.mark.parametrize("overlap", [True, False])   # pipelined steps (conv2 update beside the next conv1 forward) / plain
+def test_training_matches_eager_torch(use_graph, sizes, conv2, overlap):
     from qfedx_b200.fl.trainers_cnn import TinyCNNBatchedTrainer
     torch.manual_seed(0)
     clients = _clients(sizes)
@@ -47,7 +48,7 @@ def test_training_matches_eager_torch(use_graph, sizes, conv2):
     flat0 = flatten_state(ref_model.state_dict()).float()
     data = FederatedDataset.from_clients(clients, "cuda")
     tr = TinyCNNBatchedTrainer(TinyCNN(3).cuda(), data, epochs=2, batch_size=32, lr=0.05, momentum=0.9, p_drop=0.0,
-                               shuffle=False, use_graph=use_graph, conv2=conv2)
+                               shuffle=False, use_graph=use_graph, conv2=conv2, overlap_steps=overlap)
     ids = list(range(len(sizes)))
     out, info = tr.train(flat0.cuda(), ids, 0)
     exp = _torch_reference(ref_model, flat0.double(), [(x.double(), y) for x, y in clients], 2, 32, 0.05, 0.9)
