@@ -11,6 +11,7 @@
 // Flat parameter layout per client (state_dict order, matches models/tinycnn.py):
 //   conv1.w [16,1,5,5] @0 | conv1.b [16] @400 | conv2.w [32,16,5,5] @416 | conv2.b [32] @13216 |
 //   fc1.w [64,1568] @13248 | fc1.b [64] @113600 | fc2.w [C,64] @113664 | fc2.b [C] @113664+64C
+#include <stdlib.h>
 #include "tinycnn.cuh"
 #include "../../include/qfedx_b200.h"
 
@@ -746,30 +747,35 @@ static int train_step_impl(const float* X, const int* labels, const int* offsets
     s.split = n_selected >= 4 ? 1 : (n_selected >= 2 ? 2 : 4);
     const dim3 gsplit(batch_size, n_selected, s.split);
     if (int e = side_stream_init()) return e;
+    // profiling aid (results are wrong when set): QFX_CNN_SKIP is a bit mask of kernels to leave out, to find the
+    // step's critical path by elimination - 1 conv1 fwd, 2 conv2 fwd, 4 fc1 fwd, 8 fc1 bwd, 16 conv2 wgrad,
+    // 32 conv2 dgrad, 64 conv1 wgrad, 128 updates
+    static const int skip = getenv("QFX_CNN_SKIP") ? atoi(getenv("QFX_CNN_SKIP")) : 0;
     if (overlap) {
         g_a1_parity ^= 1;
         if (g_a1_parity) { float* t = s.a1; s.a1 = s.a1_alt; s.a1_alt = t; }
     }
-    conv1_fwd_train<<<gimg, 224, 0, stream>>>(s);   // overlapped mode: beside the previous step's conv2 wgrad + update
+    if (!(skip & 1)) conv1_fwd_train<<<gimg, 224, 0, stream>>>(s);   // overlapped mode: beside the previous step's conv2 wgrad + update
     if (g_side_pending) {
         QFX_CUDA_TRY(cudaStreamWaitEvent(stream, g_join_event, 0));
         g_side_pending = false;
     }
-    if (conv2_mode == 1) { if (int e = launch_conv2_umma_fwd(s, n_selected, stream)) return e; }
+    if (skip & 2) {}
+    else if (conv2_mode == 1) { if (int e = launch_conv2_umma_fwd(s, n_selected, stream)) return e; }
     else conv2_fwd_train<<<gsplit, 256 / s.split, CONV2_SMEM, stream>>>(s);
-    fc1_fwd_train<<<dim3(FC1_SLICES, n_selected), 128, 0, stream>>>(s);
-    fc1_bwd_train<<<dim3(49, n_selected), 256, 0, stream>>>(s);
+    if (!(skip & 4)) fc1_fwd_train<<<dim3(FC1_SLICES, n_selected), 128, 0, stream>>>(s);
+    if (!(skip & 8)) fc1_bwd_train<<<dim3(49, n_selected), 256, 0, stream>>>(s);
     // fork: the conv2 weight gradient only needs g2 and a1; it runs beside conv2 dgrad -> conv1 wgrad
     QFX_CUDA_TRY(cudaEventRecord(g_fork_event, stream));
     QFX_CUDA_TRY(cudaStreamWaitEvent(g_side_stream, g_fork_event, 0));
     if (conv2_mode == 1) {
-        if (int e = launch_conv2_umma_wgrad(s, n_selected, g_side_stream)) return e;
-        if (int e = launch_conv2_umma_dgrad(s, n_selected, stream)) return e;
+        if (!(skip & 16)) { if (int e = launch_conv2_umma_wgrad(s, n_selected, g_side_stream)) return e; }
+        if (!(skip & 32)) { if (int e = launch_conv2_umma_dgrad(s, n_selected, stream)) return e; }
     } else {
         conv2_wgrad_train<<<dim3(BS, n_selected, s.split), 320 / s.split, WGRAD_SMEM, g_side_stream>>>(s);
         conv2_dgrad_train<<<gsplit, 256 / s.split, DGRAD_SMEM, stream>>>(s);
     }
-    conv1_wgrad_train<<<gimg, 416, 0, stream>>>(s);
+    if (!(skip & 64)) conv1_wgrad_train<<<gimg, 416, 0, stream>>>(s);
     const dim3 gsgd((NCONV + 64 + 65 * n_classes + 255) / 256, n_selected);
     if (!overlap) {
         QFX_CUDA_TRY(cudaEventRecord(g_join_event, g_side_stream));
@@ -780,11 +786,11 @@ static int train_step_impl(const float* X, const int* labels, const int* offsets
         // updates conv1 + head and goes on to the next step's conv1 forward
         Step sb = s;
         sb.sgd_part = 2;
-        sgd_conv_train<<<gsgd, 256, 0, g_side_stream>>>(sb);
+        if (!(skip & 128)) sgd_conv_train<<<gsgd, 256, 0, g_side_stream>>>(sb);
         QFX_CUDA_TRY(cudaEventRecord(g_join_event, g_side_stream));
         g_side_pending = true;
         s.sgd_part = 1;
-        sgd_conv_train<<<gsgd, 256, 0, stream>>>(s);
+        if (!(skip & 128)) sgd_conv_train<<<gsgd, 256, 0, stream>>>(s);
     }
     return check_launch("tinycnn_train_step");
 }

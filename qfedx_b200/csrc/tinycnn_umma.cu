@@ -320,30 +320,39 @@ __device__ __forceinline__ void conv2_dgrad_umma_image(const float* __restrict__
 }
 
 // ------------------------------------------------------------------------------------------
-// weight gradient of one image: D_tap[oc, c] = sum_pixels g2[pixel, oc] * a1pad[pixel + tap shift, c].
-// Both operands are read MN-major straight from the half planes.  M is padded to 128 (16 chunks of 8 oc,
-// 4 real): chunks 4..15 alias the activation planes and a zero-filled tail, whose products land in
-// accumulator rows that are never read.
-constexpr int WG_PLANES = 16;
-constexpr int WGRAD_UMMA_SMEM = WG_PLANES * PLANE_BYTES + 128;   // 172,160 B; the fp32 staging tile reuses the tail
+// weight gradient of one image: D[(kx, c), oc] = sum_pixels a1pad[pixel + tap shift, c] * g2[pixel, oc] per filter row.
+// Both operands are read MN-major straight from the half planes.  The A operand is the activation half plane with
+// its 16-byte M chunks only ONE PIXEL (16 B) apart, so M chunk j is the plane shifted by j pixels: rows 0..39 of the
+// accumulator are the five kx taps x 8 channels, rows 40..127 (further shifts) are never read.  B is g2 with its four
+// 8-oc planes as N chunks (N = 32, no padding).  Ten accumulators (5 ky x 2 channel halves) of 32 columns each sit
+// in two TMEM allocations (256 + 64 columns), which leaves 192 columns for the data-gradient CTAs that share the SM.
+// The dynamic shared memory is sized so that exactly ONE weight-gradient CTA fits on an SM (two would deadlock on
+// the second TMEM allocation) while a data-gradient CTA still fits beside it.
+constexpr int WG_PLANES = 6;
+constexpr int WG_STAGE_BYTES = 32 * 401 * 4;
+constexpr int WGRAD_UMMA_SMEM = 120 * 1024;
+static_assert(WG_PLANES * PLANE_BYTES + WG_STAGE_BYTES + 128 <= WGRAD_UMMA_SMEM, "wgrad shared memory layout");
+static_assert(2 * WGRAD_UMMA_SMEM > 227 * 1024, "two weight-gradient CTAs must not fit on one SM");
 __device__ __forceinline__ void conv2_wgrad_umma_image(const float* __restrict__ g2, const float* __restrict__ a1,
                                                        float* __restrict__ part, uint8_t* smem, int n_img) {
     __shared__ __align__(8) uint64_t accum_bar;
-    __shared__ uint32_t tmem_slot;
-    uint8_t* gpl = smem;                          // planes 0..3: g2 (32 oc); 4..5: a1 (16 c); 6..15: zeros
+    __shared__ uint32_t tmem_slot[2];
+    uint8_t* gpl = smem;                          // planes 0..3: g2 (32 oc); 4..5: a1 (16 c)
     uint8_t* apl = smem + 4 * PLANE_BYTES;
+    float* stage = reinterpret_cast<float*>(smem + WG_PLANES * PLANE_BYTES);   // [32 oc][401] fp32
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (warp == 1 && lane == 0) {
         mbar_init1(&accum_bar);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_addr(&tmem_slot)) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(smem_addr(&tmem_slot[0])) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 64;" ::"r"(smem_addr(&tmem_slot[1])) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     zero_bytes16(smem, WG_PLANES * PLANE_BYTES);
     float bias_acc = 0.f;
-    uint32_t tmem = 0;
+    uint32_t tmem0 = 0, tmem1 = 0;
 #pragma unroll 1
     for (int img = 0; img < n_img; ++img) {
         // the previous image's MMAs must have consumed the planes before they are overwritten
@@ -356,48 +365,44 @@ __device__ __forceinline__ void conv2_wgrad_umma_image(const float* __restrict__
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncthreads();
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        tmem = tmem_slot;
+        tmem0 = tmem_slot[0]; tmem1 = tmem_slot[1];
         if (warp == 1 && lane == 0) {
-            // One MMA covers all five kx taps of a filter row: the B operand is read MN-major with its
-            // 16-byte N chunks only ONE PIXEL (16 B) apart, so N chunk j is the activation shifted by j pixels.
-            // N = 48 = 6 shifts x 8 channels of half plane h (the 6th shift is padding to a multiple of 16).
-            constexpr uint32_t idesc = idesc_bf16(128, 48, 1, 1);
+            constexpr uint32_t idesc = idesc_bf16(128, 32, 1, 1);
             const uint32_t ga = smem_addr(gpl), aa = smem_addr(apl);
             // K runs over the stored pixels 64 .. 511 (rows 2..15 of the padded g2 planes), 16 per MMA;
-            // 8-pixel K groups are LBO = 128 B apart.  A: 16-byte oc chunks are SBO = one plane apart.
-            const uint64_t a_hi = desc_noswz(0, 128, PLANE_BYTES) >> 32, b_hi = desc_noswz(0, 128, 16) >> 32;
+            // 8-pixel K groups are LBO = 128 B apart.  A: M chunks one pixel (16 B) apart.  B: oc chunks one plane apart.
+            const uint64_t a_hi = desc_noswz(0, 128, 16) >> 32, b_hi = desc_noswz(0, 128, PLANE_BYTES) >> 32;
             const uint32_t lbo_lo = (uint32_t)((128u >> 4) << 16);
 #pragma unroll 1
             for (int kyh = 0; kyh < 10; ++kyh) {
                 const int ky = kyh >> 1, h = kyh & 1;
-                uint32_t a_lo = (((ga + 64 * 16) >> 4) & 0x3FFF) | lbo_lo;
+                const uint32_t acc_addr = kyh < 8 ? tmem0 + 32 * kyh : tmem1 + 32 * (kyh - 8);
                 // may start 2 pixels before the plane: g2 is zero for those K rows
-                uint32_t b_lo = (((aa + (uint32_t)h * PLANE_BYTES + (uint32_t)(64 - 66 + ky * PITCH) * 16) >> 4) & 0x3FFF) | lbo_lo;
+                uint32_t a_lo = (((aa + (uint32_t)h * PLANE_BYTES + (uint32_t)(64 - 66 + ky * PITCH) * 16) >> 4) & 0x3FFF) | lbo_lo;
+                uint32_t b_lo = (((ga + 64 * 16) >> 4) & 0x3FFF) | lbo_lo;
 #pragma unroll 4
                 for (int kk = 0; kk < 28; ++kk) {
-                    umma_bf16(tmem + 48 * kyh, (a_hi << 32) | a_lo, (b_hi << 32) | b_lo, idesc, (img | kk) ? 1u : 0u);
+                    umma_bf16(acc_addr, (a_hi << 32) | a_lo, (b_hi << 32) | b_lo, idesc, (img | kk) ? 1u : 0u);
                     a_lo += 16; b_lo += 16;   // 16 pixels = 256 B
                 }
             }
             umma_commit1(&accum_bar);
         }
     }
-    if (warp == 4) {   // rows 0..31 (the real oc) live in TMEM lane quarter 0 = warps with id % 4 == 0
+    if (warp >= 4) {   // accumulator row = TMEM lane: rows 0..31 -> lane quarter 0 (warp 4), rows 32..39 -> quarter 1 (warp 5)
         mbar_wait_parity(&accum_bar, (n_img - 1) & 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        float* stage = reinterpret_cast<float*>(smem + 6 * PLANE_BYTES);   // [32 oc][401] fp32 = 51 KB over the zero tail
+        const int row = (warp - 4) * 32 + lane, kx = row >> 3, c8 = row & 7;
+        const uint32_t lane_field = (uint32_t)((warp - 4) * 32) << 16;
 #pragma unroll 1
         for (int kyh = 0; kyh < 10; ++kyh) {
             const int ky = kyh >> 1, h = kyh & 1;
-#pragma unroll 1
-            for (int part3 = 0; part3 < 3; ++part3) {          // 48 columns = 3 loads of 16 = shifts (2 part3, 2 part3 + 1)
-                uint32_t r[16];
-                tmem_ld<16>(tmem + 48 * kyh + 16 * part3, r);
+            uint32_t r[32];
+            tmem_ld<32>((kyh < 8 ? tmem0 + 32 * kyh : tmem1 + 32 * (kyh - 8)) + lane_field, r);
+            if (kx < 5) {
+                const int c = 8 * h + c8;
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    const int kx = 2 * part3 + (j >> 3), c = 8 * h + (j & 7);
-                    if (kx < 5) stage[lane * 401 + c * 25 + ky * 5 + kx] = __uint_as_float(r[j]);
-                }
+                for (int oc = 0; oc < 32; ++oc) stage[oc * 401 + c * 25 + ky * 5 + kx] = __uint_as_float(r[oc]);
             }
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -405,11 +410,11 @@ __device__ __forceinline__ void conv2_wgrad_umma_image(const float* __restrict__
         part[C2B + lane] = bias_acc;
     }
     __syncthreads();
-    {
-        const float* stage = reinterpret_cast<const float*>(smem + 6 * PLANE_BYTES);
-        for (int e = tid; e < 12800; e += blockDim.x) part[C2W + e] = stage[(e / 400) * 401 + (e % 400)];
+    for (int e = tid; e < 12800; e += blockDim.x) part[C2W + e] = stage[(e / 400) * 401 + (e % 400)];
+    if (warp == 2) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tmem0) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 64;" ::"r"(tmem1) : "memory");
     }
-    if (warp == 2) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
 }
 
 __global__ void __launch_bounds__(192) conv2_dgrad_umma_debug(const float* __restrict__ g2, const __nv_bfloat16* __restrict__ w2ub,
