@@ -337,6 +337,7 @@ __device__ __forceinline__ void conv2_wgrad_umma_image(const float* __restrict__
                                                        float* __restrict__ part, uint8_t* smem, int n_img) {
     __shared__ __align__(8) uint64_t accum_bar;
     __shared__ uint32_t tmem_slot[2];
+    __shared__ float bias_sm[32];
     uint8_t* gpl = smem;                          // planes 0..3: g2 (32 oc); 4..5: a1 (16 c)
     uint8_t* apl = smem + 4 * PLANE_BYTES;
     float* stage = reinterpret_cast<float*>(smem + WG_PLANES * PLANE_BYTES);   // [32 oc][401] fp32
@@ -351,7 +352,6 @@ __device__ __forceinline__ void conv2_wgrad_umma_image(const float* __restrict__
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     zero_bytes16(smem, WG_PLANES * PLANE_BYTES);
-    float bias_acc = 0.f;
     uint32_t tmem0 = 0, tmem1 = 0;
 #pragma unroll 1
     for (int img = 0; img < n_img; ++img) {
@@ -360,7 +360,15 @@ __device__ __forceinline__ void conv2_wgrad_umma_image(const float* __restrict__
         __syncthreads();
         fill_half_planes<32>(gpl, g2 + (size_t)img * 32 * 196);
         fill_half_planes<16>(apl, a1 + (size_t)img * 3136);
-        if (warp == 0) for (int i = 0; i < 196; ++i) bias_acc += __ldg(g2 + (size_t)img * 32 * 196 + lane * 196 + i);
+        // conv2 bias gradient in fp32 from the dense g2: every warp sums whole channels with coalesced reads
+        for (int oc = warp; oc < 32; oc += 6) {
+            const float* row = g2 + (size_t)img * 32 * 196 + oc * 196;
+            float v = 0.f;
+#pragma unroll
+            for (int i = 0; i < 7; ++i) { const int p = lane + 32 * i; v += p < 196 ? __ldg(row + p) : 0.f; }
+            v = warp_sum(v);
+            if (lane == 0) bias_sm[oc] = (img ? bias_sm[oc] : 0.f) + v;
+        }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncthreads();
@@ -389,13 +397,17 @@ __device__ __forceinline__ void conv2_wgrad_umma_image(const float* __restrict__
             umma_commit1(&accum_bar);
         }
     }
-    if (warp >= 4) {   // accumulator row = TMEM lane: rows 0..31 -> lane quarter 0 (warp 4), rows 32..39 -> quarter 1 (warp 5)
+    if (warp == 0) part[C2B + lane] = bias_sm[lane];
+    if ((warp & 3) < 2) {
+        // accumulator row = TMEM lane: rows 0..31 sit in lane quarter 0 (warps 0 and 4), rows 32..39 in quarter 1
+        // (warps 1 and 5); the two warps of a quarter take five accumulators each
         mbar_wait_parity(&accum_bar, (n_img - 1) & 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const int row = (warp - 4) * 32 + lane, kx = row >> 3, c8 = row & 7;
-        const uint32_t lane_field = (uint32_t)((warp - 4) * 32) << 16;
+        const int quarter = warp & 3, row = quarter * 32 + lane, kx = row >> 3, c8 = row & 7;
+        const uint32_t lane_field = (uint32_t)(quarter * 32) << 16;
+        const int k0 = (warp >> 2) * 5;
 #pragma unroll 1
-        for (int kyh = 0; kyh < 10; ++kyh) {
+        for (int kyh = k0; kyh < k0 + 5; ++kyh) {
             const int ky = kyh >> 1, h = kyh & 1;
             uint32_t r[32];
             tmem_ld<32>((kyh < 8 ? tmem0 + 32 * kyh : tmem1 + 32 * (kyh - 8)) + lane_field, r);
@@ -406,8 +418,6 @@ __device__ __forceinline__ void conv2_wgrad_umma_image(const float* __restrict__
             }
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    } else if (warp == 0) {   // conv2 bias gradient in fp32 from the dense g2
-        part[C2B + lane] = bias_acc;
     }
     __syncthreads();
     for (int e = tid; e < 12800; e += blockDim.x) part[C2W + e] = stage[(e / 400) * 401 + (e % 400)];
