@@ -116,3 +116,19 @@ def test_pca_reducer_roundtrip():
     assert torch.all(var[:-1] >= var[1:] - 1e-4)                 # components ordered by variance
     q = D.PCAReducer.from_state_dict(p.state_dict())
     assert torch.allclose(q.transform(X), Z)
+
+
+def test_plots_write_files_or_decline_without_matplotlib(tmp_path):
+    """R: src/CFed/Preprocess.py:71-134 - file output only; a missing matplotlib turns the calls into no-ops."""
+    import importlib.util
+    from qfedx_b200.data import partition, synthetic_mnist
+    from qfedx_b200.data.plots import class_distribution_table, plot_class_distribution, visualize_client_data
+    X, y = synthetic_mnist(120, 3, seed=0)
+    clients = partition(X, y, 4, "iid")
+    table = class_distribution_table(clients)
+    assert table.count("\n") >= 4                                   # header + one line per client
+    have = importlib.util.find_spec("matplotlib") is not None
+    a = visualize_client_data(clients, str(tmp_path / "samples.png"))
+    b = plot_class_distribution(clients, str(tmp_path / "dist.png"))
+    assert a == have and b == have
+    assert (tmp_path / "dist.png").exists() == have
