@@ -38,7 +38,19 @@ struct PassArgs {
     const int* shift_param;    // [batch] parameter index to shift, -1 none (nullable)
     const float* shift_value;  // [batch] shift in radians
     int init_zero_state;       // 1: ignore memory contents, start from |0..0>
+    // the qubits OUTSIDE the tile as ascending runs of consecutive positions (filled by the launcher): the CTA
+    // index is deposited into them run by run instead of bit by bit
+    int n_runs, run_pos[MAX_TILE_BITS + 1], run_width[MAX_TILE_BITS + 1];
 };
+
+__device__ __forceinline__ unsigned long long tile_base(const PassArgs& a, unsigned long long t) {
+    unsigned long long base = 0ull;
+    for (int r = 0; r < a.n_runs; ++r) {
+        base |= (t & ((1ull << a.run_width[r]) - 1ull)) << a.run_pos[r];
+        t >>= a.run_width[r];
+    }
+    return base;
+}
 
 __device__ __forceinline__ void cmul_acc(float2& out, float2 m, float2 v) {   // two FFMA per component
     out.x = fmaf(-m.y, v.y, fmaf(m.x, v.x, out.x));
@@ -111,14 +123,7 @@ sv_large_pass_kernel(const PassArgs a) {
         op_matrix(a, op, batch, mats[i]);
     }
     // base offset of this tile: spread blockIdx.x over the non-tile bit positions
-    unsigned long long tile_mask = 0ull;
-    for (int b = 0; b < T; ++b) tile_mask |= 1ull << a.tile_q[b];
-    unsigned long long base = 0ull;
-    {
-        unsigned long long t = blockIdx.x;
-        for (int q = 0; q < a.n_qubits; ++q)
-            if (!((tile_mask >> q) & 1ull)) { base |= (t & 1ull) << q; t >>= 1; }
-    }
+    const unsigned long long base = tile_base(a, blockIdx.x);
     // gather: the low `low_bits` tile bits are qubits 0..low-1, so 2^low consecutive amplitudes move together
     const int low = a.low_bits, chunk = 1 << low;
     for (int j0 = tid * 1; j0 < tile_n; j0 += PASS_THREADS) {
@@ -351,14 +356,7 @@ sv_large_pass_v2_kernel(const PassArgsV2 pa) {
             mats[carrier][tid] = make_float2(cg * v.x - sg * v.y, cg * v.y + sg * v.x);
         }
     }
-    unsigned long long tile_mask = 0ull;
-    for (int b = 0; b < V2_T; ++b) tile_mask |= 1ull << a.tile_q[b];
-    unsigned long long base = 0ull;
-    {
-        unsigned long long t = blockIdx.x;
-        for (int q = 0; q < a.n_qubits; ++q)
-            if (!((tile_mask >> q) & 1ull)) { base |= (t & 1ull) << q; t >>= 1; }
-    }
+    const unsigned long long base = tile_base(a, blockIdx.x);
     __shared__ unsigned long long koff[16];
     if (tid < 16) koff[tid] = deposit_bits((unsigned)tid, 8, V2_T - 8, a.tile_q);
     const unsigned long long toff = base | deposit_bits((unsigned)tid, 0, 8, a.tile_q);
@@ -665,6 +663,18 @@ extern "C" int qfx_sv_large_pass(float* states, int n_qubits, int batch, int til
         a.tile_q[b] = tile_qubits_host[b];
         QFX_ARG_CHECK(b < low_bits ? a.tile_q[b] == b : (a.tile_q[b] > a.tile_q[b - (b > 0)] || b == 0), QFX_ERR_BAD_ARG,
                       "tile qubits must be ascending and start with 0..low_bits-1");
+    }
+    {   // runs of consecutive qubits outside the tile (at most tile_bits + 1 of them)
+        unsigned long long in_tile = 0ull;
+        for (int b = 0; b < tile_bits; ++b) in_tile |= 1ull << a.tile_q[b];
+        a.n_runs = 0;
+        for (int q = 0; q < n_qubits;) {
+            if ((in_tile >> q) & 1ull) { ++q; continue; }
+            int w = 0;
+            while (q + w < n_qubits && !((in_tile >> (q + w)) & 1ull)) ++w;
+            a.run_pos[a.n_runs] = q; a.run_width[a.n_runs] = w; ++a.n_runs;
+            q += w;
+        }
     }
     a.ops = ops_dev; a.n_ops = n_ops; a.theta = theta; a.theta_rows = theta_rows > 0 ? theta_rows : 1; a.n_params = n_params;
     a.angles = angles; a.angle_rows = angle_rows > 0 ? angle_rows : 1; a.n_feature = n_feature;
