@@ -121,3 +121,68 @@ def test_ring_readout_masks_replace_the_final_ring(n, ent):
     masks = ring_readout_masks(n, ent)
     got = np.stack([(p * np.where([bin(i & m).count("1") & 1 for i in idx], -1.0, 1.0)).sum(1) for m in masks], 1)
     np.testing.assert_allclose(got, expect, atol=1e-12)
+
+
+def _emulate_pass_plan(psi, p, theta, angles):
+    """NumPy restatement of what sv_large_pass_v2_kernel does with a segment plan (csrc/sv_large.cu): gates in plan
+    order on the tile's qubits; phase-stripped RX.RZ gates apply diag(1, e^{i phi}) RX(theta) and the carrier gate
+    absorbs the product of the dropped scalars e^{-i phi/2}."""
+    from qfedx_b200.ops.large import GATE, PLAN_KIND_RXRZ_STRIPPED
+    from qfedx_b200.oracle import statevector as sv
+    plan, tq = p.plan.tolist(), [int(q) for q in p.tile_qubits]
+    n_seg, cur = plan[0] & 0xFFFF, 1
+    n_ops = len(p.ops)
+    modes, carrier = plan[len(plan) - n_ops - 1:len(plan) - 1], plan[-1]
+    dropped = sum(-0.5 * theta[int(p.ops[i][4])] for i in range(n_ops) if modes[i] == 1)
+    for _ in range(n_seg):
+        p2b, k_ops = plan[cur:cur + 12], plan[cur + 12]
+        for o in range(k_ops):
+            kind, pa, pb, idx = plan[cur + 13 + 4 * o: cur + 17 + 4 * o]
+            op = p.ops[idx]
+            q0 = tq[p2b[pa]]
+            if kind == GATE["cnot"]:
+                psi = sv.apply_cnot(psi, q0, tq[p2b[pb]])
+            elif kind == GATE["cz"]:
+                psi = sv.apply_cz(psi, q0, tq[p2b[pb]])
+            elif kind == GATE["ry_feature"]:
+                psi = sv.apply_1q(psi, sv.gate_matrix("ry", angles[int(op[3])]), q0)
+            elif kind == PLAN_KIND_RXRZ_STRIPPED:
+                assert modes[idx] == 1
+                m = np.diag([1.0, np.exp(1j * theta[int(op[4])])]) @ sv.gate_matrix("rx", theta[int(op[3])])
+                psi = sv.apply_1q(psi, m, q0)
+            elif kind == GATE["rxrz"]:
+                m = sv.gate_matrix("rz", theta[int(op[4])]) @ sv.gate_matrix("rx", theta[int(op[3])])
+                if idx == carrier:
+                    m = m * np.exp(1j * dropped)
+                psi = sv.apply_1q(psi, m, q0)
+            else:
+                name = {GATE["rx"]: "rx", GATE["ry"]: "ry", GATE["rz"]: "rz"}[kind]
+                psi = sv.apply_1q(psi, sv.gate_matrix(name, theta[int(op[3])]), q0)
+        cur += 13 + 4 * k_ops
+    return psi
+
+
+@pytest.mark.parametrize("n,L,ent,final_ring", [(12, 2, "cnot", True), (13, 2, "cnot", False), (14, 3, "cz", True),
+                                                (13, 1, "cnot", True)])
+def test_segment_plans_reproduce_the_circuit(n, L, ent, final_ring):
+    """Pass compiler + segment planner + phase folding, executed on a dense NumPy state, equal the direct simulation."""
+    from qfedx_b200.ops.large import ansatz_gates, compile_passes
+    from qfedx_b200.oracle import statevector as sv
+    rng = np.random.default_rng(n * 10 + L)
+    theta, angles = rng.normal(size=2 * n * L), rng.uniform(0, np.pi, n)
+    passes = compile_passes(n, ansatz_gates(n, L, ent, final_ring=final_ring), 12, 3)
+    assert all(p.plan is not None for p in passes)
+    psi = sv.zero_state(n)
+    for p in passes:
+        psi = _emulate_pass_plan(psi, p, theta, angles)
+    ref = sv.zero_state(n)
+    for q in range(n):
+        ref = sv.apply_1q(ref, sv.gate_matrix("ry", angles[q]), q)
+    for l in range(L):
+        for q in range(n):
+            ref = sv.apply_1q(ref, sv.gate_matrix("rx", theta[(l * n + q) * 2]), q)
+            ref = sv.apply_1q(ref, sv.gate_matrix("rz", theta[(l * n + q) * 2 + 1]), q)
+        if ent != "none" and (final_ring or l < L - 1):
+            for c, t in sv.ring_pairs(n):
+                ref = sv.apply_cnot(ref, c, t) if ent == "cnot" else sv.apply_cz(ref, c, t)
+    np.testing.assert_allclose(psi, ref, atol=1e-10)
