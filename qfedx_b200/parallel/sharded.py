@@ -64,10 +64,10 @@ def plan_sharded(n_qubits: int, g_bits: int, gates: Sequence[Gate], tile_bits: i
             else:
                 blocked |= set(qs)
                 rest.append(g)
-        if batch:
-            emit_local(batch)
         remaining = rest
         if not remaining:
+            if batch:
+                emit_local(batch)
             break
         # Which local qubits leave?  The g whose next use is farthest away (Belady); they must sit in the
         # top g local positions, because only those exchange as contiguous slices.  Qubits that are needed
@@ -92,8 +92,10 @@ def plan_sharded(n_qubits: int, g_bits: int, gates: Sequence[Gate], tile_bits: i
             other = log_at[t]
             phys_of[v], phys_of[other] = t, pa
             log_at[t], log_at[pa] = v, other
-        if relabel:
-            emit_local(relabel)
+        # the relabelling CNOTs ride in the same compiled batch as the gates before them: they often fit into a
+        # pass that is needed anyway instead of costing a sweep over the shard of their own
+        if batch or relabel:
+            emit_local(batch + relabel)
         incoming = {log_at[n_local + i]: i for i in range(g_bits)}     # logical -> bit of the slice index
         blocked, fused, rest = set(), [], []
         for g in remaining:
