@@ -6,7 +6,9 @@
 // Scheduling is a dependency-aware list scan (gates on disjoint qubits commute): a pass greedily
 // absorbs, in program order, every gate whose operands fit in the tile and whose predecessors on
 // those qubits are already scheduled; a gate that does not fit blocks its qubits for the rest of the
-// scan.  Consecutive RX / RZ on one qubit are fused into one 2x2 gate.  For the ring ansatz of
+// scan.  The tile of a pass is the better of that first-fit tile and the best window of consecutive
+// qubits (which can take the entangler linking it to the previous window together with the next layer's
+// rotations).  Consecutive RX / RZ on one qubit are fused into one 2x2 gate.  For the ring ansatz of
 // /root/reference/ROADMAP.md:126-128 on 20 qubits with 12 tile bits this finds the 2-passes-per-layer
 // schedule (qubits 0..11 | {0,1,2} + 11..19).  Plain C++ (no device code); it lives in a .cu file
 // only so that the one-command build picks it up.
@@ -67,25 +69,54 @@ extern "C" int qfx_circuit_compile(int n_qubits, int n_gates, const int* gates_i
         std::vector<char> in_tile, blocked;
         std::vector<int> chosen;
         int used = 0;
-        // reserve the low qubits for coalescing; if nothing fits next to them, give some of them up
-        for (int lb = low_bits; lb >= 0 && chosen.empty(); --lb) {
-            in_tile.assign(n_qubits, 0);
+        // One scan over the unscheduled gates in program order.  grow = true: the tile starts with `tile` and
+        // absorbs the operands of every gate that still fits (first fit).  grow = false: the tile is fixed and
+        // only gates that lie inside it are taken.  A gate that is not taken blocks its qubits for the rest of
+        // the scan, which keeps the per-qubit order.
+        auto scan = [&](std::vector<char>& tile, int& n_used, bool grow, std::vector<int>& out) {
             blocked.assign(n_qubits, 0);
-            used = 0;
-            for (int q = 0; q < lb; ++q) { in_tile[q] = 1; ++used; }
+            out.clear();
             for (int i = 0; i < G; ++i) {
                 if (done[i]) continue;
                 const Gate& g = gates[i];
                 const bool two = g.kind == QFX_GATE_CNOT || g.kind == QFX_GATE_CZ;
-                const int need = (in_tile[g.q0] ? 0 : 1) + ((two && !in_tile[g.q1]) ? 1 : 0);
+                const int need = (tile[g.q0] ? 0 : 1) + ((two && !tile[g.q1]) ? 1 : 0);
                 const bool free_qubits = !blocked[g.q0] && !(two && blocked[g.q1]);
-                if (free_qubits && used + need <= tile_bits) {
-                    if (!in_tile[g.q0]) { in_tile[g.q0] = 1; ++used; }
-                    if (two && !in_tile[g.q1]) { in_tile[g.q1] = 1; ++used; }
-                    chosen.push_back(i);
+                if (free_qubits && (grow ? n_used + need <= tile_bits : need == 0)) {
+                    if (!tile[g.q0]) { tile[g.q0] = 1; ++n_used; }
+                    if (two && !tile[g.q1]) { tile[g.q1] = 1; ++n_used; }
+                    out.push_back(i);
                 } else {
                     blocked[g.q0] = 1;
                     if (two) blocked[g.q1] = 1;
+                }
+            }
+        };
+        // reserve the low qubits for coalescing; if nothing fits next to them, give some of them up
+        for (int lb = low_bits; lb >= 0 && chosen.empty(); --lb) {
+            in_tile.assign(n_qubits, 0);
+            used = 0;
+            for (int q = 0; q < lb; ++q) { in_tile[q] = 1; ++used; }
+            scan(in_tile, used, true, chosen);
+            // First fit fills the tile with whatever comes first in program order (a whole layer of rotations)
+            // and then cannot take the entangler that links it to the previous tile.  Also try every window of
+            // consecutive qubits next to the reserved low ones and keep the tile that schedules the most gates.
+            const int width = tile_bits - lb;
+            if (width >= 1 && n_qubits - lb > width) {
+                std::vector<char> cand;
+                std::vector<int> cand_chosen;
+                for (int start = lb; start < n_qubits; ++start) {
+                    cand.assign(n_qubits, 0);
+                    int cu = 0;
+                    for (int q = 0; q < lb; ++q) { cand[q] = 1; ++cu; }
+                    for (int k = 0, q = start; k < n_qubits && cu < tile_bits; ++k, q = (q + 1 == n_qubits ? lb : q + 1))
+                        if (!cand[q]) { cand[q] = 1; ++cu; }
+                    scan(cand, cu, false, cand_chosen);
+                    if (cand_chosen.size() > chosen.size()) {
+                        chosen = cand_chosen;
+                        in_tile = cand;
+                        used = cu;
+                    }
                 }
             }
         }
