@@ -236,3 +236,16 @@ def test_random_circuits_compile_and_plan_correctly(seed):
         else:
             ref = sv.apply_1q(ref, sv.gate_matrix(names[k], theta[prm]), q0)
     np.testing.assert_allclose(psi, ref, atol=1e-10)
+
+
+def test_pass_counts_of_the_benchmark_circuits_do_not_regress():
+    """Pass count = trips of the whole state through memory; these are the schedules the measured numbers rest on."""
+    from qfedx_b200.ops.large import ansatz_gates, compile_passes
+    from qfedx_b200.parallel.sharded import plan_sharded
+    readout = lambda n, L: len(compile_passes(n, ansatz_gates(n, L, final_ring=False), 12, 3))
+    assert readout(20, 2) == 2                      # config 4
+    assert readout(24, 2) <= 3
+    assert readout(27, 2) <= 3
+    assert readout(30, 2) <= 4                      # config 5 on one GPU
+    plan = plan_sharded(30, 3, ansatz_gates(30, 2, final_ring=False))
+    assert plan.n_swaps == 1 and sum(len(p) for k, p in plan.steps if k == "local") <= 4   # config 5 on 8 GPUs
