@@ -322,7 +322,17 @@ def run_cfed(cfg, args, rank, world, local):
 def run_reference(cfg, args, rank, world, local):
     ref_dir = os.path.join(ROOT, "baseline", "_ref")
     if not os.path.exists(os.path.join(ref_dir, "Classical_FL.py")):
-        return {"impl": "reference", "unavailable": "baseline/_ref is not installed (see DESIGN.md, reference arm)"}
+        # a fresh clone: recreate the install from the reference tree if this machine has it (build() does the same)
+        try:
+            from qfedx_b200.build import ensure_reference
+            if rank == 0:
+                ensure_reference()
+            barrier(world)
+        except Exception:
+            pass
+    if not os.path.exists(os.path.join(ref_dir, "Classical_FL.py")):
+        return {"impl": "reference", "unavailable": "baseline/_ref is not installed and the reference tree "
+                                                    "(BASELINE.json reference_path) is not on this machine"}
     if args.config != "cfed":
         return {"impl": "reference",
                 "unavailable": f"the reference has no code for config {args.config!r}: no VQC, no simulator loop "
@@ -351,15 +361,19 @@ def run_reference(cfg, args, rank, world, local):
             run(args.warmup)
         if torch.cuda.is_available():
             torch.cuda.synchronize()
-        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        sampler = ClockSampler(torch.cuda.current_device())
-        with sampler:
-            s.record()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            sampler = ClockSampler(torch.cuda.current_device())
+            with sampler:
+                s.record()
+                out = run(args.steps)
+                e.record()
+                torch.cuda.synchronize()
+            ms = s.elapsed_time(e) / args.steps
+            clocks = sampler.summary()
+        else:  # CPU-only machine: the reference picks device=cpu itself (Classical_FL.py:19)
+            t0 = time.perf_counter()
             out = run(args.steps)
-            e.record()
-            torch.cuda.synchronize()
-        ms = s.elapsed_time(e) / args.steps
-        clocks = sampler.summary()
+            ms = (time.perf_counter() - t0) * 1e3 / args.steps
         acc = out["accuracies"][-1]
     barrier(world)
     from qfedx_b200.utils.timing import max_over_ranks
