@@ -34,7 +34,27 @@ inline int check_launch(const char* what) {
         }                                                                      \
     } while (0)
 
+constexpr int QFX_MAX_DEVICES = 64;   // per-device host state tables (streams, events, attribute flags)
 enum : int { QFX_ERR_BAD_ARG = -1, QFX_ERR_UNSUPPORTED = -2, QFX_ERR_TOO_LARGE = -3 };
+
+// ---- per-device host state ------------------------------------------------------------
+// Function attributes and SM counts belong to a device, not to the process: tables are indexed by the
+// current device so that one process can drive several GPUs.
+inline int current_device() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return (dev >= 0 && dev < QFX_MAX_DEVICES) ? dev : 0;
+}
+inline int device_sm_count() {
+    static int sms[QFX_MAX_DEVICES] = {};
+    const int dev = current_device();
+    if (sms[dev] == 0) cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
+    return sms[dev];
+}
+struct PerDeviceFlag {   // "done once on this device" marker
+    bool done[QFX_MAX_DEVICES] = {};
+    bool& here() { return done[current_device()]; }
+};
 
 // ---- counter-based RNG (shared bit-for-bit with qfedx_b200/fl/prng.py) --------------
 // splitmix64 finaliser as a stateless hash; streams are keyed by mixing words in.

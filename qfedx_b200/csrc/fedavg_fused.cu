@@ -368,8 +368,6 @@ fedavg_fused_kernel(const AggArgs a, const int mask_keys_in_smem) {
 
 using AggKernel = void (*)(const AggArgs, const int);
 
-static int g_num_sms = 0;
-
 static int launch_fedavg(AggArgs& a, cudaStream_t stream) {
     QFX_ARG_CHECK(a.k_local >= 0 && a.k_global >= 1 && a.k_global >= a.k_local && a.dim >= 1, QFX_ERR_BAD_ARG, "bad K/D");
     QFX_ARG_CHECK(a.k_local >= 1 || a.world > 1, QFX_ERR_BAD_ARG, "no clients to aggregate");
@@ -380,11 +378,8 @@ static int launch_fedavg(AggArgs& a, cudaStream_t stream) {
                   "bad rank/world");
     QFX_ARG_CHECK(a.world == 1 || (a.recv_slots && a.flags), QFX_ERR_BAD_ARG, "multi-GPU needs slots and flags");
     QFX_ARG_CHECK(a.scratch != nullptr, QFX_ERR_BAD_ARG, "scratch is required");
-    if (g_num_sms == 0) {
-        int dev = 0;
-        QFX_CUDA_TRY(cudaGetDevice(&dev));
-        QFX_CUDA_TRY(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
-    }
+    const int num_sms = device_sm_count();
+    QFX_ARG_CHECK(num_sms > 0, QFX_ERR_UNSUPPORTED, "cannot query the SM count of the current device");
     // pairwise mask keys are hashed once per block into shared memory when they fit
     const size_t kSmemCap = 96 * 1024;
     int mask_keys = a.secagg && agg_smem_bytes(a.k_local, a.k_global, true) <= 32 * 1024 ? 1 : 0;
@@ -397,11 +392,11 @@ static int launch_fedavg(AggArgs& a, cudaStream_t stream) {
     const bool fixed = a.secagg != 0;
     AggKernel kern = vec4 ? (fixed ? (AggKernel)fedavg_fused_kernel<4, 2, true> : (AggKernel)fedavg_fused_kernel<4, 2, false>)
                           : (fixed ? (AggKernel)fedavg_fused_kernel<1, 4, true> : (AggKernel)fedavg_fused_kernel<1, 4, false>);
-    static bool attr_set[4] = {false, false, false, false};
+    static PerDeviceFlag attr_set[4];
     const int which = (vec4 ? 2 : 0) + (fixed ? 1 : 0);
-    if (!attr_set[which]) {
+    if (!attr_set[which].here()) {
         QFX_CUDA_TRY(cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemCap));
-        attr_set[which] = true;
+        attr_set[which].here() = true;
     }
     int occ = 0;
     QFX_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)kern, AGG_THREADS, smem));
@@ -409,7 +404,7 @@ static int launch_fedavg(AggArgs& a, cudaStream_t stream) {
     // small vectors: as few CTAs as cover the vector (grid barriers get cheaper); large: fill the GPU
     const int per_thread = vec4 ? 4 : 1;
     long long blocks = ((long long)a.dim / per_thread + AGG_THREADS - 1) / AGG_THREADS;
-    const long long cap = (long long)g_num_sms * (occ > 6 ? 6 : occ);
+    const long long cap = (long long)num_sms * (occ > 6 ? 6 : occ);
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     void* params[] = {(void*)&a, (void*)&mask_keys};

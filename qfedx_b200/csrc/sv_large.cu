@@ -630,15 +630,7 @@ sv_global_swap_fused_kernel(const SwapArgs a) {
     }
 }
 
-static int g_sms = 0;
-static int num_sms() {
-    if (g_sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev);
-    }
-    return g_sms;
-}
+static int num_sms() { return device_sm_count(); }
 
 }  // namespace large
 }  // namespace qfx

@@ -642,26 +642,41 @@ __global__ void __launch_bounds__(256) head_eval(const float* __restrict__ a2, c
     }
 }
 
-// second stream + events for the fork/join inside a step (works eagerly and under stream capture, where
-// the cross-stream waits become graph dependencies)
-static cudaStream_t g_side_stream = nullptr;
-static cudaEvent_t g_fork_event = nullptr, g_join_event = nullptr;
-static int side_stream_init() {
-    if (g_side_stream) return 0;
-    QFX_CUDA_TRY(cudaStreamCreateWithFlags(&g_side_stream, cudaStreamNonBlocking));
-    QFX_CUDA_TRY(cudaEventCreateWithFlags(&g_fork_event, cudaEventDisableTiming));
-    QFX_CUDA_TRY(cudaEventCreateWithFlags(&g_join_event, cudaEventDisableTiming));
+// Per-device host state: the second stream + events for the fork/join inside a step (works eagerly and under
+// stream capture, where the cross-stream waits become graph dependencies), the pipelining bookkeeping of the
+// overlapped steps and the "attributes set" flags.  Indexed by the current device so that one process can drive
+// several GPUs.
+struct DeviceState {
+    cudaStream_t side_stream = nullptr;
+    cudaEvent_t fork_event = nullptr, join_event = nullptr, dgrad_event = nullptr;
+    bool side_pending = false;   // the side stream still owes the conv2 update of the previous step
+    int a1_parity = 0;
+    bool attr_set = false;
+};
+static DeviceState g_dev[QFX_MAX_DEVICES];
+static int device_state(DeviceState** out) {
+    int dev = 0;
+    QFX_CUDA_TRY(cudaGetDevice(&dev));
+    QFX_ARG_CHECK(dev >= 0 && dev < QFX_MAX_DEVICES, QFX_ERR_UNSUPPORTED, "device index %d beyond %d", dev, QFX_MAX_DEVICES);
+    *out = &g_dev[dev];
+    return 0;
+}
+static int side_stream_init(DeviceState& d) {
+    if (d.side_stream) return 0;
+    QFX_CUDA_TRY(cudaStreamCreateWithFlags(&d.side_stream, cudaStreamNonBlocking));
+    QFX_CUDA_TRY(cudaEventCreateWithFlags(&d.fork_event, cudaEventDisableTiming));
+    QFX_CUDA_TRY(cudaEventCreateWithFlags(&d.join_event, cudaEventDisableTiming));
+    QFX_CUDA_TRY(cudaEventCreateWithFlags(&d.dgrad_event, cudaEventDisableTiming));
     return 0;
 }
 
-static bool g_attr_set = false;
-static int set_attrs() {
-    if (g_attr_set) return 0;
+static int set_attrs(DeviceState& d) {
+    if (d.attr_set) return 0;
     QFX_CUDA_TRY(cudaFuncSetAttribute(conv2_fwd_train, cudaFuncAttributeMaxDynamicSharedMemorySize, CONV2_SMEM));
     QFX_CUDA_TRY(cudaFuncSetAttribute(conv2_fwd_eval, cudaFuncAttributeMaxDynamicSharedMemorySize, CONV2_SMEM));
     QFX_CUDA_TRY(cudaFuncSetAttribute(conv2_dgrad_train, cudaFuncAttributeMaxDynamicSharedMemorySize, DGRAD_SMEM));
     QFX_CUDA_TRY(cudaFuncSetAttribute(conv2_wgrad_train, cudaFuncAttributeMaxDynamicSharedMemorySize, WGRAD_SMEM));
-    g_attr_set = true;
+    d.attr_set = true;
     return 0;
 }
 
@@ -718,9 +733,6 @@ extern "C" int qfx_tinycnn_begin_round(const float* params, int nd, int n_select
 // epoch's loss sum and correct count - the caller zeroes them per epoch.
 // Overlapped steps: the side stream still owes the conv2 update of the previous step; the owed work is joined in
 // front of the next conv2 forward (or by qfx_tinycnn_finish_steps).  a1 alternates between two buffers.
-static bool g_side_pending = false;
-static int g_a1_parity = 0;
-
 static int train_step_impl(const float* X, const int* labels, const int* offsets, const int* perm,
                            int n_total, const int* client_ids, int n_selected, int epoch,
                            int batch_index, int batch_size, float* params, float* moment, int nd,
@@ -733,7 +745,10 @@ static int train_step_impl(const float* X, const int* labels, const int* offsets
     QFX_ARG_CHECK(n_classes >= 2 && n_classes <= MAX_CLASSES, QFX_ERR_UNSUPPORTED, "n_classes %d not in 2..10", n_classes);
     QFX_ARG_CHECK(nd >= F2W + 65 * n_classes, QFX_ERR_BAD_ARG, "parameter row stride too small");
     QFX_ARG_CHECK(n_selected >= 1 && p_drop >= 0.f && p_drop < 1.f, QFX_ERR_BAD_ARG, "bad n_selected / p_drop");
-    if (int e = set_attrs()) return e;
+    DeviceState* dsp = nullptr;
+    if (int e = device_state(&dsp)) return e;
+    DeviceState& d = *dsp;
+    if (int e = set_attrs(d)) return e;
     Step s;
     s.X = X; s.labels = labels; s.offsets = offsets; s.perm = perm; s.client_ids = client_ids;
     s.n_total = n_total; s.epoch = epoch; s.batch_index = batch_index; s.batch_size = batch_size;
@@ -746,19 +761,24 @@ static int train_step_impl(const float* X, const int* labels, const int* offsets
     // few clients -> few CTAs: spread the channel groups of the conv2 kernels over up to 4 CTAs per image
     s.split = n_selected >= 4 ? 1 : (n_selected >= 2 ? 2 : 4);
     const dim3 gsplit(batch_size, n_selected, s.split);
-    if (int e = side_stream_init()) return e;
-    // profiling aid (results are wrong when set): QFX_CNN_SKIP is a bit mask of kernels to leave out, to find the
-    // step's critical path by elimination - 1 conv1 fwd, 2 conv2 fwd, 4 fc1 fwd, 8 fc1 bwd, 16 conv2 wgrad,
-    // 32 conv2 dgrad, 64 conv1 wgrad, 128 updates
+    if (int e = side_stream_init(d)) return e;
+    cudaStream_t side = d.side_stream;
+#ifdef QFX_PROFILE_SKIP
+    // profiling builds only (results are wrong when set; never compiled into the shipped library): QFX_CNN_SKIP is a
+    // bit mask of kernels to leave out, to find the step's critical path by elimination - 1 conv1 fwd, 2 conv2 fwd,
+    // 4 fc1 fwd, 8 fc1 bwd, 16 conv2 wgrad, 32 conv2 dgrad, 64 conv1 wgrad, 128 updates
     static const int skip = getenv("QFX_CNN_SKIP") ? atoi(getenv("QFX_CNN_SKIP")) : 0;
+#else
+    constexpr int skip = 0;
+#endif
     if (overlap) {
-        g_a1_parity ^= 1;
-        if (g_a1_parity) { float* t = s.a1; s.a1 = s.a1_alt; s.a1_alt = t; }
+        d.a1_parity ^= 1;
+        if (d.a1_parity) { float* t = s.a1; s.a1 = s.a1_alt; s.a1_alt = t; }
     }
     if (!(skip & 1)) conv1_fwd_train<<<gimg, 224, 0, stream>>>(s);   // overlapped mode: beside the previous step's conv2 wgrad + update
-    if (g_side_pending) {
-        QFX_CUDA_TRY(cudaStreamWaitEvent(stream, g_join_event, 0));
-        g_side_pending = false;
+    if (d.side_pending) {
+        QFX_CUDA_TRY(cudaStreamWaitEvent(stream, d.join_event, 0));
+        d.side_pending = false;
     }
     if (skip & 2) {}
     else if (conv2_mode == 1) { if (int e = launch_conv2_umma_fwd(s, n_selected, stream)) return e; }
@@ -766,29 +786,32 @@ static int train_step_impl(const float* X, const int* labels, const int* offsets
     if (!(skip & 4)) fc1_fwd_train<<<dim3(FC1_SLICES, n_selected), 128, 0, stream>>>(s);
     if (!(skip & 8)) fc1_bwd_train<<<dim3(49, n_selected), 256, 0, stream>>>(s);
     // fork: the conv2 weight gradient only needs g2 and a1; it runs beside conv2 dgrad -> conv1 wgrad
-    QFX_CUDA_TRY(cudaEventRecord(g_fork_event, stream));
-    QFX_CUDA_TRY(cudaStreamWaitEvent(g_side_stream, g_fork_event, 0));
+    QFX_CUDA_TRY(cudaEventRecord(d.fork_event, stream));
+    QFX_CUDA_TRY(cudaStreamWaitEvent(side, d.fork_event, 0));
     if (conv2_mode == 1) {
-        if (!(skip & 16)) { if (int e = launch_conv2_umma_wgrad(s, n_selected, g_side_stream)) return e; }
+        if (!(skip & 16)) { if (int e = launch_conv2_umma_wgrad(s, n_selected, side)) return e; }
         if (!(skip & 32)) { if (int e = launch_conv2_umma_dgrad(s, n_selected, stream)) return e; }
     } else {
-        conv2_wgrad_train<<<dim3(BS, n_selected, s.split), 320 / s.split, WGRAD_SMEM, g_side_stream>>>(s);
+        conv2_wgrad_train<<<dim3(BS, n_selected, s.split), 320 / s.split, WGRAD_SMEM, side>>>(s);
         conv2_dgrad_train<<<gsplit, 256 / s.split, DGRAD_SMEM, stream>>>(s);
     }
+    if (overlap) QFX_CUDA_TRY(cudaEventRecord(d.dgrad_event, stream));   // the data gradient has read the conv2 weights
     if (!(skip & 64)) conv1_wgrad_train<<<gimg, 416, 0, stream>>>(s);
     const dim3 gsgd((NCONV + 64 + 65 * n_classes + 255) / 256, n_selected);
     if (!overlap) {
-        QFX_CUDA_TRY(cudaEventRecord(g_join_event, g_side_stream));
-        QFX_CUDA_TRY(cudaStreamWaitEvent(stream, g_join_event, 0));
+        QFX_CUDA_TRY(cudaEventRecord(d.join_event, side));
+        QFX_CUDA_TRY(cudaStreamWaitEvent(stream, d.join_event, 0));
         sgd_conv_train<<<gsgd, 256, 0, stream>>>(s);
     } else {
         // the conv2 parameters are updated on the side stream right behind their gradient; this stream only
-        // updates conv1 + head and goes on to the next step's conv1 forward
+        // updates conv1 + head and goes on to the next step's conv1 forward.  The update rewrites the operand
+        // copies (w2b / w2ub) that this step's data gradient reads on the main stream, so it waits for it.
         Step sb = s;
         sb.sgd_part = 2;
-        if (!(skip & 128)) sgd_conv_train<<<gsgd, 256, 0, g_side_stream>>>(sb);
-        QFX_CUDA_TRY(cudaEventRecord(g_join_event, g_side_stream));
-        g_side_pending = true;
+        QFX_CUDA_TRY(cudaStreamWaitEvent(side, d.dgrad_event, 0));
+        if (!(skip & 128)) sgd_conv_train<<<gsgd, 256, 0, side>>>(sb);
+        QFX_CUDA_TRY(cudaEventRecord(d.join_event, side));
+        d.side_pending = true;
         s.sgd_part = 1;
         if (!(skip & 128)) sgd_conv_train<<<gsgd, 256, 0, stream>>>(s);
     }
@@ -819,9 +842,11 @@ extern "C" int qfx_tinycnn_train_step_overlapped(const float* X, const int* labe
 }
 
 extern "C" int qfx_tinycnn_finish_steps(cudaStream_t stream) {
-    if (g_side_pending) {
-        QFX_CUDA_TRY(cudaStreamWaitEvent(stream, g_join_event, 0));
-        g_side_pending = false;
+    DeviceState* d = nullptr;
+    if (int e = device_state(&d)) return e;
+    if (d->side_pending) {
+        QFX_CUDA_TRY(cudaStreamWaitEvent(stream, d->join_event, 0));
+        d->side_pending = false;
     }
     return 0;
 }
@@ -838,7 +863,9 @@ extern "C" int qfx_tinycnn_stats_offset(int n_selected, size_t* offset) {
 extern "C" int qfx_tinycnn_eval(const float* X, const int* labels, int n, const float* params, int n_classes,
                                 void* scratch, float* out2, cudaStream_t stream) {
     QFX_ARG_CHECK(n >= 1 && n_classes >= 2 && n_classes <= MAX_CLASSES, QFX_ERR_BAD_ARG, "bad n / n_classes");
-    if (int e = set_attrs()) return e;
+    DeviceState* d = nullptr;
+    if (int e = device_state(&d)) return e;
+    if (int e = set_attrs(*d)) return e;
     char* w = (char*)scratch;
     float* w2f = (float*)w; w += 12800 * 4;
     float* w2b = (float*)w; w += 12800 * 4;

@@ -473,13 +473,13 @@ __global__ void __launch_bounds__(192) conv2_wgrad_umma_train(const Step s) {
     conv2_wgrad_umma_image(s.g2 + r * 32 * 196, s.a1 + r * 3136, part, smem_dyn, min(ipc, nb - b0));
 }
 
-static bool g_umma_attr = false;
+static PerDeviceFlag g_umma_attr;
 static int umma_attrs() {
-    if (g_umma_attr) return 0;
+    if (g_umma_attr.here()) return 0;
     QFX_CUDA_TRY(cudaFuncSetAttribute(conv2_fwd_umma_train, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM));
     QFX_CUDA_TRY(cudaFuncSetAttribute(conv2_dgrad_umma_train, cudaFuncAttributeMaxDynamicSharedMemorySize, DGRAD_UMMA_SMEM));
     QFX_CUDA_TRY(cudaFuncSetAttribute(conv2_wgrad_umma_train, cudaFuncAttributeMaxDynamicSharedMemorySize, WGRAD_UMMA_SMEM));
-    g_umma_attr = true;
+    g_umma_attr.here() = true;
     return 0;
 }
 int launch_conv2_umma_prep(const float* params, int nd, int n_selected, __nv_bfloat16* w2uf, __nv_bfloat16* w2ub,

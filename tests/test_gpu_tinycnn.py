@@ -95,3 +95,22 @@ def test_dropout_changes_updates_and_training_learns():
     oc, _ = c.train(g0, [0, 1], 0)
     l1, a1 = c.evaluate(oc.mean(0), Xt.cuda(), yt.cuda())
     assert l1 < l0 and a1 > max(a0, 0.5)
+
+
+@pytest.mark.parametrize("conv2", ["fp32", "tcgen05"])
+@pytest.mark.parametrize("sizes", [[70, 45, 32], [50]])
+def test_overlapped_steps_are_bit_identical_to_plain_steps(sizes, conv2):
+    """The pipelined step (conv2 update on the side stream, joined before the next conv2 forward) must not change a
+    single bit: the update may only start after this step's data gradient has read the conv2 operand copies."""
+    from qfedx_b200.fl.trainers_cnn import TinyCNNBatchedTrainer
+    torch.manual_seed(0)
+    clients = _clients(sizes, seed=5)
+    data = FederatedDataset.from_clients(clients, "cuda")
+    flat0 = flatten_state(TinyCNN(3).state_dict()).float().cuda()
+    outs = []
+    for overlap in (False, True, True):
+        tr = TinyCNNBatchedTrainer(TinyCNN(3).cuda(), data, epochs=3, batch_size=32, lr=0.05, momentum=0.9, p_drop=0.5,
+                                   shuffle=False, use_graph=True, conv2=conv2, overlap_steps=overlap)
+        out, _ = tr.train(flat0, list(range(len(sizes))), 0)
+        outs.append(out.clone())
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[1], outs[2])
