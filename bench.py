@@ -57,10 +57,13 @@ VQC30 = dict(clients=8, samples_per_client=1, classes=2, n_qubits=30, n_layers=2
 # "tcgen05" (single bf16 operands) is an opt-in secondary line and is reported as dtype bf16.
 CONV2_IMPL = os.environ.get("QFX_CONV2", "fp32")
 CONV2_PRECISION = {
+    "split": "persistent round kernel; conv2 on tcgen05 with a two-term bf16 split of both operands (3 MMAs per product, "
+             "fp32 accumulate in TMEM: products exact to ~2^-16, tighter than the TF32 cuDNN uses for the reference's "
+             "fp32 conv); everything else fp32",
     "fp32": "fp32 storage, operands and accumulation everywhere (conv2 on CUDA cores)",
     "tcgen05": "conv2 on tcgen05 with bf16 operands + fp32 accumulate; fp32 master weights and other layers",
 }
-CONV2_DTYPE = {"fp32": "fp32", "tcgen05": "bf16"}
+CONV2_DTYPE = {"split": "fp32", "fp32": "fp32", "tcgen05": "bf16"}
 VQC4 = dict(clients=4, n_train=11183, classes=2, n_qubits=4, n_layers=2, epochs=5, batch=32, lr=0.05, test_n=1991)
 
 
@@ -290,7 +293,8 @@ def run_cfed(cfg, args, rank, world, local):
     model = TinyCNN(cfg["classes"]).to(dev)
     trainer = TinyCNNBatchedTrainer(model, data, cfg["epochs"], cfg["batch"], cfg["lr"],
                                     shuffle_mode=os.environ.get("QFX_SHUFFLE", "array"),
-                                    conv2=CONV2_IMPL,
+                                    conv2="tcgen05" if CONV2_IMPL == "split" else CONV2_IMPL,
+                                    engine="persistent" if CONV2_IMPL == "split" else "graph",
                                     overlap_steps=os.environ.get("QFX_OVERLAP", "1") == "1")
     all_sizes = torch.tensor([len(c[0]) for c in clients], dtype=torch.float32)
     flc = FLConfig(num_rounds=10 ** 9, mode="delta", clip=cfg["clip"], sigma=cfg["sigma"], quiet=True)

@@ -167,6 +167,25 @@ int qfx_tinycnn_finish_steps(cudaStream_t stream);
 int qfx_tinycnn_eval(const float* X, const int* labels, int n, const float* params, int n_classes,
                      void* scratch, float* out2, cudaStream_t stream);
 
+/* K8p: the same local training as ONE persistent launch per round (csrc/tinycnn_persist.cu): G CTAs per client stay
+ * resident, walk epochs x minibatches themselves and meet at five group barriers per step; conv2 forward / data
+ * gradient / weight gradient run on tcgen05 with a two-term bf16 split of both operands (3 MMAs, fp32 accumulate:
+ * products exact to ~2^-16).  Restates client_update, /root/reference/src/CFed/Classical_FL.py:40-64.
+ * params [K,nd] = global model in every row, moment [K,nd] = 0 on entry; workspace from
+ * qfx_tinycnn_round_workspace_bytes (its tail at *stats_offset holds the last epoch's (loss sum, #correct) per client).
+ * ctas_per_client 0 = min(32, #SM / K).  qfx_tinycnn_round_status reports a group barrier that gave up waiting. */
+int qfx_tinycnn_round_workspace_bytes(int n_selected, size_t* bytes, size_t* stats_offset);
+int qfx_tinycnn_train_round(const float* X, const int* labels, const int* offsets, const int* perm, int n_total,
+                            const int* client_ids, int n_selected, int epochs, int n_batches, int batch_size,
+                            float* params, float* moment, int nd, int n_classes, float lr, float momentum,
+                            float p_drop, unsigned long long seed, int round, const int* round_dev,
+                            void* workspace, unsigned long long shuffle_key, int ctas_per_client, cudaStream_t stream);
+int qfx_tinycnn_round_status(int n_selected, void* workspace, cudaStream_t stream, int* timed_out);
+/* evaluation with conv2 on the same tensor-core path and precision as qfx_tinycnn_train_round;
+ * scratch: 102,400 + n * 7,840 bytes */
+int qfx_tinycnn_eval_tc(const float* X, const int* labels, int n, const float* params, int n_classes,
+                        void* scratch, float* out2, cudaStream_t stream);
+
 /* K2: batched circuit unitaries as a complex GEMM on tcgen05 / TMEM fed by TMA (no reference
  * counterpart; accelerates the planned VQC forward, /root/reference/ROADMAP.md:126-128).
  *   qfx_unitary_pack: U^T as complex64 rows (row b = U|b>, e.g. qfx_sv_forward's state_out for the

@@ -642,6 +642,12 @@ __global__ void __launch_bounds__(256) head_eval(const float* __restrict__ a2, c
     }
 }
 
+int launch_head_eval(const float* a2, const int* labels, const float* prm, int n_classes, int n, float* out2,
+                     cudaStream_t stream) {
+    head_eval<<<(n + EVB - 1) / EVB, 256, 0, stream>>>(a2, labels, prm, n_classes, n, out2);
+    return check_launch("head_eval");
+}
+
 // Per-device host state: the second stream + events for the fork/join inside a step (works eagerly and under
 // stream capture, where the cross-stream waits become graph dependencies), the pipelining bookkeeping of the
 // overlapped steps and the "attributes set" flags.  Indexed by the current device so that one process can drive

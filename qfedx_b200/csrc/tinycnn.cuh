@@ -115,5 +115,9 @@ int launch_conv2_umma_fwd(const Step& s, int n_selected, cudaStream_t stream);
 int launch_conv2_umma_dgrad(const Step& s, int n_selected, cudaStream_t stream);
 int launch_conv2_umma_wgrad(const Step& s, int n_selected, cudaStream_t stream);
 
+// evaluation head (tinycnn.cu): fc1 + ReLU + fc2 + loss / arg-max over pooled conv2 outputs a2 [n,1568]
+int launch_head_eval(const float* a2, const int* labels, const float* prm, int n_classes, int n, float* out2,
+                     cudaStream_t stream);
+
 }  // namespace cnn
 }  // namespace qfx
