@@ -53,9 +53,10 @@ VQC20 = dict(clients=16, samples_per_client=4, classes=2, n_qubits=20, n_layers=
 # two layers: the last ring is folded into the readout, so one layer would leave no entangler to simulate (and no swap)
 VQC30 = dict(clients=8, samples_per_client=1, classes=2, n_qubits=30, n_layers=2, epochs=1, batch=1, lr=0.05,
              grad="spsa", secagg=False, clip=0.0, test_n=2)
-# conv2 implementation of the cfed headline.  The default must be fp32-accurate (the reference trains in fp32);
-# "tcgen05" (single bf16 operands) is an opt-in secondary line and is reported as dtype bf16.
-CONV2_IMPL = os.environ.get("QFX_CONV2", "fp32")
+# conv2 implementation of the cfed headline.  The default must be fp32-accurate (the reference trains in fp32): "split" is
+# the persistent round kernel with split-bf16 tensor-core conv2 (passes the fp32 test tolerance), "fp32" the all-CUDA-core
+# graph path; "tcgen05" (single bf16 operands) is an opt-in secondary line and is reported as dtype bf16.
+CONV2_IMPL = os.environ.get("QFX_CONV2", "split")
 CONV2_PRECISION = {
     "split": "persistent round kernel; conv2 on tcgen05 with a two-term bf16 split of both operands (3 MMAs per product, "
              "fp32 accumulate in TMEM: products exact to ~2^-16, tighter than the TF32 cuDNN uses for the reference's "

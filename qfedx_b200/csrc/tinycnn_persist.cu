@@ -29,7 +29,11 @@
 namespace qfx {
 namespace cnn {
 
-constexpr int PNT = 512;                      // threads per CTA
+constexpr int PNT = 512;                      // worker threads per CTA (16 warps)
+constexpr int PNT_ALL = PNT + 32;             // + one warp whose lane 0 only issues the tensor-core work
+// Workers synchronise among themselves on named barrier 1; the MMA issuer never joins it, so a full MMA queue
+// cannot hold the workers up (they meet the issuer only through mbarriers).
+#define WSYNC() asm volatile("bar.sync 1, 512;" ::: "memory")
 constexpr int PPLANE = 352 * 16;              // bytes per half plane: 18 rows x 16 pixels x 16 B + zero slack
 constexpr int WOP = 25600;                    // bytes of one bf16 operand copy of the conv2 weights
 constexpr int OFF_A1 = 128;                   // [hi0 hi1 lo0 lo1] activation planes (behind 128 B of zeros)
@@ -46,7 +50,10 @@ static_assert(PSMEM <= 227 * 1024, "shared memory");
 // scratch inside [OFF_WF, OFF_WB + ...): sizes checked against the 2 * WOP bytes of the forward operand
 constexpr int FCX = 116;                      // row stride of the fc1 forward tiles (16-byte aligned rows)
 static_assert((32 + 64) * FCX * 4 <= 2 * WOP, "PB tiles");
-constexpr int TM_FWD = 0, TM_DG = 64, TM_WG = 128;   // TMEM columns: forward 2 x 32, dgrad 2 x 16, wgrad 10 x 32
+// TMEM columns.  Forward (PA) and backward (PD) accumulators are never live together and share columns:
+// forward 2 blocks x 64 (hi | lo weight halves); data gradient 2 x 32; weight gradient 10 x 40 behind it.
+constexpr int TM_FWD = 0, TM_DG = 0, TM_WG = 64, WG_N = 40;
+static_assert(TM_WG + 10 * WG_N <= 512, "TMEM columns");
 constexpr int XS1P = 37;
 
 struct Round {
@@ -56,29 +63,38 @@ struct Round {
     __nv_bfloat16* wop;      // [K,4,12800] conv2 operand copies: forward hi, forward lo, dgrad hi, dgrad lo
     unsigned* bar;           // [K] group barrier counters (zeroed by the host before the launch)
     int* err;                // set when a barrier gave up waiting (a bug elsewhere must not hang the GPU)
+    long long* prof;         // optional [K, G, 20] per-CTA cycle counters per phase (null: no timing)
 };
+// phase timer: thread 0 adds the cycles since the previous mark to slot `id`
+#define QFX_MARK(id)                                                              \
+    do {                                                                          \
+        if (R.prof && tid == 0) {                                                 \
+            const long long _t = clock64();                                       \
+            R.prof[((size_t)sel * gridDim.x + cta) * 20 + (id)] += _t - t_mark;   \
+            t_mark = _t;                                                          \
+        }                                                                         \
+    } while (0)
 
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
     unsigned v;
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
-// All G CTAs of a client meet here.  Writes before the barrier are visible to every CTA of the group after it:
-// __syncthreads orders the CTA's writes before thread 0's gpu-scope fence, the counter is read with acquire
-// semantics, and the second fence keeps later loads of this SM from being served by stale L1 lines.
+// All G CTAs of a client meet here.  Writes before the barrier are visible to every CTA of the group after it: the
+// worker barrier orders the CTA's writes before thread 0's release-add on the counter (cumulativity), the counter
+// is polled with gpu-scope acquire loads (which also drop this SM's stale L1 lines), and the second worker barrier
+// orders every thread's later loads behind thread 0's acquire.
 __device__ __forceinline__ void group_barrier(unsigned* ctr, unsigned& target, unsigned G, int* err) {
     target += G;
-    __syncthreads();
+    WSYNC();
     if (threadIdx.x == 0) {
-        __threadfence();
-        atomicAdd(ctr, 1u);
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
         unsigned spins = 0;
         while (ld_acquire_u32(ctr) < target) {
             if (++spins > (1u << 26)) { atomicExch(err, 1); break; }   // ~seconds: give up instead of hanging
         }
-        __threadfence();
     }
-    __syncthreads();
+    WSYNC();
 }
 
 __device__ __forceinline__ void mbar_wait_all(uint64_t* bar, uint32_t& parity) {
@@ -86,12 +102,41 @@ __device__ __forceinline__ void mbar_wait_all(uint64_t* bar, uint32_t& parity) {
     parity ^= 1u;
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(bar)) : "memory");
+}
+// workers: operands written -> visible to the tensor core -> tell the issuer
+__device__ __forceinline__ void hand_to_issuer(uint64_t* ready) {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    WSYNC();
+    if (threadIdx.x == 0) mbar_arrive(ready);
+}
 // generic-proxy writes to shared memory -> visible to the tensor core, then a CTA-wide sync
 __device__ __forceinline__ void publish_operands() {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+
+// Operand copies of the conv2 weights (bf16, written by PE / the prep kernel, 2048 B per filter tap):
+//   forward        [tap][k-chunk c/8 (2)][hi|lo][oc group (4)][8 oc][8 c]          B = [N = (hi|lo, oc)][K = c]
+//   data gradient  [24-tap][k-chunk oc/8 (4)][hi|lo][c group (2)][8 c][8 oc]       B = [N = (hi|lo, c)][K = oc]
+// Putting the hi and lo halves of the weights side by side in N lets ONE MMA multiply an activation half plane by
+// both (the epilogue adds the two column halves), so a split product costs two activation reads instead of three.
+__host__ __device__ __forceinline__ int wop_fwd_index(int tap, int c, int o, int hl) {
+    return ((((tap * 2 + (c >> 3)) * 2 + hl) * 4 + (o >> 3)) * 8 + (o & 7)) * 8 + (c & 7);
+}
+__host__ __device__ __forceinline__ int wop_dgrad_index(int tap, int c, int o, int hl) {
+    return 25600 + (((((24 - tap) * 4 + (o >> 3)) * 2 + hl) * 2 + (c >> 3)) * 8 + (c & 7)) * 8 + (o & 7);
+}
+__device__ __forceinline__ void store_wop(__nv_bfloat16* wo, int o, int c, int tap, float w) {
+    float hi, lo;
+    split_bf16(w, hi, lo);
+    const __nv_bfloat16 bh = __float2bfloat16_rn(hi), bl = __float2bfloat16_rn(lo);
+    wo[wop_fwd_index(tap, c, o, 0)] = bh;   wo[wop_fwd_index(tap, c, o, 1)] = bl;
+    wo[wop_dgrad_index(tap, c, o, 0)] = bh; wo[wop_dgrad_index(tap, c, o, 1)] = bl;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -154,9 +199,10 @@ __device__ __forceinline__ void rebuild_a1_planes(uint8_t* smem, const float* a1
     *reinterpret_cast<uint4*>(smem + OFF_A1 + (2 + half) * PPLANE + slot * 16) = lo;
 }
 
-// one thread: conv2 forward, D[pixel slot, oc] += sum over taps A_tap[pixel slot, c] W_tap[oc, c]^T, 3 MMAs per tap
+// one thread: conv2 forward, D[pixel slot, (hi|lo, oc)] += sum over taps A_tap[pixel slot, c] [W_hi | W_lo]_tap[oc, c]^T,
+// once for the hi and once for the lo activation planes (all four partial products; the epilogue adds the halves)
 __device__ __forceinline__ void issue_conv2_fwd(uint32_t sbase, uint32_t tmem) {
-    constexpr uint32_t idesc = idesc_bf16(128, 32, 0, 0);
+    constexpr uint32_t idesc = idesc_bf16(128, 64, 0, 0);
 #pragma unroll 1
     for (int blk = 0; blk < 2; ++blk) {
 #pragma unroll 1
@@ -165,12 +211,10 @@ __device__ __forceinline__ void issue_conv2_fwd(uint32_t sbase, uint32_t tmem) {
             // rows = 128 consecutive pixel slots; output slot p reads input slot p + ky*16 + kx - 2 (the two slots in front
             // of the first plane are zeros); 8-row groups 128 B apart, the second k-chunk (channels 8..15) one plane on
             const uint32_t a_hi = sbase + OFF_A1 + (uint32_t)((128 * blk + ky * 16 + kx - 2) * 16);
-            const uint32_t b_hi = sbase + OFF_WF + (uint32_t)tap * 1024;
             const uint64_t ah = desc_noswz(a_hi, PPLANE, 128), al = desc_noswz(a_hi + 2 * PPLANE, PPLANE, 128);
-            const uint64_t bh = desc_noswz(b_hi, 512, 128), bl = desc_noswz(b_hi + WOP, 512, 128);
-            umma_bf16(tmem + TM_FWD + 32 * blk, al, bh, idesc, tap > 0 ? 1u : 0u);
-            umma_bf16(tmem + TM_FWD + 32 * blk, ah, bl, idesc, 1u);
-            umma_bf16(tmem + TM_FWD + 32 * blk, ah, bh, idesc, 1u);
+            const uint64_t b = desc_noswz(sbase + OFF_WF + (uint32_t)tap * 2048, 1024, 128);
+            umma_bf16(tmem + TM_FWD + 64 * blk, al, b, idesc, tap > 0 ? 1u : 0u);
+            umma_bf16(tmem + TM_FWD + 64 * blk, ah, b, idesc, 1u);
         }
     }
 }
@@ -182,12 +226,13 @@ __device__ __forceinline__ void conv2_fwd_epilogue(uint32_t tmem, const float* _
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, q = warp & 3, cg = warp >> 2;
 #pragma unroll
     for (int blk = 0; blk < 2; ++blk) {
-        uint32_t r[8];
-        tmem_ld<8>(tmem + ((uint32_t)(q * 32) << 16) + TM_FWD + 32 * blk + 8 * cg, r);
+        uint32_t r[8], r2[8];
+        tmem_ld<8>(tmem + ((uint32_t)(q * 32) << 16) + TM_FWD + 64 * blk + 8 * cg, r);
+        tmem_ld<8>(tmem + ((uint32_t)(q * 32) << 16) + TM_FWD + 64 * blk + 32 + 8 * cg, r2);
         const int x = lane & 15, py = 4 * blk + q, px = x >> 1;
 #pragma unroll
         for (int o = 0; o < 8; ++o) {
-            const float v = __uint_as_float(r[o]);
+            const float v = __uint_as_float(r[o]) + __uint_as_float(r2[o]);
             const float p = __shfl_xor_sync(0xffffffffu, v, 1);
             const bool right = p > v;                       // meaningful on even-x lanes
             const float hbest = right ? p : v;
@@ -231,9 +276,10 @@ __device__ __forceinline__ void build_g2_planes(uint8_t* smem, const float* __re
     }
 }
 
-// one thread: data gradient D[pixel slot, c] += sum_tap G_tap[pixel slot, oc] Wflip_tap[c, oc]^T (K = 32 oc = 2 MMAs)
+// one thread: data gradient D[pixel slot, (hi|lo, c)] += sum_tap G_tap[pixel slot, oc] [Wflip_hi | Wflip_lo]_tap[c, oc]^T
+// (K = 32 oc = 2 MMAs), for the hi and the lo planes of g2
 __device__ __forceinline__ void issue_conv2_dgrad(uint32_t sbase, uint32_t tmem) {
-    constexpr uint32_t idesc = idesc_bf16(128, 16, 0, 0);
+    constexpr uint32_t idesc = idesc_bf16(128, 32, 0, 0);
 #pragma unroll 1
     for (int blk = 0; blk < 2; ++blk) {
 #pragma unroll 1
@@ -242,38 +288,36 @@ __device__ __forceinline__ void issue_conv2_dgrad(uint32_t sbase, uint32_t tmem)
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
                 const uint32_t a_hi = sbase + OFF_G2 + (uint32_t)(2 * j) * PPLANE + (uint32_t)((128 * blk + ky * 16 + kx - 2) * 16);
-                const uint32_t b_hi = sbase + OFF_WB + (uint32_t)tap * 1024 + (uint32_t)(2 * j) * 256;
                 const uint64_t ah = desc_noswz(a_hi, PPLANE, 128), al = desc_noswz(a_hi + 4 * PPLANE, PPLANE, 128);
-                const uint64_t bh = desc_noswz(b_hi, 256, 128), bl = desc_noswz(b_hi + WOP, 256, 128);
-                umma_bf16(tmem + TM_DG + 16 * blk, al, bh, idesc, (tap | j) ? 1u : 0u);
-                umma_bf16(tmem + TM_DG + 16 * blk, ah, bl, idesc, 1u);
-                umma_bf16(tmem + TM_DG + 16 * blk, ah, bh, idesc, 1u);
+                const uint64_t b = desc_noswz(sbase + OFF_WB + (uint32_t)tap * 2048 + (uint32_t)(2 * j) * 512, 512, 128);
+                umma_bf16(tmem + TM_DG + 32 * blk, al, b, idesc, (tap | j) ? 1u : 0u);
+                umma_bf16(tmem + TM_DG + 32 * blk, ah, b, idesc, 1u);
             }
         }
     }
 }
 
-// one thread: weight gradient.  Accumulator (ky, h): D[(kx, c8), oc] += sum over pixel slots a1[slot + shift(ky) + kx, 8h + c8]
-// g2[slot, oc]; both operands MN-major from the planes, A's M chunks one pixel apart (= the kx shifts), B's N chunks one
-// plane apart (= the four 8-oc groups); K = pixel slots 32 .. 255 (image rows), 16 per MMA.
+// one thread: weight gradient.  Accumulator (ky, h): D[(hi|lo, oc), (kx, c8)] += sum over pixel slots
+// g2[slot, oc] a1[slot + shift(ky) + kx, 8h + c8].  Both operands are read MN-major straight from the planes: A = g2 with
+// M = 64 - the eight contiguous planes [hi oc groups | lo oc groups] are the eight M chunks - and B = an activation half
+// plane whose N chunks are one pixel apart (= the five kx shifts, N = 40).  Issued for the hi and the lo activation plane,
+// so all four partial products land in the accumulator; the epilogue adds rows oc and 32 + oc.  K = pixel slots 32 .. 255.
 __device__ __forceinline__ void issue_conv2_wgrad(uint32_t sbase, uint32_t tmem, bool accumulate) {
-    constexpr uint32_t idesc = idesc_bf16(128, 32, 1, 1);
-    const uint64_t a_hi_bits = desc_noswz(0, 128, 16) >> 32, b_hi_bits = desc_noswz(0, 128, PPLANE) >> 32;
+    constexpr uint32_t idesc = idesc_bf16(64, WG_N, 1, 1);
+    const uint64_t a_hi_bits = desc_noswz(0, 128, PPLANE) >> 32, b_hi_bits = desc_noswz(0, 128, 16) >> 32;
     const uint32_t lbo_lo = (uint32_t)((128u >> 4) << 16);
 #pragma unroll 1
     for (int kyh = 0; kyh < 10; ++kyh) {
         const int ky = kyh >> 1, h = kyh & 1;
-        const uint32_t acc = tmem + TM_WG + 32 * kyh;
-        uint32_t a_h = (((sbase + OFF_A1 + (uint32_t)h * PPLANE + (uint32_t)((16 * ky - 2) * 16)) >> 4) & 0x3FFF) | lbo_lo;
-        uint32_t a_l = (((sbase + OFF_A1 + (uint32_t)(2 + h) * PPLANE + (uint32_t)((16 * ky - 2) * 16)) >> 4) & 0x3FFF) | lbo_lo;
-        uint32_t b_h = (((sbase + OFF_G2 + 32 * 16) >> 4) & 0x3FFF) | lbo_lo;
-        uint32_t b_l = (((sbase + OFF_G2 + 4 * PPLANE + 32 * 16) >> 4) & 0x3FFF) | lbo_lo;
+        const uint32_t acc = tmem + TM_WG + WG_N * kyh;
+        uint32_t a = (((sbase + OFF_G2 + 32 * 16) >> 4) & 0x3FFF) | lbo_lo;
+        uint32_t b_h = (((sbase + OFF_A1 + (uint32_t)h * PPLANE + (uint32_t)((16 * ky - 2) * 16)) >> 4) & 0x3FFF) | lbo_lo;
+        uint32_t b_l = (((sbase + OFF_A1 + (uint32_t)(2 + h) * PPLANE + (uint32_t)((16 * ky - 2) * 16)) >> 4) & 0x3FFF) | lbo_lo;
 #pragma unroll 2
         for (int kk = 0; kk < 14; ++kk) {
-            umma_bf16(acc, (a_hi_bits << 32) | a_l, (b_hi_bits << 32) | b_h, idesc, (accumulate || kk) ? 1u : 0u);
-            umma_bf16(acc, (a_hi_bits << 32) | a_h, (b_hi_bits << 32) | b_l, idesc, 1u);
-            umma_bf16(acc, (a_hi_bits << 32) | a_h, (b_hi_bits << 32) | b_h, idesc, 1u);
-            a_h += 16; a_l += 16; b_h += 16; b_l += 16;    // 16 pixel slots = 256 B
+            umma_bf16(acc, (a_hi_bits << 32) | a, (b_hi_bits << 32) | b_l, idesc, (accumulate || kk) ? 1u : 0u);
+            umma_bf16(acc, (a_hi_bits << 32) | a, (b_hi_bits << 32) | b_h, idesc, 1u);
+            a += 16; b_h += 16; b_l += 16;    // 16 pixel slots = 256 B
         }
     }
 }
@@ -297,7 +341,7 @@ static_assert(sizeof(PcSm) <= 2 * WOP, "PC scratch");
 // Head for all rows of the minibatch (every CTA of the group computes it: the work is tiny and it saves a barrier):
 // h = dropout(relu(sum of split-K partials + b1)), logits, softmax-CE, d logits, dh.  The owner CTA also accumulates
 // the epoch statistics and leaves the fc2 / fc1-bias gradients for PE.
-__device__ __forceinline__ void head_phase(const Step& s, int sel, int nb, int lo, PcSm& sm, bool owner) {
+__device__ __forceinline__ void head_phase(const Step& s, int sel, int nb, int lo, PcSm& sm, bool owner, int cta, int G) {
     HeadSm& hs = sm.hs;
     const int tid = threadIdx.x, NC = s.n_classes;
     const float* __restrict__ prm = s.params + (size_t)sel * s.nd;
@@ -334,7 +378,7 @@ __device__ __forceinline__ void head_phase(const Step& s, int sel, int nb, int l
             hs.h[b][f] = v;
         }
     }
-    __syncthreads();
+    WSYNC();
     for (int i = tid; i < BS * NC; i += PNT) {
         const int b = i / NC, c = i % NC;
         float v = __ldcg(prm + f2b + c);
@@ -342,7 +386,7 @@ __device__ __forceinline__ void head_phase(const Step& s, int sel, int nb, int l
         for (int f = 0; f < 64; ++f) v += hs.h[b][f] * hs.w2[c][f];
         hs.z[b][c] = v;
     }
-    __syncthreads();
+    WSYNC();
     if (tid < BS) {
         const int b = tid;
         if (b < nb) {
@@ -361,7 +405,7 @@ __device__ __forceinline__ void head_phase(const Step& s, int sel, int nb, int l
             for (int c = 0; c < NC; ++c) hs.dz[b][c] = 0.f;
         }
     }
-    __syncthreads();
+    WSYNC();
     for (int i = tid; i < BS * 64; i += PNT) {
         const int b = i >> 6, f = i & 63;
         float v = 0.f;
@@ -371,37 +415,28 @@ __device__ __forceinline__ void head_phase(const Step& s, int sel, int nb, int l
         }
         sm.dh[b][f] = v;
     }
-    if (owner) {
-        if (tid == 0) { s.stats[sel * 2] += hs.red[0]; s.stats[sel * 2 + 1] += hs.red[1]; }
+    if (owner && tid == 0) { s.stats[sel * 2] += hs.red[0]; s.stats[sel * 2 + 1] += hs.red[1]; }
+    WSYNC();
+    {
+        // gradients of fc2 weights, fc2 bias, fc1 bias (applied in PE): every CTA has the whole head, so the
+        // NC*64 + NC + 64 sums over the minibatch are dealt round-robin to the warps of all G CTAs; lane = row
         float* hg = s.head_grad + (size_t)sel * HEAD_GRAD_STRIDE;
-        for (int i = tid; i < NC * 64 + NC + 64; i += PNT) {
-            float g = 0.f;
-            if (i < NC * 64) {
-                const int c = i / 64, f = i % 64;
-                for (int b = 0; b < nb; ++b) g += hs.dz[b][c] * hs.h[b][f];
-            } else if (i < NC * 64 + NC) {
-                const int c = i - NC * 64;
-                for (int b = 0; b < nb; ++b) g += hs.dz[b][c];
-            } else {
-                const int f = i - NC * 64 - NC;
-                for (int b = 0; b < nb; ++b) {
-                    if (hs.h[b][f] > 0.f) {
-                        float v = 0.f;
-                        for (int c = 0; c < NC; ++c) v += hs.dz[b][c] * hs.w2[c][f];
-                        g += v * keep_scale;
-                    }
-                }
-            }
-            hg[i] = g;
+        const int warp = tid >> 5, b = tid & 31;
+        for (int i = warp * G + cta; i < NC * 64 + NC + 64; i += (PNT / 32) * G) {
+            float t;
+            if (i < NC * 64) t = hs.dz[b][i / 64] * hs.h[b][i % 64];
+            else if (i < NC * 64 + NC) t = hs.dz[b][i - NC * 64];
+            else t = sm.dh[b][i - NC * 64 - NC];
+            t = warp_sum(b < nb ? t : 0.f);
+            if (b == 0) hg[i] = t;
         }
     }
-    __syncthreads();
 }
 
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(PNT, 1) tinycnn_round_kernel(const Round R) {
+__global__ void __launch_bounds__(PNT_ALL, 1) tinycnn_round_kernel(const Round R) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ __align__(8) uint64_t bar_f, bar_d, bar_w;
+    __shared__ __align__(8) uint64_t bar_f, bar_d, bar_w, rdy_f, rdy_b;
     __shared__ uint32_t tmem_slot;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int sel = blockIdx.y, cta = blockIdx.x, G = gridDim.x;
@@ -413,12 +448,13 @@ __global__ void __launch_bounds__(PNT, 1) tinycnn_round_kernel(const Round R) {
     unsigned* bar = R.bar + sel;
     unsigned bar_target = 0;
     uint32_t pf = 0, pd = 0, pw = 0;          // mbarrier phase parities
+    long long t_mark = clock64();
 
     // ---- one-time set-up: zero planes and image borders, TMEM, mbarriers
-    for (int i = tid * 16; i < OFF_WF; i += PNT * 16) *reinterpret_cast<uint4*>(smem + i) = make_uint4(0, 0, 0, 0);
-    for (int i = OFF_X32 + tid * 16; i < OFF_W1C; i += PNT * 16) *reinterpret_cast<uint4*>(smem + i) = make_uint4(0, 0, 0, 0);
+    for (int i = tid * 16; i < OFF_WF; i += PNT_ALL * 16) *reinterpret_cast<uint4*>(smem + i) = make_uint4(0, 0, 0, 0);
+    for (int i = OFF_X32 + tid * 16; i < OFF_W1C; i += PNT_ALL * 16) *reinterpret_cast<uint4*>(smem + i) = make_uint4(0, 0, 0, 0);
     if (warp == 1 && lane == 0) {
-        mbar_init1(&bar_f); mbar_init1(&bar_d); mbar_init1(&bar_w);
+        mbar_init1(&bar_f); mbar_init1(&bar_d); mbar_init1(&bar_w); mbar_init1(&rdy_f); mbar_init1(&rdy_b);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
@@ -435,6 +471,39 @@ __global__ void __launch_bounds__(PNT, 1) tinycnn_round_kernel(const Round R) {
     float* b2g = b2s + 32;                                       // conv2 bias gradient of this CTA's images
     const int NC = s.n_classes;
 
+    if (warp == PNT / 32) {
+        // ---- MMA issuer: lane 0 walks the same steps as the workers and issues each image's tensor-core work as soon as
+        // the workers have published its operands; completion goes back through bar_f / bar_d / bar_w
+        if (lane == 0) {
+            uint32_t prf = 0, prb = 0;
+#pragma unroll 1
+            for (int epoch = 0; epoch < R.epochs; ++epoch) {
+                s.epoch = epoch;
+#pragma unroll 1
+                for (int bi = 0; bi < R.n_batches; ++bi) {
+                    s.batch_index = bi;
+                    int lo;
+                    const int nb = batch_rows(s, sel, &lo);
+                    if (nb <= 0) continue;
+                    const int my_imgs = cta < nb ? (nb - cta + G - 1) / G : 0;
+#pragma unroll 1
+                    for (int i = 0; i < my_imgs; ++i) {
+                        mbar_wait_all(&rdy_f, prf);
+                        issue_conv2_fwd(sbase, tmem);
+                        umma_commit1(&bar_f);
+                    }
+#pragma unroll 1
+                    for (int i = 0; i < my_imgs; ++i) {
+                        mbar_wait_all(&rdy_b, prb);
+                        issue_conv2_dgrad(sbase, tmem);
+                        umma_commit1(&bar_d);
+                        issue_conv2_wgrad(sbase, tmem, i > 0);
+                        umma_commit1(&bar_w);
+                    }
+                }
+            }
+        }
+    } else {
 #pragma unroll 1
     for (int epoch = 0; epoch < R.epochs; ++epoch) {
         s.epoch = epoch;
@@ -456,6 +525,7 @@ __global__ void __launch_bounds__(PNT, 1) tinycnn_round_kernel(const Round R) {
                     cp_async16(smem + OFF_WF + 16 * i, reinterpret_cast<const uint8_t*>(wop) + 16 * i);
             }
             if (tid < 32) b2g[tid] = 0.f;
+            QFX_MARK(15);
 #pragma unroll 1
             for (int img = cta; img < nb; img += G) {
                 const size_t row = (size_t)sel * BS + img;
@@ -465,19 +535,20 @@ __global__ void __launch_bounds__(PNT, 1) tinycnn_round_kernel(const Round R) {
                     cp_async8(xs32 + (y + 2) * 32 + 2 + 2 * x2, src + y * 28 + 2 * x2);
                 }
                 cp_async_wait_all();
-                __syncthreads();
+                WSYNC();
+                QFX_MARK(0);
                 conv1_to_planes(smem, s.a1 + row * 3136, s.i1 + row * 3136);
-                publish_operands();
-                if (warp == 1 && lane == 0) {
-                    issue_conv2_fwd(sbase, tmem);
-                    umma_commit1(&bar_f);
-                }
+                hand_to_issuer(&rdy_f);
+                QFX_MARK(1);
                 mbar_wait_all(&bar_f, pf);
+                QFX_MARK(2);
                 conv2_fwd_epilogue(tmem, b2s, s.a2 + row * 1568, s.i2 + row * 1568);
-                __syncthreads();
+                WSYNC();
+                QFX_MARK(3);
             }
             cp_async_wait_all();
             group_barrier(bar, bar_target, G, R.err);
+            QFX_MARK(4);
 
             // ================= PB: fc1 forward, split-K partial products per 112-column slice =================
 #pragma unroll 1
@@ -486,7 +557,7 @@ __global__ void __launch_bounds__(PNT, 1) tinycnn_round_kernel(const Round R) {
                 float* wsm = xs + BS * FCX;                                 // [64][FCX]
                 const float* x = s.a2 + (size_t)sel * BS * 1568 + sl * FC1_KS;
                 const float* w = prm + F1W + sl * FC1_KS;
-                __syncthreads();
+                WSYNC();
                 for (int i = tid; i < (BS + 64) * (FC1_KS / 4); i += PNT) {
                     const int r = i / (FC1_KS / 4), c = i - r * (FC1_KS / 4);
                     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -494,7 +565,7 @@ __global__ void __launch_bounds__(PNT, 1) tinycnn_round_kernel(const Round R) {
                     else v = __ldcg(reinterpret_cast<const float4*>(w + (size_t)(r - BS) * 1568) + c);
                     *reinterpret_cast<float4*>(xs + r * FCX + 4 * c) = v;
                 }
-                __syncthreads();
+                WSYNC();
                 if (tid < 128) {
                     const int bt = (tid >> 4) * 4, f0 = tid & 15;
                     float acc[4][4] = {};
@@ -519,16 +590,19 @@ __global__ void __launch_bounds__(PNT, 1) tinycnn_round_kernel(const Round R) {
                         for (int j = 0; j < 4; ++j) out[(bt + i) * 64 + f0 + 16 * j] = acc[i][j];
                 }
             }
+            QFX_MARK(5);
             group_barrier(bar, bar_target, G, R.err);
+            QFX_MARK(6);
 
             // ================= PC: head, then fc1 backward per 32-column chunk =================
             {
                 PcSm& sm = *reinterpret_cast<PcSm*>(smem + OFF_WF);
-                head_phase(s, sel, nb, lo, sm, cta == 0);
+                head_phase(s, sel, nb, lo, sm, cta == 0, cta, G);
+                QFX_MARK(7);
 #pragma unroll 1
                 for (int chunk = cta; chunk < 49; chunk += G) {
                     const int k0 = chunk * 32;
-                    __syncthreads();
+                    WSYNC();
                     for (int i = tid; i < (BS + 64) * 8; i += PNT) {
                         const int r = i >> 3, c = i & 7;
                         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -549,7 +623,7 @@ __global__ void __launch_bounds__(PNT, 1) tinycnn_round_kernel(const Round R) {
 #pragma unroll
                         for (int j = 0; j < 8; ++j) mprev[j] = __ldcg(mom + F1W + (size_t)(fg + j) * 1568 + k0 + k);
                     }
-                    __syncthreads();
+                    WSYNC();
                     if (tid < 256) {
                         // dx[b][k] = sum_f dh[b][f] W1[f][k], masked by the ReLU of a2: rows bq, bq+8, bq+16, bq+24
                         const int bq = t >> 5;
@@ -586,19 +660,21 @@ __global__ void __launch_bounds__(PNT, 1) tinycnn_round_kernel(const Round R) {
                     }
                 }
             }
+            QFX_MARK(8);
             group_barrier(bar, bar_target, G, R.err);
+            QFX_MARK(9);
 
             // ================= PD: backward through the convolutions, per image =================
             {
                 float* gsm = reinterpret_cast<float*>(smem + OFF_WF);                        // [16][196]
                 unsigned short* osm = reinterpret_cast<unsigned short*>(smem + OFF_WF + 12544);   // [16][196]
                 unsigned char* i1s = smem + OFF_WF + 12544 + 6272;                            // [16][196]
-                float c1acc = 0.f;                    // conv1 weight (tid < 400) / bias (400..415) gradient of my images
+                float c1acc = 0.f;                    // warp o, lane t: conv1 weight (o, tap t < 25) / bias (t == 25) gradient of my images
                 int n_done = 0;
 #pragma unroll 1
                 for (int img = cta; img < nb; img += G, ++n_done) {
                     const size_t row = (size_t)sel * BS + img;
-                    __syncthreads();
+                    WSYNC();
                     const float* src = s.X + (size_t)sample_index(s, sel, lo, img) * 784;
                     for (int i = tid; i < 784; i += PNT) {
                         const int y = i / 28, x = i - y * 28;
@@ -616,18 +692,15 @@ __global__ void __launch_bounds__(PNT, 1) tinycnn_round_kernel(const Round R) {
                         }
                     }
                     cp_async_wait_all();
-                    publish_operands();
-                    if (warp == 1 && lane == 0) {
-                        issue_conv2_dgrad(sbase, tmem);
-                        umma_commit1(&bar_d);
-                        issue_conv2_wgrad(sbase, tmem, n_done > 0);
-                        umma_commit1(&bar_w);
-                    }
+                    hand_to_issuer(&rdy_b);
+                    QFX_MARK(10);
                     mbar_wait_all(&bar_d, pd);
+                    QFX_MARK(11);
                     {   // data-gradient epilogue: through conv1's ReLU into the sparse form the conv1 weight gradient reads
                         const int q = warp & 3, combo = warp >> 2, blk = combo >> 1, cg = combo & 1;
-                        uint32_t r[8];
-                        tmem_ld<8>(tmem + ((uint32_t)(q * 32) << 16) + TM_DG + 16 * blk + 8 * cg, r);
+                        uint32_t r[8], r2[8];
+                        tmem_ld<8>(tmem + ((uint32_t)(q * 32) << 16) + TM_DG + 32 * blk + 8 * cg, r);
+                        tmem_ld<8>(tmem + ((uint32_t)(q * 32) << 16) + TM_DG + 32 * blk + 16 + 8 * cg, r2);
                         const int slot = 128 * blk + 32 * q + lane, y = slot >> 4, x = slot & 15;
                         if (y < 14 && x < 14) {
                             const int p = y * 14 + x;
@@ -635,55 +708,82 @@ __global__ void __launch_bounds__(PNT, 1) tinycnn_round_kernel(const Round R) {
                             for (int c = 0; c < 8; ++c) {
                                 const int ch = 8 * cg + c;
                                 const int byte = i1s[ch * 196 + p];
-                                gsm[ch * 196 + p] = (byte & 4) ? __uint_as_float(r[c]) : 0.f;
+                                gsm[ch * 196 + p] = (byte & 4) ? __uint_as_float(r[c]) + __uint_as_float(r2[c]) : 0.f;
                                 osm[ch * 196 + p] = (unsigned short)((2 * y + ((byte >> 1) & 1)) * XS1P + 2 * x + (byte & 1));
                             }
                         }
                         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                     }
-                    __syncthreads();
-                    if (tid < 400) {
-                        const int o = tid / 25, tap = tid - o * 25, ky = tap / 5, kx = tap - ky * 5;
-                        const float* xt = xs37 + ky * XS1P + kx;
-                        float acc = 0.f;
-#pragma unroll 4
-                        for (int p = 0; p < 196; ++p) acc += gsm[o * 196 + p] * xt[osm[o * 196 + p]];
-                        c1acc += acc;
-                    } else if (tid < 416) {
-                        const int o = tid - 400;
-                        float acc = 0.f;
-                        for (int p = 0; p < 196; ++p) acc += gsm[o * 196 + p];
-                        c1acc += acc;
+                    WSYNC();
+                    {   // conv1 weight gradient: warp = output channel, lanes = pooled positions; every non-zero of the
+                        // (sparse) gradient meets its 5x5 input window; the 25 + 1 sums are reduced over the warp and
+                        // lane `tap` keeps the running total of (channel, tap) across this CTA's images
+                        const int o = warp;
+                        float acc[26];
+#pragma unroll
+                        for (int t = 0; t < 26; ++t) acc[t] = 0.f;
+#pragma unroll 1
+                        for (int p = lane; p < 196; p += 32) {
+                            const float g = gsm[o * 196 + p];
+                            const float* xt = xs37 + osm[o * 196 + p];
+#pragma unroll
+                            for (int ky = 0; ky < 5; ++ky)
+#pragma unroll
+                                for (int kx = 0; kx < 5; ++kx) acc[ky * 5 + kx] += g * xt[ky * XS1P + kx];
+                            acc[25] += g;
+                        }
+#pragma unroll
+                        for (int t = 0; t < 26; ++t) {
+                            const float v = warp_sum(acc[t]);
+                            if (lane == t) c1acc += v;
+                        }
                     }
+                    QFX_MARK(12);
                     mbar_wait_all(&bar_w, pw);       // the planes may be rebuilt only after the weight-gradient MMAs read them
+                    QFX_MARK(13);
                 }
                 if (my_imgs > 0) {
                     // weight-gradient accumulators -> [oc][c][ky][kx] through shared memory -> this CTA's gradient row
-                    __syncthreads();
+                    WSYNC();
                     float* stage = reinterpret_cast<float*>(smem + OFF_WF);    // [32][401]
                     float* part = s.conv_part + ((size_t)sel * BS + cta) * NCONV;
-                    if ((warp & 3) < 2) {
-                        const int quarter = warp & 3, rowm = quarter * 32 + lane, kx = rowm >> 3, c8 = rowm & 7;
+                    {
+                        // M = 64 accumulators: row r sits in TMEM lane 32 * (r / 16) + r % 16, so lane quarter q holds
+                        // rows 16q .. 16q+15 in its first 16 lanes: quarters 0, 1 = hi part of oc 0..31, quarters 2, 3 = lo part
+                        const int q = warp & 3, oc = 16 * (q & 1) + (lane & 15);
+                        for (int pass = 0; pass < 2; ++pass) {        // hi rows store, lo rows add
+                            if ((q >> 1) == pass) {
 #pragma unroll 1
-                        for (int kyh = warp >> 2; kyh < 10; kyh += 4) {
-                            const int ky = kyh >> 1, h = kyh & 1;
-                            uint32_t r[32];
-                            tmem_ld<32>(tmem + ((uint32_t)(quarter * 32) << 16) + TM_WG + 32 * kyh, r);
-                            if (kx < 5) {
-                                const int c = 8 * h + c8;
+                                for (int kyh = warp >> 2; kyh < 10; kyh += 4) {
+                                    const int ky = kyh >> 1, h = kyh & 1;
+                                    uint32_t r[32], r8[8];
+                                    const uint32_t ta = tmem + ((uint32_t)(q * 32) << 16) + TM_WG + WG_N * kyh;
+                                    tmem_ld<32>(ta, r);
+                                    tmem_ld<8>(ta + 32, r8);
+                                    if (lane < 16) {
 #pragma unroll
-                                for (int oc = 0; oc < 32; ++oc) stage[oc * 401 + c * 25 + ky * 5 + kx] = __uint_as_float(r[oc]);
+                                        for (int col = 0; col < 40; ++col) {
+                                            const int kx = col >> 3, c = 8 * h + (col & 7);
+                                            const float v = __uint_as_float(col < 32 ? r[col] : r8[col - 32]);
+                                            float* d = stage + oc * 401 + c * 25 + ky * 5 + kx;
+                                            *d = pass ? *d + v : v;
+                                        }
+                                    }
+                                }
                             }
+                            WSYNC();
                         }
                         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                     }
-                    if (tid < 416) part[C1W + tid] = c1acc;
-                    __syncthreads();
+                    if (warp < 16 && lane < 26) part[lane < 25 ? C1W + warp * 25 + lane : C1B + warp] = c1acc;
+                    WSYNC();
                     if (tid < 32) part[C2B + tid] = b2g[tid];
                     for (int e = tid; e < 12800; e += PNT) part[C2W + e] = stage[(e / 400) * 401 + (e % 400)];
                 }
             }
+            QFX_MARK(14);
             group_barrier(bar, bar_target, G, R.err);
+            QFX_MARK(16);
 
             // ================= PE: reduce the gradient rows, SGD-momentum, refresh the operand copies =================
             {
@@ -699,28 +799,29 @@ __global__ void __launch_bounds__(PNT, 1) tinycnn_round_kernel(const Round R) {
                         continue;
                     }
                     const float* part = s.conv_part + (size_t)sel * BS * NCONV + p0;
+                    float pv[BS];
+#pragma unroll
+                    for (int r = 0; r < BS; ++r) pv[r] = r < rows ? __ldcg(part + (size_t)r * NCONV) : 0.f;   // all loads in flight
                     float g = 0.f;
-#pragma unroll 4
-                    for (int r = 0; r < rows; ++r) g += __ldcg(part + (size_t)r * NCONV);
+#pragma unroll
+                    for (int r = 0; r < BS; ++r) g += pv[r];
                     const float m = s.momentum * __ldcg(mom + p0) + g;
                     mom[p0] = m;
                     const float w = __ldcg(prm + p0) - s.lr * m;
                     prm[p0] = w;
                     if (p0 >= C2W && p0 < C2B) {
                         const int i = p0 - C2W, o = i / 400, rem = i - o * 400, c = rem / 25, tap = rem - c * 25;
-                        float hi, lw;
-                        split_bf16(w, hi, lw);
-                        __nv_bfloat16* wo = R.wop + (size_t)sel * 4 * 12800;
-                        const int fi = (((tap * 2 + (c >> 3)) * 4 + (o >> 3)) * 8 + (o & 7)) * 8 + (c & 7);
-                        const int bi2 = ((((24 - tap) * 4 + (o >> 3)) * 2 + (c >> 3)) * 8 + (c & 7)) * 8 + (o & 7);
-                        wo[fi] = __float2bfloat16_rn(hi);            wo[12800 + fi] = __float2bfloat16_rn(lw);
-                        wo[2 * 12800 + bi2] = __float2bfloat16_rn(hi); wo[3 * 12800 + bi2] = __float2bfloat16_rn(lw);
+                        store_wop(R.wop + (size_t)sel * 4 * 12800, o, c, tap, w);
                     }
                 }
             }
+            QFX_MARK(17);
             group_barrier(bar, bar_target, G, R.err);
+            QFX_MARK(18);
         }
     }
+    }   // workers
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
 }
@@ -730,13 +831,7 @@ __global__ void __launch_bounds__(256) conv2_weight_prep_split(const float* __re
     const int sel = blockIdx.y, i = blockIdx.x * 256 + threadIdx.x;
     if (i >= 12800) return;
     const int o = i / 400, rem = i - o * 400, c = rem / 25, tap = rem - c * 25;
-    float hi, lo;
-    split_bf16(params[(size_t)sel * nd + C2W + i], hi, lo);
-    __nv_bfloat16* wo = wop + (size_t)sel * 4 * 12800;
-    const int fi = (((tap * 2 + (c >> 3)) * 4 + (o >> 3)) * 8 + (o & 7)) * 8 + (c & 7);
-    const int bi = ((((24 - tap) * 4 + (o >> 3)) * 2 + (c >> 3)) * 8 + (c & 7)) * 8 + (o & 7);
-    wo[fi] = __float2bfloat16_rn(hi);             wo[12800 + fi] = __float2bfloat16_rn(lo);
-    wo[2 * 12800 + bi] = __float2bfloat16_rn(hi); wo[3 * 12800 + bi] = __float2bfloat16_rn(lo);
+    store_wop(wop + (size_t)sel * 4 * 12800, o, c, tap, params[(size_t)sel * nd + C2W + i]);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -758,7 +853,7 @@ __global__ void __launch_bounds__(PNT, 1) tinycnn_eval_conv_kernel(const float* 
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 64;" ::"r"(smem_addr(&tmem_slot)) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 128;" ::"r"(smem_addr(&tmem_slot)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     for (int i = tid; i < 104; i += PNT) cp_async16(smem + OFF_W1C + 16 * i, prm + C1W + 4 * i);
@@ -790,9 +885,10 @@ __global__ void __launch_bounds__(PNT, 1) tinycnn_eval_conv_kernel(const float* 
         __syncthreads();
     }
     __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 64;" ::"r"(tmem) : "memory");
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 128;" ::"r"(tmem) : "memory");
 }
 
+static long long* g_round_prof[QFX_MAX_DEVICES] = {};
 static PerDeviceFlag g_round_attr;
 static int round_attrs() {
     if (g_round_attr.here()) return 0;
@@ -888,10 +984,21 @@ extern "C" int qfx_tinycnn_train_round(const float* X, const int* labels, const 
         R.wop = w.wop + (size_t)k0 * 4 * 12800;
         R.bar = w.bar + k0;
         R.err = w.err;
+        R.prof = g_round_prof[current_device()] ? g_round_prof[current_device()] + (size_t)k0 * 32 * 20 : nullptr;
         void* args[] = {(void*)&R};
-        QFX_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)tinycnn_round_kernel, dim3((unsigned)G, (unsigned)kc), dim3(PNT),
+        QFX_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)tinycnn_round_kernel, dim3((unsigned)G, (unsigned)kc), dim3(PNT_ALL),
                                                  args, (size_t)PSMEM, stream));
     }
+    return 0;
+}
+
+// Phase timing for tuning: cycles per phase and CTA are added into prof [K, G, 20] (int64, caller-zeroed; G = CTAs per
+// client of the launch) by every following qfx_tinycnn_train_round on the current device; null switches it off.
+// Slots: 15 weight load issue, 0 image load, 1 conv1, 2 conv2 forward MMAs, 3 forward epilogue, 4 barrier 1, 5 fc1
+// forward, 6 barrier 2, 7 head, 8 fc1 backward, 9 barrier 3, 10 plane build, 11 data-gradient MMAs, 12 its epilogue +
+// conv1 weight gradient, 13 weight-gradient MMA wait, 14 weight-gradient epilogue, 16 barrier 4, 17 update, 18 barrier 5.
+extern "C" int qfx_tinycnn_round_profile(long long* prof) {
+    g_round_prof[current_device()] = prof;
     return 0;
 }
 
