@@ -26,8 +26,13 @@ def _templates(num_classes: int, gen: torch.Generator) -> torch.Tensor:
 
 
 def synthetic_mnist(n: int, num_classes: int = 3, seed: int = 0, noise: float = 0.25,
-                    class_counts=None):
-    """Return (X float32 [n,1,28,28] in [0,1], y int64 [n])."""
+                    class_counts=None, contrast: float = 1.0, label_noise: float = 0.0):
+    """Return (X float32 [n,1,28,28] in [0,1], y int64 [n]).
+
+    ``contrast`` < 1 pulls the class templates towards their common mean and ``label_noise`` re-draws that fraction
+    of the labels uniformly AFTER the images were made: together with a larger ``noise`` they give a task that a
+    TinyCNN does not solve perfectly (accuracy ceiling about 1 - label_noise * (C-1)/C), which is what the
+    convergence-parity tests need - the default task is separable within a round."""
     gen = torch.Generator().manual_seed(seed)
     if class_counts is not None:
         y = torch.cat([torch.full((int(c),), k, dtype=torch.long) for k, c in enumerate(class_counts)])
@@ -36,7 +41,13 @@ def synthetic_mnist(n: int, num_classes: int = 3, seed: int = 0, noise: float = 
     else:
         y = torch.randint(0, num_classes, (n,), generator=gen)
     tmpl = _templates(num_classes, torch.Generator().manual_seed(1234))
+    if contrast != 1.0:
+        mean = tmpl.mean(0, keepdim=True)
+        tmpl = mean + contrast * (tmpl - mean)
     X = tmpl[y] + noise * torch.randn(n, 1, 28, 28, generator=gen)
+    if label_noise > 0.0:
+        flip = torch.rand(n, generator=gen) < label_noise
+        y = torch.where(flip, torch.randint(0, num_classes, (n,), generator=gen), y)
     return X.clamp_(0.0, 1.0).contiguous(), y
 
 
