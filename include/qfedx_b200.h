@@ -84,6 +84,24 @@ int qfx_vqc_local_train(int n_qubits, int n_layers, int basis, int entangler, in
 int qfx_vqc_eval(int n_qubits, int n_layers, int basis, int entangler, int n_classes, const float* angles,
                  const int* labels, const float* params, int n_samples, float* out2, cudaStream_t stream);
 
+/* Noisy variants (noise models of /root/reference/ROADMAP.md:64-73 in the K3 epilogue): the exact <Z> of every logit
+ * qubit goes through E' = noise_alpha * E + noise_beta (depolarizing on the measured qubit, amplitude damping, readout
+ * confusion - all affine on <Z>) and, when shots > 0, is replaced by the mean of `shots` sampled +-1 outcomes (counter RNG
+ * keyed by noise_key, epoch, sample, qubit); gradients flow through the affine part.  alpha 1 / beta 0 / shots 0 = exact. */
+int qfx_vqc_local_train_noisy(int n_qubits, int n_layers, int basis, int entangler, int n_classes,
+                              const float* angles, const int* labels, const int* offsets, const int* perm,
+                              int n_total, const float* params_in, const int* client_ids, int n_selected,
+                              float* params_out, float* stats_out, int epochs, int batch_size, int optimizer,
+                              float lr, float beta1, float beta2, float eps, int grad_mode, int cluster_size,
+                              int lane_mode, unsigned long long shuffle_key, float noise_alpha, float noise_beta,
+                              int shots, unsigned long long noise_key, cudaStream_t stream);
+int qfx_vqc_eval_noisy(int n_qubits, int n_layers, int basis, int entangler, int n_classes, const float* angles,
+                       const int* labels, const float* params, int n_samples, float* out2, float noise_alpha,
+                       float noise_beta, int shots, unsigned long long noise_key, cudaStream_t stream);
+/* the same readout noise as a stand-alone pass over exact expectation values [batch, n_qubits] (in place allowed) */
+int qfx_readout_noise(const float* expvals, float* out, int batch, int n_qubits, float noise_alpha,
+                      float noise_beta, int shots, unsigned long long noise_key, cudaStream_t stream);
+
 /* K7: fused FedAvg + per-client L2 clip + Gaussian noise + pairwise-mask secure aggregation +
  * server update, one cooperative launch.  client_params [K,D]; weights [K] sample counts;
  * participate [K] 0/1 (nullable); mode 0 = average weights (the reference's federated_averaging,
@@ -133,6 +151,22 @@ int qfx_symm_open(const unsigned char* handle64, void** ptr);
 int qfx_symm_close(void* ptr);
 int qfx_symm_free(void* ptr);
 int qfx_enable_peer(int dev, int peer);
+
+/* K7 with per-pair mask secrets: pair_keys [k_global, k_global] holds at [lo * k_global + hi] the 64-bit secret clients
+ * lo < hi agreed on at registration (qfedx_b200/fl/secagg.py: KeyAgreement - the "seed exchange API" planned in
+ * /root/reference/ROADMAP.md:52-55); each pair's mask stream is keyed by its secret instead of the job seed. */
+int qfx_fedavg_fused_pairkeys(const float* client_params, const float* global_in, float* global_out,
+                              const float* weights, const int* participate, int n_clients, int dim, int mode,
+                              int n_wrap, float clip, float sigma, float server_lr, unsigned long long seed,
+                              int round, const unsigned long long* pair_keys, float* norms_out,
+                              long long* masked_out, float* scratch, cudaStream_t stream);
+int qfx_fedavg_fused_multi_pairkeys(const float* client_params, const float* global_in, float* global_out,
+                                    const float* weights, const int* participate, const int* client_gids,
+                                    int k_local, int k_global, int dim, int mode, int n_wrap, float clip,
+                                    float sigma, float server_lr, unsigned long long seed, int round,
+                                    const unsigned long long* pair_keys, float* norms_out, float* scratch,
+                                    int rank, int world, long long* const* recv_slots,
+                                    unsigned int* const* flags, unsigned int epoch, cudaStream_t stream);
 
 /* K8: TinyCNN (the reference's model, /root/reference/src/CFed/Classical_FL.py:21-38) trained for
  * all selected clients at once.  One call = one SGD-momentum step of client_update

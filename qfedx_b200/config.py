@@ -19,6 +19,7 @@ from .noise import NoiseConfig
 
 @dataclass
 class DataConfig:
+    dataset: str = "mnist"           # mnist (idx files or the synthetic fallback) | iris (4 features -> 4 qubits)
     raw_folder: str = "./dataset/raw"
     processed_folder: str = "./dataset/processed"
     digits: Tuple[int, ...] = (0, 1, 2)
@@ -39,7 +40,7 @@ class ModelConfig:
     n_layers: int = 2
     entangler: str = "cnot"
     grad_method: str = "adjoint"     # adjoint | param_shift
-    engine: str = "auto"             # auto | registers | passes | sharded | torch
+    engine: str = "auto"             # auto | registers | passes | sharded | torch | graph (tinycnn: step-per-node engine)
 
 
 @dataclass
@@ -49,6 +50,7 @@ class TrainConfig:
     lr: float = 0.05
     optimizer: str = "adam"          # adam | sgd | spsa (torch engine)
     momentum: float = 0.9
+    centralized: bool = False        # pool every client's data into one: the centralized baseline (ROADMAP.md:4)
 
 
 @dataclass

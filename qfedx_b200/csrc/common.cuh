@@ -83,6 +83,36 @@ __device__ __forceinline__ float uniform_from_bits(uint64_t r) {
     return ((uint32_t)(r >> 40)) * (1.0f / 16777216.0f);                     // [0,1)
 }
 
+// ---- readout-level noise on <Z> (noise models of /root/reference/ROADMAP.md:64-73) ------------------
+// Depolarizing noise on the measured qubit, amplitude damping towards |0> and a readout confusion matrix all act on
+// an exact <Z> as one affine map E' = alpha E + beta; `shots` > 0 then replaces E' by the mean of that many +-1
+// measurement outcomes (binomial sample, keyed counter RNG; gradients flow through the affine part only).
+// Mirrors qfedx_b200/noise: readout_affine / apply_to_expvals.
+struct ReadoutNoise {
+    float alpha, beta;
+    int shots;
+    unsigned long long key;
+};
+__device__ __forceinline__ float sample_shots(float e, int shots, unsigned long long key) {
+    const float p0 = fminf(fmaxf(0.5f * (1.f + e), 0.f), 1.f);
+    float k;
+    if (shots <= 128) {          // exact: one Bernoulli draw per shot
+        int c = 0;
+        for (int i = 0; i < shots; ++i) c += uniform_from_bits(stream_at(key, (unsigned long long)i)) < p0 ? 1 : 0;
+        k = (float)c;
+    } else {                     // normal approximation of Binomial(shots, p0), rounded and clamped
+        const float z = normal_from_bits(stream_at(key, 0ull));
+        k = rintf((float)shots * p0 + sqrtf((float)shots * p0 * (1.f - p0)) * z);
+        k = fminf(fmaxf(k, 0.f), (float)shots);
+    }
+    return 2.f * k / (float)shots - 1.f;
+}
+__device__ __forceinline__ float readout_noise(float e, const ReadoutNoise& rn, unsigned long long sample, int qubit) {
+    float v = rn.alpha * e + rn.beta;
+    if (rn.shots > 0) v = sample_shots(v, rn.shots, key3(rn.key, sample, (unsigned long long)qubit));
+    return v;
+}
+
 // ---- keyed permutation of [0, n) without storage -----------------------------------------
 // Four-round (unbalanced) Feistel network on exactly ceil(log2 n) bits with cycle walking: a bijection of
 // [0, n) evaluated in O(1) per index (fewer than two walks on average), so a kernel can visit a client's

@@ -46,6 +46,8 @@ struct AggArgs {
     float* norms_out;            // [K_local] pre-clip norms, nullable
     float* scratch;              // [K_local] squared-norm accumulators (zeroed by the launcher)
     long long* masked_out;       // [K_local, D] masked fixed-point messages, nullable (inspection)
+    const unsigned long long* pair_keys;   // [K_global, K_global] pair secrets from the key agreement (entry lo*K+hi), or
+                                           // null: every pair's mask stream is derived from the job seed
     // multi-GPU
     int rank, world;
     long long* const* recv_slots;  // [world] device pointers: recv_slots[r] = base of rank r's slot array
@@ -149,7 +151,8 @@ fedavg_fused_kernel(const AggArgs a, const int mask_keys_in_smem) {
             const int k = i / a.k_global, j = i - k * a.k_global;
             const int gk = a.client_gids ? a.client_gids[k] : k;
             const int lo = min(gk, j), hi = max(gk, j);
-            mkey[i] = key3(a.seed ^ TAG_MASK, (uint64_t)a.round, (uint64_t)lo * (uint64_t)a.k_global + (uint64_t)hi);
+            const uint64_t pid = (uint64_t)lo * (uint64_t)a.k_global + (uint64_t)hi;
+            mkey[i] = key3((a.pair_keys ? a.pair_keys[pid] : a.seed) ^ TAG_MASK, (uint64_t)a.round, pid);
         }
     }
 
@@ -285,8 +288,8 @@ fedavg_fused_kernel(const AggArgs a, const int mask_keys_in_smem) {
                                 mk = mkey[(size_t)k * a.k_global + j];
                             } else {
                                 const int lo = min(gk, j), hi = max(gk, j);
-                                mk = key3(a.seed ^ TAG_MASK, (uint64_t)a.round,
-                                          (uint64_t)lo * (uint64_t)a.k_global + (uint64_t)hi);
+                                const uint64_t pid = (uint64_t)lo * (uint64_t)a.k_global + (uint64_t)hi;
+                                mk = key3((a.pair_keys ? a.pair_keys[pid] : a.seed) ^ TAG_MASK, (uint64_t)a.round, pid);
                             }
                             const uint64_t m = stream_at(mk, (uint64_t)d);
                             y += (gk < j) ? m : (0ull - m);
@@ -445,6 +448,42 @@ extern "C" int qfx_fedavg_fused_multi(const float* client_params, const float* g
     a.k_local = k_local; a.k_global = k_global; a.dim = dim; a.mode = mode; a.n_wrap = n_wrap;
     a.clip = clip; a.sigma = sigma; a.server_lr = server_lr; a.seed = seed; a.round = round; a.secagg = secagg;
     a.norms_out = norms_out; a.scratch = scratch; a.masked_out = nullptr;
+    a.rank = rank; a.world = world; a.recv_slots = recv_slots; a.flags = flags; a.epoch = epoch;
+    return launch_fedavg(a, stream);
+}
+
+// Same as qfx_fedavg_fused / qfx_fedavg_fused_multi with per-pair mask secrets: pair_keys [k_global, k_global] holds, at
+// [lo * k_global + hi], the 64-bit secret clients lo < hi agreed on at registration (fl/secagg.py: KeyAgreement, the
+// "seed exchange API" of /root/reference/ROADMAP.md:52-55); the mask stream of a pair is keyed by it instead of the job seed.
+extern "C" int qfx_fedavg_fused_pairkeys(const float* client_params, const float* global_in, float* global_out,
+                                         const float* weights, const int* participate, int n_clients, int dim, int mode,
+                                         int n_wrap, float clip, float sigma, float server_lr, unsigned long long seed,
+                                         int round, const unsigned long long* pair_keys, float* norms_out,
+                                         long long* masked_out, float* scratch, cudaStream_t stream) {
+    QFX_ARG_CHECK(pair_keys != nullptr, QFX_ERR_BAD_ARG, "pair_keys is required");
+    AggArgs a = {};
+    a.client_params = client_params; a.global_in = global_in; a.global_out = global_out;
+    a.weights = weights; a.participate = participate; a.client_gids = nullptr;
+    a.k_local = n_clients; a.k_global = n_clients; a.dim = dim; a.mode = mode; a.n_wrap = n_wrap;
+    a.clip = clip; a.sigma = sigma; a.server_lr = server_lr; a.seed = seed; a.round = round; a.secagg = 1;
+    a.norms_out = norms_out; a.scratch = scratch; a.masked_out = masked_out; a.pair_keys = pair_keys;
+    a.rank = 0; a.world = 1; a.recv_slots = nullptr; a.flags = nullptr; a.epoch = 0;
+    return launch_fedavg(a, stream);
+}
+extern "C" int qfx_fedavg_fused_multi_pairkeys(const float* client_params, const float* global_in, float* global_out,
+                                               const float* weights, const int* participate, const int* client_gids,
+                                               int k_local, int k_global, int dim, int mode, int n_wrap, float clip,
+                                               float sigma, float server_lr, unsigned long long seed, int round,
+                                               const unsigned long long* pair_keys, float* norms_out, float* scratch,
+                                               int rank, int world, long long* const* recv_slots,
+                                               unsigned int* const* flags, unsigned int epoch, cudaStream_t stream) {
+    QFX_ARG_CHECK(pair_keys != nullptr, QFX_ERR_BAD_ARG, "pair_keys is required");
+    AggArgs a = {};
+    a.client_params = client_params; a.global_in = global_in; a.global_out = global_out;
+    a.weights = weights; a.participate = participate; a.client_gids = client_gids;
+    a.k_local = k_local; a.k_global = k_global; a.dim = dim; a.mode = mode; a.n_wrap = n_wrap;
+    a.clip = clip; a.sigma = sigma; a.server_lr = server_lr; a.seed = seed; a.round = round; a.secagg = 1;
+    a.norms_out = norms_out; a.scratch = scratch; a.masked_out = nullptr; a.pair_keys = pair_keys;
     a.rank = rank; a.world = world; a.recv_slots = recv_slots; a.flags = flags; a.epoch = epoch;
     return launch_fedavg(a, stream);
 }

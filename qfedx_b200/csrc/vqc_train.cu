@@ -40,6 +40,7 @@ struct TrainArgs {
     int grad_mode;            // 0 adjoint, 1 parameter shift
     int ring_offset_floats;   // where the CNOT-ring scratch starts in dynamic shared memory (set by the launcher)
     unsigned long long shuffle_key;   // non-zero and perm == null: samples are visited in a keyed Feistel order
+    ReadoutNoise rn;          // readout-level noise applied to <Z> before the logits (alpha 1, beta 0, shots 0 = exact)
 };
 
 // Gradient sink: reduce over the whole warp (dead circuits contribute zero) and add into the warp's private
@@ -174,6 +175,13 @@ vqc_local_train_kernel(const TrainArgs a) {
                 ansatz_forward_merged(psi, tab, dt, a.n_layers, a.ent, lg, ring_buf);
                 float ez[NQ];
                 psi.expval_z_all(ez, lg);
+                if (a.rn.alpha != 1.f || a.rn.beta != 0.f || a.rn.shots > 0) {
+                    // noisy readout of the logit qubits; shot noise is keyed by (epoch, sample) so that every lane of the
+                    // circuit draws the same outcome
+#pragma unroll
+                    for (int q = 0; q < NQ; ++q)
+                        if (q < NC) ez[q] = readout_noise(ez[q], a.rn, ((unsigned long long)e << 32) | (unsigned)sidx, q);
+                }
 
                 float z[TR_MAX_C], dz[TR_MAX_C];
 #pragma unroll
@@ -181,9 +189,9 @@ vqc_local_train_kernel(const TrainArgs a) {
                     if (q < NC) z[q] = prm[P + q] * ez[q] + prm[P + NC + q];
                 bool correct;
                 const float loss = loss_and_grad(z, dz, NC, y, &correct);
-                float cot[NQ];
+                float cot[NQ];   // d loss / d <Z_q> of the EXACT expectation: through the affine part of the noise
 #pragma unroll
-                for (int q = 0; q < NQ; ++q) cot[q] = (q < NC) ? dz[q] * prm[P + q] : 0.f;
+                for (int q = 0; q < NQ; ++q) cot[q] = (q < NC) ? dz[q] * prm[P + q] * a.rn.alpha : 0.f;
                 {
                     // readout and statistics: one contribution per circuit (its lane 0)
                     WarpRowSink once{my_row, live && lg == 0, lane, ps == 0};
@@ -301,7 +309,8 @@ vqc_local_train_kernel(const TrainArgs a) {
 template <int NQ>
 __global__ void __launch_bounds__(TR_THREADS)
 vqc_eval_kernel(int n_layers, int basis, int ent, int n_classes, const float* __restrict__ angles,
-                const int* __restrict__ labels, const float* __restrict__ params, int N, float* __restrict__ out) {
+                const int* __restrict__ labels, const float* __restrict__ params, int N, float* __restrict__ out,
+                const ReadoutNoise rn) {
     using C = SvCfg<NQ>;
     __shared__ float2 tab[TR_MAX_P];
     __shared__ float red[2];
@@ -328,6 +337,11 @@ vqc_eval_kernel(int n_layers, int basis, int ent, int n_classes, const float* __
         ansatz_forward(psi, trig, n_layers, ent, lg);
         float ez[NQ];
         psi.expval_z_all(ez, lg);
+        if (rn.alpha != 1.f || rn.beta != 0.f || rn.shots > 0) {
+#pragma unroll
+            for (int q = 0; q < NQ; ++q)
+                if (q < n_classes) ez[q] = readout_noise(ez[q], rn, (unsigned long long)jj, q);
+        }
         float z[TR_MAX_C], dz[TR_MAX_C];
 #pragma unroll
         for (int q = 0; q < NQ; ++q)
@@ -387,12 +401,12 @@ struct TrainLaunch {
 template <int NQ>
 struct EvalLaunch {
     static int run(int L, int basis, int ent, int nc, const float* angles, const int* labels, const float* params,
-                   int N, float* out, cudaStream_t st) {
+                   int N, float* out, ReadoutNoise rn, cudaStream_t st) {
         QFX_CUDA_TRY(cudaMemsetAsync(out, 0, 2 * sizeof(float), st));
         const int slots_cta = TR_THREADS >> SvCfg<NQ>::LB;
         int blocks = (N + slots_cta - 1) / slots_cta;
         if (blocks > 4 * 148) blocks = 4 * 148;
-        vqc_eval_kernel<NQ><<<blocks, TR_THREADS, 0, st>>>(L, basis, ent, nc, angles, labels, params, N, out);
+        vqc_eval_kernel<NQ><<<blocks, TR_THREADS, 0, st>>>(L, basis, ent, nc, angles, labels, params, N, out, rn);
         return check_launch("vqc_eval_kernel");
     }
 };
@@ -419,12 +433,13 @@ static int dispatch_nq2(int n_qubits, Args&&... args) {
 
 using namespace qfx;
 
-extern "C" int qfx_vqc_local_train(int n_qubits, int n_layers, int basis, int entangler, int n_classes,
+extern "C" int qfx_vqc_local_train_noisy(int n_qubits, int n_layers, int basis, int entangler, int n_classes,
                                    const float* angles, const int* labels, const int* offsets, const int* perm,
                                    int n_total, const float* params_in, const int* client_ids, int n_selected,
                                    float* params_out, float* stats_out, int epochs, int batch_size, int optimizer,
                                    float lr, float beta1, float beta2, float eps, int grad_mode, int cluster_size,
-                                   int lane_mode, unsigned long long shuffle_key, cudaStream_t stream) {
+                                   int lane_mode, unsigned long long shuffle_key, float noise_alpha, float noise_beta,
+                                   int shots, unsigned long long noise_key, cudaStream_t stream) {
     QFX_ARG_CHECK(n_qubits >= 1 && n_qubits <= 10, QFX_ERR_UNSUPPORTED, "n_qubits %d not in 1..10", n_qubits);
     QFX_ARG_CHECK(n_layers >= 1 && 2 * n_qubits * n_layers <= TR_MAX_P, QFX_ERR_TOO_LARGE, "too many parameters");
     QFX_ARG_CHECK(n_classes >= 1 && n_classes <= n_qubits && n_classes <= TR_MAX_C, QFX_ERR_BAD_ARG,
@@ -440,16 +455,54 @@ extern "C" int qfx_vqc_local_train(int n_qubits, int n_layers, int basis, int en
     a.params_in = params_in; a.client_ids = client_ids; a.params_out = params_out; a.stats_out = stats_out;
     a.epochs = epochs; a.batch_size = batch_size; a.opt = optimizer; a.lr = lr; a.beta1 = beta1; a.beta2 = beta2;
     a.eps = eps; a.grad_mode = grad_mode; a.shuffle_key = shuffle_key;
+    QFX_ARG_CHECK(shots >= 0, QFX_ERR_BAD_ARG, "shots must be >= 0");
+    a.rn = ReadoutNoise{noise_alpha, noise_beta, shots, noise_key};
     return dispatch_nq2<TrainLaunch>(n_qubits, a, n_selected, cluster_size, lane_mode, stream);
+}
+
+extern "C" int qfx_vqc_local_train(int n_qubits, int n_layers, int basis, int entangler, int n_classes,
+                                   const float* angles, const int* labels, const int* offsets, const int* perm,
+                                   int n_total, const float* params_in, const int* client_ids, int n_selected,
+                                   float* params_out, float* stats_out, int epochs, int batch_size, int optimizer,
+                                   float lr, float beta1, float beta2, float eps, int grad_mode, int cluster_size,
+                                   int lane_mode, unsigned long long shuffle_key, cudaStream_t stream) {
+    return qfx_vqc_local_train_noisy(n_qubits, n_layers, basis, entangler, n_classes, angles, labels, offsets, perm, n_total,
+                                     params_in, client_ids, n_selected, params_out, stats_out, epochs, batch_size, optimizer,
+                                     lr, beta1, beta2, eps, grad_mode, cluster_size, lane_mode, shuffle_key, 1.f, 0.f, 0, 0ull,
+                                     stream);
+}
+
+extern "C" int qfx_vqc_eval_noisy(int n_qubits, int n_layers, int basis, int entangler, int n_classes,
+                                  const float* angles, const int* labels, const float* params, int n_samples,
+                                  float* out2, float noise_alpha, float noise_beta, int shots,
+                                  unsigned long long noise_key, cudaStream_t stream) {
+    QFX_ARG_CHECK(n_qubits >= 1 && n_qubits <= 10, QFX_ERR_UNSUPPORTED, "n_qubits %d not in 1..10", n_qubits);
+    QFX_ARG_CHECK(n_layers >= 0 && 2 * n_qubits * n_layers <= TR_MAX_P, QFX_ERR_TOO_LARGE, "too many parameters");
+    QFX_ARG_CHECK(n_classes >= 1 && n_classes <= n_qubits, QFX_ERR_BAD_ARG, "bad n_classes");
+    QFX_ARG_CHECK(n_samples > 0, QFX_ERR_BAD_ARG, "empty dataset");
+    QFX_ARG_CHECK(shots >= 0, QFX_ERR_BAD_ARG, "shots must be >= 0");
+    return dispatch_nq2<EvalLaunch>(n_qubits, n_layers, basis, entangler, n_classes, angles, labels, params,
+                                    n_samples, out2, ReadoutNoise{noise_alpha, noise_beta, shots, noise_key}, stream);
 }
 
 extern "C" int qfx_vqc_eval(int n_qubits, int n_layers, int basis, int entangler, int n_classes,
                             const float* angles, const int* labels, const float* params, int n_samples,
                             float* out2, cudaStream_t stream) {
-    QFX_ARG_CHECK(n_qubits >= 1 && n_qubits <= 10, QFX_ERR_UNSUPPORTED, "n_qubits %d not in 1..10", n_qubits);
-    QFX_ARG_CHECK(n_layers >= 0 && 2 * n_qubits * n_layers <= TR_MAX_P, QFX_ERR_TOO_LARGE, "too many parameters");
-    QFX_ARG_CHECK(n_classes >= 1 && n_classes <= n_qubits, QFX_ERR_BAD_ARG, "bad n_classes");
-    QFX_ARG_CHECK(n_samples > 0, QFX_ERR_BAD_ARG, "empty dataset");
-    return dispatch_nq2<EvalLaunch>(n_qubits, n_layers, basis, entangler, n_classes, angles, labels, params,
-                                    n_samples, out2, stream);
+    return qfx_vqc_eval_noisy(n_qubits, n_layers, basis, entangler, n_classes, angles, labels, params, n_samples, out2,
+                              1.f, 0.f, 0, 0ull, stream);
+}
+
+// K3 epilogue as a stand-alone pass for the autograd path: E [B, n] exact <Z> -> noisy readout (in place allowed).
+__global__ void __launch_bounds__(256) readout_noise_kernel(const float* __restrict__ E, float* __restrict__ out, int B, int n,
+                                                            const qfx::ReadoutNoise rn) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= B * n) return;
+    out[i] = qfx::readout_noise(E[i], rn, (unsigned long long)(i / n), i % n);
+}
+extern "C" int qfx_readout_noise(const float* expvals, float* out, int batch, int n_qubits, float noise_alpha,
+                                 float noise_beta, int shots, unsigned long long noise_key, cudaStream_t stream) {
+    QFX_ARG_CHECK(expvals && out && batch >= 1 && n_qubits >= 1 && shots >= 0, QFX_ERR_BAD_ARG, "bad arguments");
+    readout_noise_kernel<<<(batch * n_qubits + 255) / 256, 256, 0, stream>>>(expvals, out, batch, n_qubits,
+                                                                             ReadoutNoise{noise_alpha, noise_beta, shots, noise_key});
+    return check_launch("readout_noise_kernel");
 }

@@ -30,10 +30,12 @@ def stream_at(key, idx):
         return mix64(_U(key) ^ (np.asarray(idx, dtype=_U) * _U(0x9E3779B97F4A7C15)))
 
 
-def pair_mask(seed: int, rnd: int, i: int, j: int, n_clients: int, dim: int) -> np.ndarray:
-    """uint64 [dim] mask shared by clients i<j in round ``rnd``."""
+def pair_mask(seed: int, rnd: int, i: int, j: int, n_clients: int, dim: int, pair_keys=None) -> np.ndarray:
+    """uint64 [dim] mask shared by clients i<j in round ``rnd``.  ``pair_keys`` [K, K] (uint64): the pair's secret from
+    the key agreement keys the stream instead of the job seed (csrc/fedavg_fused.cu does the same)."""
     lo, hi = (i, j) if i < j else (j, i)
-    k = key3(_U(seed) ^ _U(TAG_MASK), rnd, lo * n_clients + hi)
+    base = _U(seed) if pair_keys is None else _U(pair_keys[lo, hi])
+    k = key3(base ^ _U(TAG_MASK), rnd, lo * n_clients + hi)
     return stream_at(k, np.arange(dim, dtype=_U))
 
 

@@ -17,14 +17,17 @@ TAG_SAMPLE = 0x53414D50
 TAG_DROP = 0x44524F50
 
 
-def sample_clients(n_clients: int, fraction: float, rnd: int, seed: int = 0, poisson: bool = False) -> np.ndarray:
-    """Sorted array of selected client ids."""
+def sample_clients(n_clients: int, fraction: float, rnd: int, seed: int = 0, poisson: bool = False,
+                   allow_empty: bool = False) -> np.ndarray:
+    """Sorted array of selected client ids.  Poisson sampling may come up empty: by default the client with the
+    smallest draw is taken then (training always proceeds); ``allow_empty`` returns the empty set, which is what
+    the sampled-Gaussian accountant assumes."""
     if fraction >= 1.0:
         return np.arange(n_clients)
     u = uniform_bits(seed, TAG_SAMPLE, rnd, 0, n_clients)
     if poisson:
         chosen = np.flatnonzero(u < fraction)
-        return chosen if chosen.size else np.array([int(np.argmin(u))])
+        return chosen if (chosen.size or allow_empty) else np.array([int(np.argmin(u))])
     m = max(1, int(round(fraction * n_clients)))
     return np.sort(np.argsort(u, kind="stable")[:m])
 

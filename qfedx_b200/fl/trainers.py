@@ -115,7 +115,7 @@ class VQCFusedTrainer:
     def __init__(self, model: VQC, data: FederatedDataset, epochs: int = 5, batch_size: int = 32,
                  lr: float = 0.05, optimizer: str = "adam", momentum: float = 0.9, betas=(0.9, 0.999),
                  eps: float = 1e-8, grad_method: str = "adjoint", cluster_size: int = 0, shuffle: bool = True,
-                 generator=None, lane_mode: str = "latency", shuffle_mode: str = "feistel", seed: int = 0):
+                 generator=None, lane_mode: str = "latency", shuffle_mode: str = "feistel", seed: int = 0, noise=None):
         if model.encoding != "angle":
             raise ValueError("the fused trainer takes angle-encoded features")
         self.model, self.data = model, data
@@ -126,6 +126,16 @@ class VQCFusedTrainer:
         # 'array': one device sort per round produces explicit permutations
         self.shuffle_mode, self.seed = shuffle_mode, seed
         self.n_wrap = model.n_angle_params
+        # readout-level noise (qfedx_b200.noise.NoiseConfig): applied inside the kernels' <Z> epilogue on CUDA, through
+        # the model's forward on the CPU fallback
+        from ..noise import readout_affine
+        self.noise = noise if (noise is not None and noise.enabled) else getattr(model, "noise", None)
+        if self.noise is not None and self.noise.kind != "none" and self.noise.kind not in ("depolarizing", "amplitude"):
+            raise ValueError(f"unknown noise kind {self.noise.kind!r}")
+        self._noise_ab = readout_affine(self.noise) if self.noise is not None else (1.0, 0.0)
+        self._shots = int(self.noise.shots) if self.noise is not None else 0
+        if self.noise is not None:
+            model.noise = self.noise
         self.cuda = data.device.type == "cuda"
         self.launches = 0
         if self.cuda:
@@ -176,7 +186,8 @@ class VQCFusedTrainer:
         skey = shuffle_key(self.seed, rnd) if (self.shuffle and not use_array) else 0
         beta1 = self.momentum if self.optimizer == "sgd" else self.betas[0]
         g = global_flat.contiguous().float()
-        _lib.call("qfx_vqc_local_train", _lib.c_int(m.n_qubits), _lib.c_int(m.n_layers), _lib.c_int(BASIS[m.basis]),
+        from .prng import shuffle_key as _key
+        _lib.call("qfx_vqc_local_train_noisy", _lib.c_int(m.n_qubits), _lib.c_int(m.n_layers), _lib.c_int(BASIS[m.basis]),
                   _lib.c_int(ENTANGLER[m.entangler]), _lib.c_int(m.n_logits), _lib.ptr(self.angles),
                   _lib.ptr(self.labels), _lib.ptr(self.data.offsets), _lib.ptr(perm),
                   _lib.c_int(self.angles.shape[0]), _lib.ptr(g), _lib.ptr(sel), _lib.c_int(K), _lib.ptr(out),
@@ -184,7 +195,9 @@ class VQCFusedTrainer:
                   _lib.c_int(OPTIMIZERS[self.optimizer]), _lib.c_float(self.lr), _lib.c_float(beta1),
                   _lib.c_float(self.betas[1]), _lib.c_float(self.eps),
                   _lib.c_int(0 if self.grad_method == "adjoint" else 1), _lib.c_int(self.cluster_size),
-                  _lib.c_int(self.lane_mode), _lib.c_u64(skey), _lib.stream_ptr())
+                  _lib.c_int(self.lane_mode), _lib.c_u64(skey), _lib.c_float(self._noise_ab[0]),
+                  _lib.c_float(self._noise_ab[1]), _lib.c_int(self._shots), _lib.c_u64(_key(self.seed ^ 0x5EED, rnd)),
+                  _lib.stream_ptr())
         self.launches += 1
         self._last_stats = stats
         return out, {"train_stats": stats}
@@ -194,10 +207,13 @@ class VQCFusedTrainer:
             return self._fallback.evaluate(global_flat, X, y)
         m = self.model
         out2 = torch.empty(2, device=X.device, dtype=torch.float32)
-        _lib.call("qfx_vqc_eval", _lib.c_int(m.n_qubits), _lib.c_int(m.n_layers), _lib.c_int(BASIS[m.basis]),
+        self._eval_calls = getattr(self, "_eval_calls", 0) + 1
+        _lib.call("qfx_vqc_eval_noisy", _lib.c_int(m.n_qubits), _lib.c_int(m.n_layers), _lib.c_int(BASIS[m.basis]),
                   _lib.c_int(ENTANGLER[m.entangler]), _lib.c_int(m.n_logits), _lib.ptr(X.contiguous().float()),
                   _lib.ptr(y.to(torch.int32).contiguous()), _lib.ptr(global_flat.contiguous().float()),
-                  _lib.c_int(X.shape[0]), _lib.ptr(out2), _lib.stream_ptr())
+                  _lib.c_int(X.shape[0]), _lib.ptr(out2), _lib.c_float(self._noise_ab[0]),
+                  _lib.c_float(self._noise_ab[1]), _lib.c_int(self._shots),
+                  _lib.c_u64((self.seed * 0x9E3779B97F4A7C15 + self._eval_calls) & (2 ** 64 - 1)), _lib.stream_ptr())
         self.launches += 1
         res = out2.cpu()  # the round's single host sync
         return float(res[0]) / X.shape[0], float(res[1]) / X.shape[0]

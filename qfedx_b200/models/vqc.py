@@ -24,7 +24,7 @@ from ..ops import statevector as _sv
 class VQC(nn.Module):
     def __init__(self, n_qubits: int = 4, n_layers: int = 2, num_classes: int = 2, basis: str = "ry",
                  entangler: str = "cnot", encoding: str = "angle", grad_method: str = "adjoint",
-                 init_scale: float = 0.1):
+                 init_scale: float = 0.1, noise=None):
         super().__init__()
         self.n_qubits, self.n_layers = n_qubits, n_layers
         self.n_logits = 1 if num_classes <= 2 else num_classes
@@ -32,6 +32,8 @@ class VQC(nn.Module):
             raise ValueError(f"{num_classes} classes need at least {self.n_logits} readout qubits")
         self.num_classes = num_classes
         self.basis, self.entangler, self.encoding, self.grad_method = basis, entangler, encoding, grad_method
+        # optional qfedx_b200.noise.NoiseConfig: readout-level noise (depolarizing / damping / confusion / shots) on <Z>
+        self.noise = noise if (noise is not None and noise.enabled) else None
         self.theta = nn.Parameter(init_scale * torch.randn(n_layers, n_qubits, 2))
         self.readout_scale = nn.Parameter(torch.ones(self.n_logits))
         self.readout_bias = nn.Parameter(torch.zeros(self.n_logits))
@@ -59,8 +61,11 @@ class VQC(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         """x: [B, n] feature-map angles (or [B, 2^n] unit-norm amplitudes) -> logits [B, n_logits]."""
-        E = self.expvals(x)
-        return self.readout_scale * E[:, : self.n_logits] + self.readout_bias
+        E = self.expvals(x)[:, : self.n_logits]
+        if self.noise is not None:
+            from ..noise import apply_to_expvals
+            E = apply_to_expvals(E, self.noise)      # affine channels keep the gradient, shots are straight-through
+        return self.readout_scale * E + self.readout_bias
 
     def loss(self, logits: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         if self.n_logits == 1:

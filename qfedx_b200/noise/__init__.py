@@ -32,6 +32,33 @@ class NoiseConfig:
         return self.kind != "none" or self.shots > 0 or self.readout_p01 > 0 or self.readout_p10 > 0
 
 
+def readout_affine(cfg: NoiseConfig):
+    """(alpha, beta) with E' = alpha * E + beta for the closed-form channels acting on a measured <Z>: depolarizing
+    on the readout qubit, amplitude damping towards |0>, then the readout confusion matrix.  The sm_100a training and
+    evaluation kernels apply exactly this map in their <Z> epilogue (csrc/common.cuh: ReadoutNoise)."""
+    a, b = 1.0, 0.0
+    if cfg.kind == "depolarizing" and cfg.p > 0:
+        a, b = (1.0 - cfg.p) * a, (1.0 - cfg.p) * b
+    if cfg.kind == "amplitude" and cfg.gamma > 0:
+        a, b = (1.0 - cfg.gamma) * a, (1.0 - cfg.gamma) * b + cfg.gamma
+    if cfg.readout_p01 > 0 or cfg.readout_p10 > 0:
+        s, t = 1.0 - cfg.readout_p01 - cfg.readout_p10, cfg.readout_p10 - cfg.readout_p01
+        a, b = s * a, s * b + t
+    return a, b
+
+
+def noisy_expvals_cuda(E: torch.Tensor, cfg: NoiseConfig, key: int = 0) -> torch.Tensor:
+    """Readout noise on CUDA expectation values through the library's K3 epilogue pass (no autograd)."""
+    from ..ops import _lib
+    a, b = readout_affine(cfg)
+    E = E.contiguous().float()
+    out = torch.empty_like(E)
+    _lib.call("qfx_readout_noise", _lib.ptr(E), _lib.ptr(out), _lib.c_int(E.shape[0]), _lib.c_int(E.shape[1]),
+              _lib.c_float(a), _lib.c_float(b), _lib.c_int(int(cfg.shots)), _lib.c_u64(key & (2 ** 64 - 1)),
+              _lib.stream_ptr())
+    return out
+
+
 def apply_to_expvals(E: torch.Tensor, cfg: NoiseConfig, generator=None) -> torch.Tensor:
     """Readout-level noise on exact <Z> values [B, n] (differentiable except for shot sampling)."""
     out = E

@@ -41,13 +41,16 @@ class MultiGpuAggregator:
         self.slot_tables = [s.peer_table() for s in self.slots]
         self.flag_table = self.flags.peer_table()
         self.epoch = 0
-        self._scratch = torch.empty(4096, device=device, dtype=torch.float32)
+        self._scratch = torch.empty(4096, device=device, dtype=torch.float32)   # grown on demand (one float per local client)
+        self._pair_keys = None
 
     def __call__(self, client_params, global_params, weights, participate=None, mode="delta", n_wrap=0, clip=0.0,
-                 sigma=0.0, server_lr=1.0, seed=0, rnd=0, secagg=False, gids=None, out=None, **_):
+                 sigma=0.0, server_lr=1.0, seed=0, rnd=0, secagg=False, gids=None, out=None, pair_keys=None, **_):
         dev = self.device
         k_local = 0 if client_params is None else client_params.shape[0]
         k_global = weights.numel()
+        if k_local > self._scratch.numel():      # the kernel clears and accumulates one squared norm per local client
+            self._scratch = torch.empty(k_local, device=dev, dtype=torch.float32)
         w = weights.to(dev, torch.float32).contiguous()
         part = None if participate is None else torch.as_tensor(participate).to(dev, torch.int32).contiguous()
         g = global_params.contiguous().float()
@@ -56,6 +59,18 @@ class MultiGpuAggregator:
         cp = client_params.contiguous().float() if k_local else g  # any valid pointer when there are no rows
         self.epoch += 1
         tab = self.slot_tables[self.epoch & 1]
+        if secagg and pair_keys is not None:
+            from ..ops.aggregate import pair_keys_tensor
+            if self._pair_keys is None:
+                self._pair_keys = pair_keys_tensor(pair_keys, dev)
+            _lib.call("qfx_fedavg_fused_multi_pairkeys", _lib.ptr(cp), _lib.ptr(g), _lib.ptr(new), _lib.ptr(w), _lib.ptr(part),
+                      _lib.ptr(gid_t), _lib.c_int(k_local), _lib.c_int(k_global), _lib.c_int(self.dim),
+                      _lib.c_int(MODES[mode]), _lib.c_int(n_wrap), _lib.c_float(clip or 0.0), _lib.c_float(sigma or 0.0),
+                      _lib.c_float(server_lr), _lib.c_u64(seed & (2 ** 64 - 1)), _lib.c_int(rnd),
+                      _lib.ptr(self._pair_keys), _lib.ptr(None), _lib.ptr(self._scratch), _lib.c_int(self.rank),
+                      _lib.c_int(self.world), _lib.ptr(tab), _lib.ptr(self.flag_table), _lib.c_u32(self.epoch),
+                      _lib.stream_ptr())
+            return AggResult(new)
         _lib.call("qfx_fedavg_fused_multi", _lib.ptr(cp), _lib.ptr(g), _lib.ptr(new), _lib.ptr(w), _lib.ptr(part),
                   _lib.ptr(gid_t), _lib.c_int(k_local), _lib.c_int(k_global), _lib.c_int(self.dim),
                   _lib.c_int(MODES[mode]), _lib.c_int(n_wrap), _lib.c_float(clip or 0.0), _lib.c_float(sigma or 0.0),
