@@ -408,18 +408,29 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="cfed", choices=["cfed", "vqc8", "vqc4", "vqc20", "vqc30"])
     ap.add_argument("--no-aux", action="store_true", help="skip the secondary measurements")
+    ap.add_argument("--allow-shrink", action="store_true",
+                    help="honour QFX_BENCH_CLIENTS / QFX_BENCH_SCALE (smoke runs; the line then says so and is not a headline)")
     args = ap.parse_args()
     rank, world, local = dist_env()
     init_dist(world, local)
     cfgs = {"cfed": CFED, "vqc8": VQC8, "vqc4": VQC4, "vqc20": VQC20, "vqc30": VQC30}
     cfg = dict(cfgs[args.config])
-    if os.environ.get("QFX_BENCH_CLIENTS"):  # profiling aid: change the client count
-        cfg["clients"] = int(os.environ["QFX_BENCH_CLIENTS"])
-    if os.environ.get("QFX_BENCH_SCALE"):  # shrink the job for smoke runs
-        f = float(os.environ["QFX_BENCH_SCALE"])
-        for k in ("samples_per_client", "n_train", "test_n"):
-            if k in cfg:
-                cfg[k] = max(64, int(cfg[k] * f))
+    # every QFX_* variable this process can see is echoed in the JSON line; the two that change the size of the timed
+    # job are refused unless --allow-shrink is given (and then mark the line as shrunk)
+    env_seen = {k: v for k, v in sorted(os.environ.items()) if k.startswith("QFX_")}
+    shrunk = False
+    if os.environ.get("QFX_BENCH_CLIENTS") or os.environ.get("QFX_BENCH_SCALE"):
+        if not args.allow_shrink:
+            raise SystemExit("QFX_BENCH_CLIENTS / QFX_BENCH_SCALE change the timed job: pass --allow-shrink to use them "
+                             "(the result is then labelled as shrunk and is not the headline config)")
+        shrunk = True
+        if os.environ.get("QFX_BENCH_CLIENTS"):
+            cfg["clients"] = int(os.environ["QFX_BENCH_CLIENTS"])
+        if os.environ.get("QFX_BENCH_SCALE"):
+            f = float(os.environ["QFX_BENCH_SCALE"])
+            for k in ("samples_per_client", "n_train", "test_n"):
+                if k in cfg:
+                    cfg[k] = max(64, int(cfg[k] * f))
 
     if args.impl == "reference":
         r = run_reference(cfg, args, rank, world, local)
@@ -463,6 +474,7 @@ def main():
                     "d2h_bytes_per_step": r["d2h"]},
             "gpu_launches": r["launches"],
             "final_eval": {"loss": r["eval"][0], "accuracy": r["eval"][1]} if r.get("eval") else None,
+            "env": env_seen, "shrunk": shrunk,
             "aux": aux,
         }
         print(json.dumps(line))

@@ -42,7 +42,8 @@ def federated_learning(client_data: Sequence[TensorPair], test_data: Optional[Te
     trainer = None
     if engine != "torch" and dev.type == "cuda":
         from .trainers_cnn import TinyCNNBatchedTrainer
-        trainer = TinyCNNBatchedTrainer(model, data, epochs=local_epochs, batch_size=batch_size, lr=learning_rate)
+        trainer = TinyCNNBatchedTrainer(model, data, epochs=local_epochs, batch_size=batch_size, lr=learning_rate,
+                                        seed=cfg.seed)
     if trainer is None:
         trainer = TorchLocalTrainer(model, data, torch.nn.CrossEntropyLoss(), local_epochs, batch_size,
                                     learning_rate, "sgd", 0.9)
@@ -64,8 +65,9 @@ def quantum_federated_learning(client_data: Sequence[TensorPair], test_data: Opt
                                local_epochs: int = 5, learning_rate: float = 0.05, batch_size: int = 32,
                                optimizer: str = "adam", reducer: str = "block", grad_method: str = "adjoint",
                                device=None, fl_config: FLConfig | None = None, entangler: str = "cnot",
-                               **fl_kwargs) -> dict:
-    """VQC FedAvg.  Inputs are images (reduced to angles here) or already [N, n_qubits] angles."""
+                               noise=None, **fl_kwargs) -> dict:
+    """VQC FedAvg.  Inputs are images (reduced to angles here) or already [N, n_qubits] angles.
+    ``noise``: an optional qfedx_b200.noise.NoiseConfig applied to the readout during training and evaluation."""
     dev = _device(device)
     if fl_config is None:
         fl_kwargs.setdefault("mode", "delta")
@@ -83,10 +85,10 @@ def quantum_federated_learning(client_data: Sequence[TensorPair], test_data: Opt
 
     clients = [(feats(X), y.to(dev).long()) for X, y in client_data]
     data = FederatedDataset.from_clients(clients, dev)
-    model = VQC(n_qubits, n_layers, num_classes, entangler=entangler, grad_method=grad_method).to(dev)
+    model = VQC(n_qubits, n_layers, num_classes, entangler=entangler, grad_method=grad_method, noise=noise).to(dev)
     test = None if test_data is None else (feats(test_data[0]), test_data[1].to(dev).long())
     trainer = VQCFusedTrainer(model, data, local_epochs, batch_size, learning_rate, optimizer,
-                              grad_method=grad_method)
+                              grad_method=grad_method, seed=cfg.seed, noise=noise)
     out = FederatedRunner(trainer, cfg, test).run()
     out["pca"] = pca
     return out
