@@ -152,6 +152,31 @@ int qfx_symm_close(void* ptr);
 int qfx_symm_free(void* ptr);
 int qfx_enable_peer(int dev, int peer);
 
+/* K7 across GPUs with an explicit exchange algorithm.  two_shot 0: every rank pushes its partial sum into every peer's
+ * slot and reduces W slots locally (one cross-GPU barrier; recv_slots: world x dim 64-bit words per rank) - the choice for
+ * latency-bound vectors.  two_shot 1: partials stay local, rank r pulls slice r of every peer's partial, reduces and
+ * updates it, then every rank gathers the other slices by peer loads (two barriers; recv_slots: 2 x dim words per rank):
+ * 2 (W-1)/W D instead of (W-1) D words over NVLink per rank.  pair_keys nullable; flags >= 32 words per rank. */
+int qfx_fedavg_fused_multi_ex(const float* client_params, const float* global_in, float* global_out,
+                              const float* weights, const int* participate, const int* client_gids,
+                              int k_local, int k_global, int dim, int mode, int n_wrap, float clip,
+                              float sigma, float server_lr, unsigned long long seed, int round, int secagg,
+                              const unsigned long long* pair_keys, float* norms_out, float* scratch,
+                              int rank, int world, long long* const* recv_slots,
+                              unsigned int* const* flags, unsigned int epoch, int two_shot, cudaStream_t stream);
+
+/* Loopback world for tests on a single GPU: `world` logical ranks of K7's multi-GPU path in ONE cooperative launch
+ * (blockIdx.y = rank; every "rank's" receive slots and flag words live in this GPU's memory).  client_params, client_gids,
+ * k_local, global_out and scratch are HOST arrays with one entry per rank; args_dev is world * 512 bytes of device scratch. */
+int qfx_fedavg_fused_loopback(int world, const float* const* client_params, const int* const* client_gids,
+                              const int* k_local, float* const* global_out, float* const* scratch,
+                              const float* global_in, const float* weights, const int* participate,
+                              int k_global, int dim, int mode, int n_wrap, float clip, float sigma,
+                              float server_lr, unsigned long long seed, int round, int secagg,
+                              const unsigned long long* pair_keys, long long* const* recv_slots,
+                              unsigned int* const* flags, unsigned int epoch, int two_shot, void* args_dev,
+                              cudaStream_t stream);
+
 /* K7 with per-pair mask secrets: pair_keys [k_global, k_global] holds at [lo * k_global + hi] the 64-bit secret clients
  * lo < hi agreed on at registration (qfedx_b200/fl/secagg.py: KeyAgreement - the "seed exchange API" planned in
  * /root/reference/ROADMAP.md:52-55); each pair's mask stream is keyed by its secret instead of the job seed. */
@@ -288,6 +313,15 @@ int qfx_tinycnn_conv2_fwd_umma(const float* a1, const float* weight, const float
 int qfx_tinycnn_conv2_dgrad_umma(const float* g2, const float* weight, int n, float* da1, void* scratch,
                                  cudaStream_t stream);
 int qfx_tinycnn_conv2_wgrad_umma(const float* g2, const float* a1, int n, float* part, cudaStream_t stream);
+
+/* tuning knob of K6: CTAs per SM of the fused swap's grid on the current device (0 = default 4) */
+int qfx_sv_swap_set_ctas_per_sm(int ctas_per_sm);
+
+/* NVLink bandwidth probes on the symmetric heap (csrc/p2p_probe.cu), run beside K6 so that its roofline is measured in the
+ * same job: mode 0 ring pull (peer copy), 1 all-to-all pull (the swap's pattern without gates), 2 all-to-all push.
+ * Plain loads / stores on peer pointers; the host orders the launches.  No reference counterpart. */
+int qfx_p2p_probe(const float* const* src_table, float* const* dst_table, size_t shard_bytes, int rank, int world,
+                  int mode, int unroll, int ctas_per_sm, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

@@ -119,8 +119,68 @@ def large_state_throughput(n=20, L=2, batch=16, tile_bits=12, low_bits=3, regist
             "expvals_ms": _time_ms(lambda: vqc.expvals(ang, theta), iters=5, warmup=2)}
 
 
+def multi_gpu_aggregation(rank, world, dev, D=100_000_000 // 8 * 8, iters=5):
+    """K7 across GPUs (peer stores + flags inside the cooperative launch) against NCCL all_reduce on a 1e8-float
+    vector: every rank holds ONE client row, plain FedAvg of weights (one sweep), max time over ranks."""
+    import torch.distributed as dist
+    from .parallel.runtime import MultiGpuAggregator
+    from .utils.timing import max_over_ranks
+    fused = MultiGpuAggregator(rank, world, D, dev)
+    row = torch.randn(1, D, device=dev)
+    glob = torch.zeros(D, device=dev)
+    out = torch.empty(D, device=dev)
+    w = torch.ones(world)
+
+    def run_fused():
+        fused(row, glob, w, None, mode="weights", gids=[rank], out=out)
+
+    def run_nccl():
+        out.copy_(row[0])
+        out.mul_(1.0 / world)
+        dist.all_reduce(out)
+
+    res = {}
+    for name, fn in (("fused_ms", run_fused), ("nccl_all_reduce_ms", run_nccl)):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize(); dist.barrier()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(iters):
+            fn()
+        e.record(); torch.cuda.synchronize()
+        res[name] = max_over_ranks(s.elapsed_time(e) / iters)
+    run_fused(); a = out.clone(); run_nccl()
+    res["max_abs_diff_vs_nccl"] = float((a - out).abs().max())
+    res.update({"floats": D, "world": world,
+                "fused_algbw_gbs": D * 4 / res["fused_ms"] / 1e6, "nccl_algbw_gbs": D * 4 / res["nccl_all_reduce_ms"] / 1e6,
+                "fused_vs_nccl": res["nccl_all_reduce_ms"] / res["fused_ms"]})
+    del fused
+    torch.cuda.empty_cache()
+    return res
+
+
+def multi_gpu_aux(rank, world, local):
+    """Secondary measurements that need every rank: the K6 swap against its rooflines and baselines, and K7 across
+    GPUs against NCCL.  Sized to the job: 27 local qubits per GPU (1 GiB shards) as in BASELINE config 5."""
+    import math
+    from .bench_sharded import swap_measurements
+    dev = torch.device("cuda", local)
+    out = {}
+    g = int(math.log2(world))
+    if (1 << g) == world and world in (2, 4, 8):
+        out["k6_swap"] = swap_measurements(rank, world, dev, 27 + g, layers=1, iters=5, with_layer=(world == 8))
+    out["k7_allreduce_1e8"] = multi_gpu_aggregation(rank, world, dev)
+    return out
+
+
 def aux_measurements(args=None, rank=0, world=1, local=0, skip=None):
     out = {}
+    if world > 1:
+        try:
+            out.update(multi_gpu_aux(rank, world, local))
+        except Exception as exc:   # keep the single-GPU numbers if a collective measurement fails
+            out["multi_gpu_error"] = f"{type(exc).__name__}: {exc}"
     if rank != 0:
         return out
     out["sv8_throughput"] = small_circuit_throughput(8, 6, 1 << 15)

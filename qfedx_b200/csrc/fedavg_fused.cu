@@ -54,6 +54,10 @@ struct AggArgs {
                                    // [world][dim] int64 (secagg) or viewed as float (plain)
     unsigned int* const* flags;    // [world] device pointers: flags[r] = rank r's flag array [world]
     unsigned int epoch;            // value written into flags this round (monotonic)
+    int two_shot;                  // 0: every rank pushes its partial to every peer and reduces W slots locally (one
+                                   //    barrier; best for latency-bound sizes).  1: partials stay local, rank r pulls slice r
+                                   //    of every peer's partial, reduces and updates it, then every rank gathers the other
+                                   //    slices (two barriers, 2 (W-1)/W D words over NVLink per rank instead of (W-1) D)
 };
 
 __device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
@@ -120,8 +124,7 @@ template <> struct VecIO<4> {
 // VEC: floats per access (4 needs dim % 4 == 0 and 16-byte aligned bases).  UNR: independent accesses per
 // thread per trip (with the one-client-ahead prefetch in phase 2: 2 x UNR x VEC x 4 bytes in flight).
 template <int VEC, int UNR, bool FIXED>
-__global__ void __launch_bounds__(AGG_THREADS)
-fedavg_fused_kernel(const AggArgs a, const int mask_keys_in_smem) {
+__device__ __forceinline__ void fedavg_fused_body(const AggArgs& a, const int mask_keys_in_smem) {
     using IO = VecIO<VEC>;
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(16) unsigned char agg_smem[];
@@ -315,10 +318,16 @@ fedavg_fused_kernel(const AggArgs a, const int mask_keys_in_smem) {
                 }
                 IO::st(a.global_out + d, o);
             } else {
-                // push this rank's partial into slot [rank] of every rank (self included)
-                for (int r = 0; r < a.world; ++r) {
-                    if constexpr (FIXED) IO::st(a.recv_slots[r] + (size_t)a.rank * a.dim + d, iacc[u]);
-                    else IO::st(reinterpret_cast<float*>(a.recv_slots[r]) + (size_t)a.rank * a.dim + d, facc[u]);
+                if (a.two_shot) {
+                    // keep the partial here (region 0 of this rank's symmetric buffer); peers pull their slice of it
+                    if constexpr (FIXED) IO::st(a.recv_slots[a.rank] + d, iacc[u]);
+                    else IO::st(reinterpret_cast<float*>(a.recv_slots[a.rank]) + d, facc[u]);
+                } else {
+                    // push this rank's partial into slot [rank] of every rank (self included)
+                    for (int r = 0; r < a.world; ++r) {
+                        if constexpr (FIXED) IO::st(a.recv_slots[r] + (size_t)a.rank * a.dim + d, iacc[u]);
+                        else IO::st(reinterpret_cast<float*>(a.recv_slots[r]) + (size_t)a.rank * a.dim + d, facc[u]);
+                    }
                 }
             }
         }
@@ -334,6 +343,64 @@ fedavg_fused_kernel(const AggArgs a, const int mask_keys_in_smem) {
         while ((int)(ld_acquire_sys(f) - a.epoch) < 0) { __nanosleep(64); }
     }
     grid.sync();
+    if (a.two_shot) {
+        // ---- reduce-scatter by peer loads: this rank owns vectors [lo, hi) ------------------------------
+        const int chunk = (nvec + a.world - 1) / a.world;
+        const int lo = min(nvec, a.rank * chunk), hi = min(nvec, lo + chunk);
+        float* result = reinterpret_cast<float*>(a.recv_slots[a.rank] + a.dim);    // region 1: the updated slice
+        for (int v = lo + g0; v < hi; v += gstride) {
+            const size_t d = (size_t)v * VEC;
+            float upd[VEC];
+            if constexpr (FIXED) {
+                unsigned long long sacc[VEC];
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) sacc[e] = 0ull;
+                for (int r = 0; r < a.world; ++r) {
+                    long long t[VEC];
+                    IO::ldcv(a.recv_slots[r] + d, t);
+#pragma unroll
+                    for (int e = 0; e < VEC; ++e) sacc[e] += (unsigned long long)t[e];
+                }
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) upd[e] = (float)((double)(long long)sacc[e] / FIXED_SCALE);
+            } else {
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) upd[e] = 0.f;
+                for (int r = 0; r < a.world; ++r) {           // fixed rank order: the sum is the same on every run
+                    float t[VEC];
+                    IO::ldcv(reinterpret_cast<const float*>(a.recv_slots[r]) + d, t);
+#pragma unroll
+                    for (int e = 0; e < VEC; ++e) upd[e] += t[e];
+                }
+            }
+            float g[VEC], o[VEC];
+            IO::ld(a.global_in + d, g);
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) o[e] = (a.mode == 1) ? g[e] + a.server_lr * upd[e] : upd[e];
+            IO::st(a.global_out + d, o);
+            IO::st(result + d, o);
+        }
+        // ---- second barrier (its own flag words), then gather the other ranks' slices ---------------------
+        __threadfence_system();
+        grid.sync();
+        if (blockIdx.x == 0 && tid < a.world) st_release_sys(a.flags[tid] + AGG_MAX_WORLD + a.rank, a.epoch);
+        if (blockIdx.x == 0 && tid < a.world) {
+            const unsigned int* f = a.flags[a.rank] + AGG_MAX_WORLD + tid;
+            while ((int)(ld_acquire_sys(f) - a.epoch) < 0) { __nanosleep(64); }
+        }
+        grid.sync();
+        for (int q = 1; q < a.world; ++q) {
+            const int r = (a.rank + q) % a.world;             // start with the next rank: W ranks, W different targets
+            const int rlo = min(nvec, r * chunk), rhi = min(nvec, rlo + chunk);
+            const float* src = reinterpret_cast<const float*>(a.recv_slots[r] + a.dim);
+            for (int v = rlo + g0; v < rhi; v += gstride) {
+                float t[VEC];
+                IO::ldcv(src + (size_t)v * VEC, t);
+                IO::st(a.global_out + (size_t)v * VEC, t);
+            }
+        }
+        return;
+    }
     const long long* mine = a.recv_slots[a.rank];
     for (int v = g0; v < nvec; v += gstride) {
         const size_t d = (size_t)v * VEC;
@@ -369,7 +436,25 @@ fedavg_fused_kernel(const AggArgs a, const int mask_keys_in_smem) {
     }
 }
 
+template <int VEC, int UNR, bool FIXED>
+__global__ void __launch_bounds__(AGG_THREADS)
+fedavg_fused_kernel(const AggArgs a, const int mask_keys_in_smem) {
+    fedavg_fused_body<VEC, UNR, FIXED>(a, mask_keys_in_smem);
+}
+// Loopback world: ONE cooperative launch plays every rank of a W-rank job on one GPU - blockIdx.y is the rank, the
+// receive slots and flag words of all "ranks" live in this device's memory.  The blocks of all ranks are co-resident
+// (cooperative launch), so the flag waits of the cross-rank barriers are safe; grid.sync() then spans all ranks, which
+// is stronger than the per-rank barrier the real job has and changes nothing else.  This is how the multi-GPU phases
+// (publish, flag wait, slot reduce / reduce-scatter + all-gather) are exercised on a single-GPU test box.
+template <int VEC, int UNR, bool FIXED>
+__global__ void __launch_bounds__(AGG_THREADS)
+fedavg_fused_loopback_kernel(const AggArgs* __restrict__ ranks, const int mask_keys_in_smem) {
+    const AggArgs a = ranks[blockIdx.y];
+    fedavg_fused_body<VEC, UNR, FIXED>(a, mask_keys_in_smem);
+}
+
 using AggKernel = void (*)(const AggArgs, const int);
+using AggLoopKernel = void (*)(const AggArgs*, const int);
 
 static int launch_fedavg(AggArgs& a, cudaStream_t stream) {
     QFX_ARG_CHECK(a.k_local >= 0 && a.k_global >= 1 && a.k_global >= a.k_local && a.dim >= 1, QFX_ERR_BAD_ARG, "bad K/D");
@@ -449,6 +534,86 @@ extern "C" int qfx_fedavg_fused_multi(const float* client_params, const float* g
     a.clip = clip; a.sigma = sigma; a.server_lr = server_lr; a.seed = seed; a.round = round; a.secagg = secagg;
     a.norms_out = norms_out; a.scratch = scratch; a.masked_out = nullptr;
     a.rank = rank; a.world = world; a.recv_slots = recv_slots; a.flags = flags; a.epoch = epoch;
+    return launch_fedavg(a, stream);
+}
+
+// Loopback test entry: `world` logical ranks on the current GPU in one cooperative launch (see the kernel above).
+// Per-rank arrays are HOST arrays of length world; everything else is shared.  args_dev: world * 512 bytes of device
+// scratch for the per-rank argument blocks.  Requires dim % 4 == 0 alignment rules to agree across ranks (the test
+// allocates every buffer with torch, 256-byte aligned).
+extern "C" int qfx_fedavg_fused_loopback(int world, const float* const* client_params, const int* const* client_gids,
+                                         const int* k_local, float* const* global_out, float* const* scratch,
+                                         const float* global_in, const float* weights, const int* participate,
+                                         int k_global, int dim, int mode, int n_wrap, float clip, float sigma,
+                                         float server_lr, unsigned long long seed, int round, int secagg,
+                                         const unsigned long long* pair_keys, long long* const* recv_slots,
+                                         unsigned int* const* flags, unsigned int epoch, int two_shot, void* args_dev,
+                                         cudaStream_t stream) {
+    QFX_ARG_CHECK(world >= 2 && world <= AGG_MAX_WORLD && args_dev && recv_slots && flags, QFX_ERR_BAD_ARG, "bad loopback arguments");
+    static_assert(sizeof(AggArgs) <= 512, "argument block");
+    AggArgs host[AGG_MAX_WORLD];
+    int kmax = 0;
+    bool vec4 = dim % 4 == 0;
+    auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+    for (int r = 0; r < world; ++r) {
+        AggArgs a = {};
+        a.client_params = client_params[r] ? client_params[r] : global_in; a.global_in = global_in; a.global_out = global_out[r];
+        a.weights = weights; a.participate = participate; a.client_gids = client_gids[r];
+        a.k_local = k_local[r]; a.k_global = k_global; a.dim = dim; a.mode = mode; a.n_wrap = n_wrap;
+        a.clip = clip; a.sigma = sigma; a.server_lr = server_lr; a.seed = seed; a.round = round; a.secagg = secagg;
+        a.norms_out = nullptr; a.scratch = scratch[r]; a.masked_out = nullptr; a.pair_keys = pair_keys;
+        a.rank = r; a.world = world; a.recv_slots = recv_slots; a.flags = flags; a.epoch = epoch; a.two_shot = two_shot ? 1 : 0;
+        QFX_ARG_CHECK(a.k_local >= 0 && a.scratch && a.global_out, QFX_ERR_BAD_ARG, "bad per-rank arguments");
+        vec4 = vec4 && al16(a.client_params) && al16(a.global_in) && al16(a.global_out);
+        if (a.k_local > kmax) kmax = a.k_local;
+        if (a.k_local > 0) QFX_CUDA_TRY(cudaMemsetAsync(a.scratch, 0, sizeof(float) * a.k_local, stream));
+        host[r] = a;
+    }
+    char* dev_args = (char*)args_dev;
+    // one argument block per rank at a 512-byte pitch is awkward for indexing: pack them contiguously instead
+    QFX_CUDA_TRY(cudaMemcpyAsync(dev_args, host, sizeof(AggArgs) * world, cudaMemcpyHostToDevice, stream));
+    QFX_CUDA_TRY(cudaStreamSynchronize(stream));     // `host` is a stack array
+    const bool fixed = secagg != 0;
+    int mask_keys = fixed && agg_smem_bytes(kmax, k_global, true) <= 32 * 1024 ? 1 : 0;
+    const size_t smem = agg_smem_bytes(kmax, k_global, mask_keys != 0);
+    AggLoopKernel kern = vec4 ? (fixed ? (AggLoopKernel)fedavg_fused_loopback_kernel<4, 2, true> : (AggLoopKernel)fedavg_fused_loopback_kernel<4, 2, false>)
+                              : (fixed ? (AggLoopKernel)fedavg_fused_loopback_kernel<1, 4, true> : (AggLoopKernel)fedavg_fused_loopback_kernel<1, 4, false>);
+    QFX_CUDA_TRY(cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    int occ = 0;
+    QFX_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)kern, AGG_THREADS, smem));
+    QFX_ARG_CHECK(occ >= 1, QFX_ERR_TOO_LARGE, "aggregation kernel does not fit on an SM");
+    const int per_thread = vec4 ? 4 : 1;
+    long long blocks = ((long long)dim / per_thread + AGG_THREADS - 1) / AGG_THREADS;
+    const long long cap = (long long)device_sm_count() * (occ > 6 ? 6 : occ) / world;     // all ranks co-resident
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    const AggArgs* ranks = reinterpret_cast<const AggArgs*>(dev_args);
+    void* params[] = {(void*)&ranks, (void*)&mask_keys};
+    QFX_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)kern, dim3((unsigned)blocks, (unsigned)world), dim3(AGG_THREADS),
+                                             params, smem, stream));
+    return 0;
+}
+
+// qfx_fedavg_fused_multi with an explicit exchange algorithm: two_shot = 0 is the one-barrier all-gather of partials
+// (recv_slots: world x dim words per rank), two_shot = 1 the reduce-scatter + all-gather by peer loads (recv_slots: 2 x dim
+// words per rank: partial, updated slice) - (W-1) D versus 2 (W-1)/W D words over NVLink per rank.
+// pair_keys may be null (masks from the job seed).  flags: at least 2 * 16 words per rank.
+extern "C" int qfx_fedavg_fused_multi_ex(const float* client_params, const float* global_in, float* global_out,
+                                         const float* weights, const int* participate, const int* client_gids,
+                                         int k_local, int k_global, int dim, int mode, int n_wrap, float clip,
+                                         float sigma, float server_lr, unsigned long long seed, int round, int secagg,
+                                         const unsigned long long* pair_keys, float* norms_out, float* scratch,
+                                         int rank, int world, long long* const* recv_slots,
+                                         unsigned int* const* flags, unsigned int epoch, int two_shot,
+                                         cudaStream_t stream) {
+    AggArgs a = {};
+    a.client_params = client_params; a.global_in = global_in; a.global_out = global_out;
+    a.weights = weights; a.participate = participate; a.client_gids = client_gids;
+    a.k_local = k_local; a.k_global = k_global; a.dim = dim; a.mode = mode; a.n_wrap = n_wrap;
+    a.clip = clip; a.sigma = sigma; a.server_lr = server_lr; a.seed = seed; a.round = round; a.secagg = secagg;
+    a.norms_out = norms_out; a.scratch = scratch; a.masked_out = nullptr; a.pair_keys = pair_keys;
+    a.rank = rank; a.world = world; a.recv_slots = recv_slots; a.flags = flags; a.epoch = epoch;
+    a.two_shot = two_shot ? 1 : 0;
     return launch_fedavg(a, stream);
 }
 

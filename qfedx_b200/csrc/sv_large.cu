@@ -713,6 +713,15 @@ extern "C" int qfx_sv_large_expz_masks(const float* states, int n_local, int n_o
     return check_launch("sv_large_expz_masks_kernel");
 }
 
+// CTAs per SM of the fused swap's grid (tuning knob, per device; results do not depend on it).  More CTAs keep more
+// 16-byte peer loads in flight per SM; beyond what fits on an SM the extra CTAs simply run as a second wave.
+static int g_swap_ctas_per_sm[QFX_MAX_DEVICES] = {};
+extern "C" int qfx_sv_swap_set_ctas_per_sm(int ctas_per_sm) {
+    QFX_ARG_CHECK(ctas_per_sm >= 0 && ctas_per_sm <= 32, QFX_ERR_BAD_ARG, "ctas_per_sm must be in 0..32 (0 = default)");
+    g_swap_ctas_per_sm[current_device()] = ctas_per_sm;
+    return 0;
+}
+
 // src_table: device array of `world` pointers (every rank's source shard, symmetric heap);
 // flags_table: device array of `world` pointers to u32[world] flag arrays (nullable = no barrier,
 // e.g. single-process emulation where the caller orders the launches).
@@ -730,7 +739,8 @@ extern "C" int qfx_sv_global_swap_fused(const float* const* src_table, float* ds
     a.flags = flags_table; a.epoch = epoch;
     const size_t slice = (size_t)1 << (n_local - g_bits);
     size_t blocks = (slice / 2 + 255) / 256;
-    const size_t cap = (size_t)num_sms() * 4;  // co-resident: every CTA spins on the flags first
+    const int cps = g_swap_ctas_per_sm[current_device()] > 0 ? g_swap_ctas_per_sm[current_device()] : 4;
+    const size_t cap = (size_t)num_sms() * cps;  // block 0 (always in the first wave) publishes this rank's flag
     if (blocks > cap) blocks = cap;
     if (g_bits == 1) sv_global_swap_fused_kernel<1><<<(unsigned)blocks, 256, 0, stream>>>(a);
     else if (g_bits == 2) sv_global_swap_fused_kernel<2><<<(unsigned)blocks, 256, 0, stream>>>(a);

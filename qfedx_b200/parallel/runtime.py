@@ -31,10 +31,16 @@ def local_clients(rank: int, n_clients: int, world: int) -> list:
 
 
 class MultiGpuAggregator:
-    def __init__(self, rank: int, world: int, dim: int, device: torch.device):
+    """K7 across GPUs.  Small vectors use the one-barrier exchange (every rank pushes its partial to every peer);
+    from ``two_shot_min_dim`` on the reduce-scatter + all-gather exchange, which moves 2 (W-1)/W D instead of (W-1) D
+    words per rank and needs 2 instead of W receive regions."""
+
+    def __init__(self, rank: int, world: int, dim: int, device: torch.device, two_shot: bool | None = None,
+                 two_shot_min_dim: int = 1 << 18):
         from .symm import SymmetricBuffer
         self.rank, self.world, self.dim, self.device = rank, world, dim, device
-        slot_bytes = world * dim * 8
+        self.two_shot = (dim >= two_shot_min_dim) if two_shot is None else bool(two_shot)
+        slot_bytes = (2 if self.two_shot else world) * dim * 8
         # two receive-slot sets (alternated by epoch parity) + flags
         self.slots = [SymmetricBuffer(slot_bytes, rank, world, device) for _ in range(2)]
         self.flags = SymmetricBuffer(256, rank, world, device)
@@ -59,25 +65,17 @@ class MultiGpuAggregator:
         cp = client_params.contiguous().float() if k_local else g  # any valid pointer when there are no rows
         self.epoch += 1
         tab = self.slot_tables[self.epoch & 1]
-        if secagg and pair_keys is not None:
+        if secagg and pair_keys is not None and self._pair_keys is None:
             from ..ops.aggregate import pair_keys_tensor
-            if self._pair_keys is None:
-                self._pair_keys = pair_keys_tensor(pair_keys, dev)
-            _lib.call("qfx_fedavg_fused_multi_pairkeys", _lib.ptr(cp), _lib.ptr(g), _lib.ptr(new), _lib.ptr(w), _lib.ptr(part),
-                      _lib.ptr(gid_t), _lib.c_int(k_local), _lib.c_int(k_global), _lib.c_int(self.dim),
-                      _lib.c_int(MODES[mode]), _lib.c_int(n_wrap), _lib.c_float(clip or 0.0), _lib.c_float(sigma or 0.0),
-                      _lib.c_float(server_lr), _lib.c_u64(seed & (2 ** 64 - 1)), _lib.c_int(rnd),
-                      _lib.ptr(self._pair_keys), _lib.ptr(None), _lib.ptr(self._scratch), _lib.c_int(self.rank),
-                      _lib.c_int(self.world), _lib.ptr(tab), _lib.ptr(self.flag_table), _lib.c_u32(self.epoch),
-                      _lib.stream_ptr())
-            return AggResult(new)
-        _lib.call("qfx_fedavg_fused_multi", _lib.ptr(cp), _lib.ptr(g), _lib.ptr(new), _lib.ptr(w), _lib.ptr(part),
+            self._pair_keys = pair_keys_tensor(pair_keys, dev)
+        pk = self._pair_keys if (secagg and pair_keys is not None) else None
+        _lib.call("qfx_fedavg_fused_multi_ex", _lib.ptr(cp), _lib.ptr(g), _lib.ptr(new), _lib.ptr(w), _lib.ptr(part),
                   _lib.ptr(gid_t), _lib.c_int(k_local), _lib.c_int(k_global), _lib.c_int(self.dim),
                   _lib.c_int(MODES[mode]), _lib.c_int(n_wrap), _lib.c_float(clip or 0.0), _lib.c_float(sigma or 0.0),
                   _lib.c_float(server_lr), _lib.c_u64(seed & (2 ** 64 - 1)), _lib.c_int(rnd),
-                  _lib.c_int(1 if secagg else 0), _lib.ptr(None), _lib.ptr(self._scratch), _lib.c_int(self.rank),
-                  _lib.c_int(self.world), _lib.ptr(tab), _lib.ptr(self.flag_table), _lib.c_u32(self.epoch),
-                  _lib.stream_ptr())
+                  _lib.c_int(1 if secagg else 0), _lib.ptr(pk), _lib.ptr(None), _lib.ptr(self._scratch),
+                  _lib.c_int(self.rank), _lib.c_int(self.world), _lib.ptr(tab), _lib.ptr(self.flag_table),
+                  _lib.c_u32(self.epoch), _lib.c_int(1 if self.two_shot else 0), _lib.stream_ptr())
         return AggResult(new)
 
 
