@@ -51,8 +51,8 @@ VQC8 = dict(clients=64, n_train=16760, classes=3, n_qubits=8, n_layers=6, epochs
 VQC20 = dict(clients=16, samples_per_client=4, classes=2, n_qubits=20, n_layers=2, epochs=1, batch=4, lr=0.05,
              grad="param_shift", secagg=True, clip=1.0, test_n=16)
 # two layers: the last ring is folded into the readout, so one layer would leave no entangler to simulate (and no swap)
-VQC30 = dict(clients=8, samples_per_client=1, classes=2, n_qubits=30, n_layers=2, epochs=1, batch=1, lr=0.05,
-             grad="spsa", secagg=False, clip=0.0, test_n=2)
+VQC30 = dict(clients=8, samples_per_client=8, classes=2, n_qubits=30, n_layers=2, epochs=1, batch=8, lr=0.05,
+             grad="spsa", secagg=False, clip=0.0, test_n=4)
 # conv2 implementation of the cfed headline.  The default must be fp32-accurate (the reference trains in fp32): "split" is
 # the persistent round kernel with split-bf16 tensor-core conv2 (passes the fp32 test tolerance), "fp32" the all-CUDA-core
 # graph path; "tcgen05" (single bf16 operands) is an opt-in secondary line and is reported as dtype bf16.

@@ -314,6 +314,17 @@ int qfx_tinycnn_conv2_dgrad_umma(const float* g2, const float* weight, int n, fl
                                  cudaStream_t stream);
 int qfx_tinycnn_conv2_wgrad_umma(const float* g2, const float* a1, int n, float* part, cudaStream_t stream);
 
+/* Adjoint differentiation on the pass engine (K4a for large states; the "adjoint" option of /root/reference/ROADMAP.md:23,27):
+ * qfx_sv_large_parity_obs builds lambda = (sum_q cot[b][q] Z-string(masks[q])) psi after the forward passes;
+ * qfx_sv_large_adjoint_pass walks one compiled pass BACKWARDS over psi and lambda (both end as they were before the pass)
+ * and accumulates d/d theta into grad [theta_rows][n_params] (caller-zeroed).  Call it for the passes in reverse order. */
+int qfx_sv_large_parity_obs(const float* psi, float* lam, int n_local, int n_out, const unsigned long long* masks_host,
+                            const float* cot, int batch, cudaStream_t stream);
+int qfx_sv_large_adjoint_pass(float* psi, float* lam, int n_qubits, int batch, int tile_bits, int low_bits,
+                              const int* tile_qubits_host, const int* ops_dev, int n_ops, const float* theta,
+                              int theta_rows, int n_params, const float* angles, int angle_rows, int n_feature,
+                              float* grad, cudaStream_t stream);
+
 /* tuning knob of K6: CTAs per SM of the fused swap's grid on the current device (0 = default 4) */
 int qfx_sv_swap_set_ctas_per_sm(int ctas_per_sm);
 

@@ -99,6 +99,29 @@ def unitary_gemm_throughput(n=8, L=6, B=1 << 15):
     return out
 
 
+def unitary_gemm_vs_engines():
+    """Where K2 earns its place in the product (models/vqc.py: inference_expvals picks it there): 12 qubits, where no
+    register kernel exists, against the pass engine K5; and a deep 10-qubit circuit over a large batch against the
+    register kernel K1, whose cost grows with the depth while the GEMM's does not.  Times include building and
+    packing the unitary (once per parameter set) separately from the per-batch pipeline."""
+    from .models import VQC
+    dev = torch.device("cuda")
+    out = {}
+    for name, (n, L, B, other) in {"12q_4L_4096": (12, 4, 4096, "passes"), "10q_24L_16384": (10, 24, 16384, "registers")}.items():
+        torch.manual_seed(0)
+        m = VQC(n, L, 2).to(dev)
+        x = torch.rand(B, n, device=dev) * math.pi
+        t_build = _time_ms(lambda: (setattr(m, "_ug_key", None), m.inference_expvals(x[:64], "gemm")), iters=3, warmup=1)
+        a = m.inference_expvals(x, "gemm")
+        b = m.inference_expvals(x, other)
+        t_gemm = _time_ms(lambda: m.inference_expvals(x, "gemm"), iters=10)
+        t_other = _time_ms(lambda: m.inference_expvals(x, other), iters=5)
+        out[name] = {"n_qubits": n, "layers": L, "batch": B, "gemm_ms": t_gemm, "unitary_build_and_pack_ms": t_build,
+                     "other_engine": other, "other_ms": t_other, "speedup": t_other / t_gemm,
+                     "max_abs_diff": float((a - b).abs().max()), "auto_picks_gemm": True}
+    return out
+
+
 def large_state_throughput(n=20, L=2, batch=16, tile_bits=12, low_bits=3, register_engine=True):
     """K5: gates/s of the pass engine on `batch` n-qubit states (config 4 shape: 16 clients x 20 qubits)."""
     from .ops.large import LargeVQC, expvals_z
@@ -192,6 +215,7 @@ def aux_measurements(args=None, rank=0, world=1, local=0, skip=None):
     out["agg_1e8_clip"] = aggregation_latency(4, 25_000_000, sigma=0.0, iters=10)
     out["agg_1e8_weights"] = aggregation_latency(4, 25_000_000, mode="weights", clip=0.0, sigma=0.0, iters=10)
     out["unitary_gemm_8q"] = unitary_gemm_throughput(8, 6, 1 << 15)
+    out["unitary_gemm_vs_engines"] = unitary_gemm_vs_engines()
     out["sv20_pass_engine"] = large_state_throughput(20, 2, 16)
     return out
 

@@ -630,6 +630,194 @@ sv_global_swap_fused_kernel(const SwapArgs a) {
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Adjoint differentiation on the pass engine (K4a for states that do not fit in registers; the "adjoint" option of
+// /root/reference/ROADMAP.md:23,27 next to the parameter-shift rule).  After the forward passes, lambda = O psi with
+// O = sum_q cot_q Z-string_q (diagonal, sv_large_parity_obs_kernel); then the passes are walked BACKWARDS with both
+// states in shared memory: at every parametrised gate R(theta) = exp(-i theta P / 2) the gradient is Im <lambda|P|psi>
+// taken just after the gate, after which R^dagger is applied to both states.  One forward and one backward sweep
+// replace the 2P shifted circuits of the shift rule.
+struct ObsArgs { unsigned long long m[32]; };
+__global__ void __launch_bounds__(256)
+sv_large_parity_obs_kernel(const float2* __restrict__ psi, float2* __restrict__ lam, int n_local, int n_out,
+                           const ObsArgs masks, const float* __restrict__ cot /*[batch][n_out]*/) {
+    const int batch = blockIdx.y;
+    const size_t N = (size_t)1 << n_local;
+    const float2* p = psi + ((size_t)batch << n_local);
+    float2* l = lam + ((size_t)batch << n_local);
+    float c[32];
+#pragma unroll
+    for (int q = 0; q < 32; ++q) c[q] = q < n_out ? cot[(size_t)batch * n_out + q] : 0.f;
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < N; i += (size_t)gridDim.x * 256) {
+        float w = 0.f;
+#pragma unroll
+        for (int q = 0; q < 32; ++q)
+            if (q < n_out) w += (__popcll(i & masks.m[q]) & 1) ? -c[q] : c[q];
+        const float2 v = p[i];
+        l[i] = make_float2(w * v.x, w * v.y);
+    }
+}
+
+struct AdjArgs {
+    PassArgs base;             // states = psi; ops / theta / angles as in the forward pass
+    float2* lam;               // [batch][2^n]
+    float* grad;               // [theta_rows][n_params], accumulated with atomics
+};
+
+__device__ __forceinline__ float block_sum_256(float v, float* red /*[8]*/) {
+    v = warp_sum(v);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float t = 0.f;
+    if (threadIdx.x < 8) t = red[threadIdx.x];
+    if (threadIdx.x < 32) t = group_sum<8>(t);
+    return t;   // valid on thread 0
+}
+// apply the 2x2 matrix m to the pairs (j0, j1 = j0 | 1 << b) of BOTH tiles
+__device__ __forceinline__ void apply_pair_both(float2* psi, float2* lam, int tile_n, int b, float2 m00, float2 m01,
+                                                float2 m10, float2 m11) {
+    for (int idx = threadIdx.x; idx < (tile_n >> 1); idx += PASS_THREADS) {
+        const int j0 = ((idx >> b) << (b + 1)) | (idx & ((1 << b) - 1)), j1 = j0 | (1 << b);
+        const float2 p0 = psi[j0], p1 = psi[j1], l0 = lam[j0], l1 = lam[j1];
+        psi[j0] = cmul2(m00, p0, m01, p1); psi[j1] = cmul2(m10, p0, m11, p1);
+        lam[j0] = cmul2(m00, l0, m01, l1); lam[j1] = cmul2(m10, l0, m11, l1);
+    }
+}
+// Im <lambda| P |psi> over this tile for P = X (0), Y (1), Z (2) on tile bit b (partial sum of this thread)
+__device__ __forceinline__ float pauli_im(const float2* psi, const float2* lam, int tile_n, int b, int pauli) {
+    float acc = 0.f;
+    for (int idx = threadIdx.x; idx < (tile_n >> 1); idx += PASS_THREADS) {
+        const int j0 = ((idx >> b) << (b + 1)) | (idx & ((1 << b) - 1)), j1 = j0 | (1 << b);
+        const float2 p0 = psi[j0], p1 = psi[j1], l0 = lam[j0], l1 = lam[j1];
+        // Im(conj(l) * v) = l.x v.y - l.y v.x
+        if (pauli == 0) acc += (l0.x * p1.y - l0.y * p1.x) + (l1.x * p0.y - l1.y * p0.x);
+        else if (pauli == 1) acc += -(l0.x * p1.x + l0.y * p1.y) + (l1.x * p0.x + l1.y * p0.y);   // Y psi = (-i p1, i p0)
+        else acc += (l0.x * p0.y - l0.y * p0.x) - (l1.x * p1.y - l1.y * p1.x);
+    }
+    return acc;
+}
+
+__global__ void __launch_bounds__(PASS_THREADS)
+sv_large_adjoint_pass_kernel(const AdjArgs A) {
+    const PassArgs& a = A.base;
+    extern __shared__ __align__(16) float2 tiles[];        // psi [2^T] | lambda [2^T]
+    __shared__ float trig[MAX_OPS_PER_PASS][4];            // cos, sin of param 0 / param 1 (half angles)
+    __shared__ int sops[MAX_OPS_PER_PASS][5];
+    __shared__ float red[8];
+    const int tid = threadIdx.x, batch = blockIdx.y;
+    const int T = a.tile_bits, tile_n = 1 << T;
+    float2* psi = tiles;
+    float2* lam = tiles + tile_n;
+    float2* st = a.states + ((size_t)batch << a.n_qubits);
+    float2* sl = A.lam + ((size_t)batch << a.n_qubits);
+    const float* th = a.theta ? a.theta + (size_t)(batch % a.theta_rows) * a.n_params : nullptr;
+    float* grad = A.grad + (size_t)(batch % a.theta_rows) * a.n_params;
+    for (int i = tid; i < a.n_ops; i += PASS_THREADS) {
+        const int* op = a.ops + 5 * i;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) sops[i][k] = op[k];
+        float s0 = 0.f, c0 = 1.f, s1 = 0.f, c1 = 1.f;
+        const int kind = op[0];
+        if (kind == QFX_GATE_RX || kind == QFX_GATE_RY || kind == QFX_GATE_RZ || kind == QFX_GATE_RXRZ) sincosf(0.5f * th[op[3]], &s0, &c0);
+        if (kind == QFX_GATE_RXRZ) sincosf(0.5f * th[op[4]], &s1, &c1);
+        if (kind == QFX_GATE_RY_FEATURE) sincosf(0.5f * a.angles[(size_t)(batch % a.angle_rows) * a.n_feature + op[3]], &s0, &c0);
+        trig[i][0] = c0; trig[i][1] = s0; trig[i][2] = c1; trig[i][3] = s1;
+    }
+    const unsigned long long base = tile_base(a, blockIdx.x);
+    const int low = a.low_bits, chunk = 1 << low;
+    for (int j0 = tid; j0 < tile_n; j0 += PASS_THREADS) {
+        const int jl = j0 & (chunk - 1), jh = j0 >> low;
+        unsigned long long off = base | (unsigned long long)jl;
+        for (int b = low; b < T; ++b) off |= (unsigned long long)((jh >> (b - low)) & 1) << a.tile_q[b];
+        psi[j0] = st[off];
+        lam[j0] = sl[off];
+    }
+    __syncthreads();
+    const float2 zero = make_float2(0.f, 0.f);
+    for (int i = a.n_ops - 1; i >= 0; --i) {
+        const int kind = sops[i][0], b0 = sops[i][1], b1 = sops[i][2];
+        const float c = trig[i][0], s = trig[i][1], cp = trig[i][2], sp = trig[i][3];
+        if (kind == QFX_GATE_CNOT || kind == QFX_GATE_CZ) {         // self-inverse: the same move on both states
+            for (int idx = tid; idx < (tile_n >> 2); idx += PASS_THREADS) {
+                const int lo = min(b0, b1), hi = max(b0, b1);
+                int j = idx;
+                j = ((j >> lo) << (lo + 1)) | (j & ((1 << lo) - 1));
+                j = ((j >> hi) << (hi + 1)) | (j & ((1 << hi) - 1));
+                if (kind == QFX_GATE_CNOT) {
+                    const int ja = j | (1 << b0), jb = ja | (1 << b1);
+                    float2 t = psi[ja]; psi[ja] = psi[jb]; psi[jb] = t;
+                    t = lam[ja]; lam[ja] = lam[jb]; lam[jb] = t;
+                } else {
+                    j |= (1 << b0) | (1 << b1);
+                    psi[j] = make_float2(-psi[j].x, -psi[j].y);
+                    lam[j] = make_float2(-lam[j].x, -lam[j].y);
+                }
+            }
+            __syncthreads();
+            continue;
+        }
+        if (kind == QFX_GATE_RXRZ) {
+            // the gate is RZ(phi) RX(theta): walking backwards meets RZ first
+            float g = block_sum_256(pauli_im(psi, lam, tile_n, b0, 2), red);
+            if (tid == 0) atomicAdd(grad + sops[i][4], g);
+            __syncthreads();
+            apply_pair_both(psi, lam, tile_n, b0, make_float2(cp, sp), zero, zero, make_float2(cp, -sp));   // RZ(phi)^dagger
+            __syncthreads();
+            g = block_sum_256(pauli_im(psi, lam, tile_n, b0, 0), red);
+            if (tid == 0) atomicAdd(grad + sops[i][3], g);
+            __syncthreads();
+            apply_pair_both(psi, lam, tile_n, b0, make_float2(c, 0.f), make_float2(0.f, s), make_float2(0.f, s), make_float2(c, 0.f));
+            __syncthreads();
+            continue;
+        }
+        if (kind == QFX_GATE_RX || kind == QFX_GATE_RY || kind == QFX_GATE_RZ) {
+            const int pauli = kind == QFX_GATE_RX ? 0 : (kind == QFX_GATE_RY ? 1 : 2);
+            const float g = block_sum_256(pauli_im(psi, lam, tile_n, b0, pauli), red);
+            if (tid == 0) atomicAdd(grad + sops[i][3], g);
+            __syncthreads();
+        }
+        // inverse rotation (RY_FEATURE carries no trainable parameter: it is only undone)
+        if (kind == QFX_GATE_RX) apply_pair_both(psi, lam, tile_n, b0, make_float2(c, 0.f), make_float2(0.f, s), make_float2(0.f, s), make_float2(c, 0.f));
+        else if (kind == QFX_GATE_RY || kind == QFX_GATE_RY_FEATURE)
+            apply_pair_both(psi, lam, tile_n, b0, make_float2(c, 0.f), make_float2(s, 0.f), make_float2(-s, 0.f), make_float2(c, 0.f));
+        else if (kind == QFX_GATE_RZ) apply_pair_both(psi, lam, tile_n, b0, make_float2(c, s), zero, zero, make_float2(c, -s));
+        __syncthreads();
+    }
+    for (int j0 = tid; j0 < tile_n; j0 += PASS_THREADS) {
+        const int jl = j0 & (chunk - 1), jh = j0 >> low;
+        unsigned long long off = base | (unsigned long long)jl;
+        for (int b = low; b < T; ++b) off |= (unsigned long long)((jh >> (b - low)) & 1) << a.tile_q[b];
+        st[off] = psi[j0];
+        sl[off] = lam[j0];
+    }
+}
+
+static int fill_pass_args(PassArgs& a, float* states, int n_qubits, int tile_bits, int low_bits, const int* tile_qubits_host,
+                          const int* ops_dev, int n_ops, const float* theta, int theta_rows, int n_params,
+                          const float* angles, int angle_rows, int n_feature) {
+    QFX_ARG_CHECK(n_qubits >= 2 && n_qubits <= 34, QFX_ERR_UNSUPPORTED, "n_qubits %d not in 2..34", n_qubits);
+    QFX_ARG_CHECK(tile_bits >= 1 && tile_bits <= MAX_TILE_BITS && tile_bits <= n_qubits, QFX_ERR_BAD_ARG, "bad tile_bits %d", tile_bits);
+    QFX_ARG_CHECK(low_bits >= 0 && low_bits <= tile_bits, QFX_ERR_BAD_ARG, "bad low_bits");
+    QFX_ARG_CHECK(n_ops >= 0 && n_ops <= MAX_OPS_PER_PASS, QFX_ERR_TOO_LARGE, "pass has %d ops (max %d)", n_ops, MAX_OPS_PER_PASS);
+    a = PassArgs{};
+    a.states = reinterpret_cast<float2*>(states);
+    a.n_qubits = n_qubits; a.tile_bits = tile_bits; a.low_bits = low_bits;
+    unsigned long long in_tile = 0ull;
+    for (int b = 0; b < tile_bits; ++b) { a.tile_q[b] = tile_qubits_host[b]; in_tile |= 1ull << a.tile_q[b]; }
+    a.n_runs = 0;
+    for (int q = 0; q < n_qubits;) {
+        if ((in_tile >> q) & 1ull) { ++q; continue; }
+        int w = 0;
+        while (q + w < n_qubits && !((in_tile >> (q + w)) & 1ull)) ++w;
+        a.run_pos[a.n_runs] = q; a.run_width[a.n_runs] = w; ++a.n_runs;
+        q += w;
+    }
+    a.ops = ops_dev; a.n_ops = n_ops; a.theta = theta; a.theta_rows = theta_rows > 0 ? theta_rows : 1; a.n_params = n_params;
+    a.angles = angles; a.angle_rows = angle_rows > 0 ? angle_rows : 1; a.n_feature = n_feature;
+    return 0;
+}
+
 static int num_sms() { return device_sm_count(); }
 
 }  // namespace large
@@ -746,4 +934,43 @@ extern "C" int qfx_sv_global_swap_fused(const float* const* src_table, float* ds
     else if (g_bits == 2) sv_global_swap_fused_kernel<2><<<(unsigned)blocks, 256, 0, stream>>>(a);
     else sv_global_swap_fused_kernel<3><<<(unsigned)blocks, 256, 0, stream>>>(a);
     return check_launch("sv_global_swap_fused_kernel");
+}
+
+// lambda = (sum_q cot[b][q] * Z-string(masks[q])) psi: the start of the adjoint sweep (lam may not alias psi)
+extern "C" int qfx_sv_large_parity_obs(const float* psi, float* lam, int n_local, int n_out,
+                                       const unsigned long long* masks_host, const float* cot, int batch,
+                                       cudaStream_t stream) {
+    QFX_ARG_CHECK(psi && lam && cot && masks_host && n_local >= 1 && n_local <= 34 && n_out >= 1 && n_out <= 32 && batch >= 1 &&
+                  batch <= 65535, QFX_ERR_BAD_ARG, "bad arguments");
+    ObsArgs m = {};
+    for (int q = 0; q < n_out; ++q) m.m[q] = masks_host[q];
+    size_t blocks = (((size_t)1 << n_local) + 256 * 8 - 1) / (256 * 8);
+    const size_t cap = (size_t)num_sms() * 8 / (batch > 8 ? 8 : batch) + 1;
+    if (blocks > cap) blocks = cap;
+    sv_large_parity_obs_kernel<<<dim3((unsigned)blocks, batch), 256, 0, stream>>>(
+        reinterpret_cast<const float2*>(psi), reinterpret_cast<float2*>(lam), n_local, n_out, m, cot);
+    return check_launch("sv_large_parity_obs_kernel");
+}
+
+// One pass of the adjoint sweep: the ops of a compiled pass walked backwards over psi and lambda (both updated in
+// place to their values BEFORE the pass); d/d theta accumulates into grad [theta_rows][n_params] (caller-zeroed).
+extern "C" int qfx_sv_large_adjoint_pass(float* psi, float* lam, int n_qubits, int batch, int tile_bits, int low_bits,
+                                         const int* tile_qubits_host, const int* ops_dev, int n_ops, const float* theta,
+                                         int theta_rows, int n_params, const float* angles, int angle_rows, int n_feature,
+                                         float* grad, cudaStream_t stream) {
+    QFX_ARG_CHECK(psi && lam && grad && theta && batch >= 1 && batch <= 65535, QFX_ERR_BAD_ARG, "bad arguments");
+    AdjArgs A;
+    if (int e = fill_pass_args(A.base, psi, n_qubits, tile_bits, low_bits, tile_qubits_host, ops_dev, n_ops, theta, theta_rows,
+                               n_params, angles, angle_rows, n_feature)) return e;
+    A.lam = reinterpret_cast<float2*>(lam);
+    A.grad = grad;
+    const size_t smem = (sizeof(float2) << tile_bits) * 2;
+    static PerDeviceFlag attr;
+    if (!attr.here()) {
+        QFX_CUDA_TRY(cudaFuncSetAttribute(sv_large_adjoint_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024));
+        attr.here() = true;
+    }
+    dim3 grid(1u << (n_qubits - tile_bits), batch);
+    sv_large_adjoint_pass_kernel<<<grid, PASS_THREADS, smem, stream>>>(A);
+    return check_launch("sv_large_adjoint_pass_kernel");
 }

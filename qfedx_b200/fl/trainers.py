@@ -26,6 +26,15 @@ from .spsa import spsa_gradient
 OPTIMIZERS = {"sgd": 0, "adam": 1}
 
 
+def _check_labels(y: torch.Tensor, n_classes: int, what: str) -> None:
+    """The kernels index logits by label: anything outside [0, n_classes) is rejected up front (torch's losses raise
+    for the same input)."""
+    if y.numel():
+        lo, hi = int(y.min()), int(y.max())
+        if lo < 0 or hi >= max(2, n_classes):
+            raise _lib.QfxError(f"{what}: labels must lie in [0, {max(2, n_classes)}), found [{lo}, {hi}]")
+
+
 def make_optimizer(params, name: str, lr: float, momentum: float = 0.9, betas=(0.9, 0.999), eps: float = 1e-8):
     if name == "sgd":
         return torch.optim.SGD(params, lr=lr, momentum=momentum)
@@ -118,6 +127,7 @@ class VQCFusedTrainer:
                  generator=None, lane_mode: str = "latency", shuffle_mode: str = "feistel", seed: int = 0, noise=None):
         if model.encoding != "angle":
             raise ValueError("the fused trainer takes angle-encoded features")
+        _check_labels(data.y, model.num_classes, "client data")
         self.model, self.data = model, data
         self.epochs, self.batch_size, self.lr = epochs, batch_size, lr
         self.optimizer, self.momentum, self.betas, self.eps = optimizer, momentum, betas, eps
@@ -203,6 +213,7 @@ class VQCFusedTrainer:
         return out, {"train_stats": stats}
 
     def evaluate(self, global_flat: torch.Tensor, X: torch.Tensor, y: torch.Tensor, batch_size: int = 0):
+        _check_labels(y, self.model.num_classes, "evaluation data")
         if not self.cuda:
             return self._fallback.evaluate(global_flat, X, y)
         m = self.model

@@ -39,6 +39,9 @@ class PassBackend(_ExpvalBackend):
     def shift_grad(self, angles, theta, cot):
         return self.vqc.param_shift_grad(angles, theta, cot, self.max_states)
 
+    def adjoint_grad(self, angles, theta, cot):
+        return self.vqc.adjoint_grad(angles, theta, cot[:, : self.n_out] if self.n_out else cot)
+
 
 class ShardedBackend(_ExpvalBackend):
     """One circuit at a time, its state sharded over every rank of the job."""
@@ -124,6 +127,10 @@ class LargeVQCTrainer:
                     lp = self._loss_and_cot(self.backend.expvals(xb, theta + self.spsa_c * delta), a, b, yb)[0]
                     lm = self._loss_and_cot(self.backend.expvals(xb, theta - self.spsa_c * delta), a, b, yb)[0]
                     gth = (lp - lm) / (2 * self.spsa_c) * delta
+                elif self.grad_method == "adjoint":
+                    if not hasattr(self.backend, "adjoint_grad"):
+                        raise ValueError("adjoint differentiation is implemented for the pass engine (PassBackend)")
+                    gth = self.backend.adjoint_grad(xb, theta, cot)
                 else:
                     gth = self.backend.shift_grad(xb, theta, cot)
                 g = torch.cat([gth, ga, gb])
@@ -146,6 +153,15 @@ class LargeVQCTrainer:
     def evaluate(self, global_flat, X, y, batch_size: int = 64):
         P, C = self.model.n_angle_params, self.model.n_logits
         theta, a, b = global_flat[:P], global_flat[P:P + C], global_flat[P + C:]
+        from ..ops.unitary_gemm import UnitaryGemm, prefers_unitary_gemm
+        if X.is_cuda and isinstance(self.backend, PassBackend) and prefers_unitary_gemm(self.model.n_qubits,
+                                                                                          self.model.n_layers, len(X)):
+            # 11-12 qubits, a test set of hundreds of samples: one tcgen05 GEMM with the round's unitary (K2)
+            ug = UnitaryGemm(theta.reshape(1, self.model.n_layers, self.model.n_qubits, 2), self.model.entangler)
+            z = a * ug.expvals(X.float())[:, :C] + b
+            loss = F.binary_cross_entropy_with_logits(z[:, 0], y.float()) if C == 1 else F.cross_entropy(z, y)
+            pred = (z[:, 0] > 0).long() if C == 1 else z.argmax(1)
+            return float(loss), float((pred == y).float().mean())
         tot, correct = 0.0, 0
         for lo in range(0, len(X), batch_size):
             xb, yb = X[lo:lo + batch_size].float(), y[lo:lo + batch_size]

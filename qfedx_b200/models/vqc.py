@@ -73,6 +73,41 @@ class VQC(nn.Module):
         return F.cross_entropy(logits, y)
 
     @torch.no_grad()
-    def predict(self, x: torch.Tensor) -> torch.Tensor:
-        z = self.forward(x)
+    def inference_expvals(self, x: torch.Tensor, engine: str = "auto") -> torch.Tensor:
+        """<Z_q> [B, n] without autograd, on the fastest engine for the shape: the register kernel K1 (n <= 10), the
+        tcgen05 unitary GEMM K2 (11-12 qubits, or deep circuits over large batches: its cost does not grow with the
+        depth) or the pass engine K5 (n > 12).  ``engine`` forces 'registers' | 'gemm' | 'passes'."""
+        if not x.is_cuda or self.encoding != "angle":
+            return self.expvals(x)
+        from ..ops.unitary_gemm import MAX_QUBITS, UnitaryGemm, prefers_unitary_gemm
+        n, L, B = self.n_qubits, self.n_layers, x.shape[0]
+        if engine == "auto":
+            if prefers_unitary_gemm(n, L, B):
+                engine = "gemm"
+            else:
+                engine = "registers" if n <= _sv.MAX_REG_QUBITS else "passes"
+        if engine == "gemm":
+            key = (self.theta._version, self.theta.data_ptr(), self.entangler, self.basis)
+            if getattr(self, "_ug_key", None) != key:     # the packed unitary is rebuilt only when theta changed
+                self._ug = UnitaryGemm(self.theta.detach(), self.entangler, self.basis)
+                self._ug_key = key
+            return self._ug.expvals(x.float())
+        if engine == "passes":
+            from ..ops.large import LargeVQC
+            if getattr(self, "_large", None) is None:
+                self._large = LargeVQC(n, L, self.entangler)
+            return self._large.expvals(x.float(), self.theta.detach().reshape(1, -1), None)
+        return _sv.sv_forward(x, self.theta.detach(), None, self.basis, self.entangler)
+
+    @torch.no_grad()
+    def predict_logits(self, x: torch.Tensor, engine: str = "auto") -> torch.Tensor:
+        E = self.inference_expvals(x, engine)[:, : self.n_logits]
+        if self.noise is not None:
+            from ..noise import apply_to_expvals
+            E = apply_to_expvals(E, self.noise)
+        return self.readout_scale * E + self.readout_bias
+
+    @torch.no_grad()
+    def predict(self, x: torch.Tensor, engine: str = "auto") -> torch.Tensor:
+        z = self.predict_logits(x, engine)
         return (z[:, 0] > 0).long() if self.n_logits == 1 else z.argmax(1)

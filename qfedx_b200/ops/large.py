@@ -320,6 +320,39 @@ class LargeVQC:
                 grad[ps] = 0.5 * (val[:, 0] - val[:, 1])
         return grad
 
+    def adjoint_grad(self, angles: torch.Tensor, theta: torch.Tensor, cot: torch.Tensor) -> torch.Tensor:
+        """Same gradient as ``param_shift_grad`` by adjoint differentiation: one forward sweep, lambda = O psi, one
+        backward sweep over the compiled passes carrying psi and lambda (csrc/sv_large.cu: sv_large_adjoint_pass_kernel)
+        - a constant number of state sweeps instead of 2P shifted circuits.  theta [P] shared by the samples."""
+        n_out = cot.shape[1]
+        S, P, dev = angles.shape[0], self.n_params, angles.device
+        th = theta.reshape(1, P).contiguous().float()
+        if not angles.is_cuda:
+            t = th.detach().clone().requires_grad_(True)
+            E = ref.expval_z_all(ref.vqc_state_ref(angles, t.reshape(1, self.L, self.n, 2), None, "ry", self.entangler)).float()
+            return torch.autograd.grad((E[:, :n_out] * cot).sum(), t)[0].reshape(P)
+        ang = angles.contiguous().float()
+        psi = self.states(ang, th, before_final_ring=True)
+        lam = torch.empty_like(psi)
+        masks = (ctypes.c_ulonglong * n_out)(*[int(m) for m in self.readout_masks[:n_out]])
+        _lib.call("qfx_sv_large_parity_obs", _lib.ptr(torch.view_as_real(psi)), _lib.ptr(torch.view_as_real(lam)),
+                  _lib.c_int(self.n), _lib.c_int(n_out), masks, _lib.ptr(cot.contiguous().float()), _lib.c_int(S),
+                  _lib.stream_ptr())
+        grad = torch.zeros(1, P, device=dev)
+        for p in reversed(self.readout_passes):
+            if p.ops_dev is None or p.ops_dev.device != dev:
+                p.ops_dev = torch.as_tensor(p.ops, device=dev).contiguous()
+            T = len(p.tile_qubits)
+            tq = np.ascontiguousarray(p.tile_qubits, dtype=np.int32)
+            low = 0
+            while low < min(self.low_bits, T) and tq[low] == low:
+                low += 1
+            _lib.call("qfx_sv_large_adjoint_pass", _lib.ptr(torch.view_as_real(psi)), _lib.ptr(torch.view_as_real(lam)),
+                      _lib.c_int(self.n), _lib.c_int(S), _lib.c_int(T), _lib.c_int(low), tq.ctypes.data_as(ctypes.c_void_p),
+                      _lib.ptr(p.ops_dev), _lib.c_int(len(p.ops)), _lib.ptr(th), _lib.c_int(1), _lib.c_int(P), _lib.ptr(ang),
+                      _lib.c_int(S), _lib.c_int(ang.shape[1]), _lib.ptr(grad), _lib.stream_ptr())
+        return grad.reshape(P)
+
     def _first_pass_of_param(self) -> dict:
         """parameter index -> index of the (only) readout pass whose gates use it."""
         if getattr(self, "_param_pass", None) is None:

@@ -9,18 +9,36 @@ from __future__ import annotations
 import torch
 
 from . import _lib, ref
-from .statevector import BASIS, sv_forward
+from .statevector import BASIS, MAX_REG_QUBITS, sv_forward
 
 MIN_QUBITS, MAX_QUBITS = 6, 12
 
 
 def ansatz_unitary_t(theta: torch.Tensor, entangler: str = "cnot") -> torch.Tensor:
-    """U^T as complex64 [2^n, 2^n]: row b is U|b> (computed by K1 on the 2^n basis states)."""
+    """U^T as complex64 [2^n, 2^n]: row b is U|b> - the 2^n basis states pushed through the ansatz by the register
+    kernel K1 (n <= 10) or, for 11 and 12 qubits where no register kernel exists, by the pass engine K5."""
     theta = theta if theta.dim() == 4 else theta[None]
-    n = theta.shape[2]
-    eye = torch.eye(1 << n, device=theta.device, dtype=torch.float32)
-    _, psi = sv_forward(None, theta, None, "ry", entangler, init_state=eye, want_state=True)
+    L, n = theta.shape[1], theta.shape[2]
+    if n <= MAX_REG_QUBITS:
+        eye = torch.eye(1 << n, device=theta.device, dtype=torch.float32)
+        _, psi = sv_forward(None, theta, None, "ry", entangler, init_state=eye, want_state=True)
+        return psi
+    from .large import ansatz_gates, compile_passes, run_passes
+    psi = torch.eye(1 << n, device=theta.device, dtype=torch.complex64)
+    passes = compile_passes(n, ansatz_gates(n, L, entangler, feature_map=False))
+    run_passes(psi, n, passes, theta.reshape(1, -1).contiguous().float(), None)
     return psi
+
+
+def prefers_unitary_gemm(n_qubits: int, n_layers: int, batch: int) -> bool:
+    """Where K2 is the faster inference engine (measured on B200, bench aux `unitary_gemm_*`): its cost does not depend
+    on the circuit depth, the register kernel's grows linearly with it, and for 11-12 qubits the alternative is the
+    pass engine, which streams every state through HBM once per pass."""
+    if not (MIN_QUBITS <= n_qubits <= MAX_QUBITS):
+        return False
+    if n_qubits > MAX_REG_QUBITS:
+        return batch >= 256
+    return batch >= 4096 and n_qubits >= 8 and n_layers >= (12 if n_qubits >= 10 else 10)
 
 
 class UnitaryGemm:

@@ -1,7 +1,12 @@
 #!/bin/bash
-# ncu captures of the headline kernels at their benchmark shapes (one GPU); the raw CSV comes back in
-# gpurun_out/ and is summarised into profiles/ (see profiles/README.md).
+# ncu captures of the headline kernels (one GPU; never under a multi-rank launcher).  The plain run must exit 0 first.
+# Raw CSV pages come back in gpurun_out/; scripts/summarise_ncu.py condenses them into profiles/.
 mkdir -p gpurun_out
-timeout 600 python scripts/profile_kernels.py all > gpurun_out/plain_prof.log 2>&1 && \
-timeout 1500 ncu --set full --clock-control none -k regex:'sv_forward_kernel|sv_adjoint_kernel|unitary_gemm_kernel|fedavg_fused_kernel|sv_large_pass_kernel|sv_global_swap_fused_kernel|pack_product' -c 30 -o /tmp/prof_kernels python scripts/profile_kernels.py all > gpurun_out/ncu_kernels.log 2>&1; echo "ncu rc=$?"; tail -2 gpurun_out/ncu_kernels.log | cut -c1-200
-ncu -i /tmp/prof_kernels.ncu-rep --page raw --csv > gpurun_out/prof_kernels_raw.csv 2>/dev/null; ls -la /tmp/prof_kernels.ncu-rep gpurun_out/prof_kernels_raw.csv
+WHICH=${1:-all}
+KREGEX='sv_forward_kernel|sv_adjoint_kernel|unitary_gemm_kernel|fedavg_fused_kernel|fedavg_fused_loopback_kernel|sv_large_pass|sv_large_adjoint|sv_large_parity|sv_large_expz|sv_global_swap_fused_kernel|pack_product|tinycnn_round_kernel|tinycnn_eval_conv_kernel|head_eval|vqc_local_train_kernel'
+timeout 600 python scripts/profile_kernels.py $WHICH > gpurun_out/plain_prof.log 2>&1 && \
+timeout 2400 ncu --set full --clock-control none --import-source on -k regex:"$KREGEX" -c 60 -o /tmp/prof_kernels python scripts/profile_kernels.py $WHICH > gpurun_out/ncu_kernels.log 2>&1
+echo "ncu rc=$?"; tail -2 gpurun_out/ncu_kernels.log | cut -c1-200
+ncu -i /tmp/prof_kernels.ncu-rep --page raw --csv > gpurun_out/prof_kernels_raw.csv 2>/dev/null
+cp /tmp/prof_kernels.ncu-rep gpurun_out/ 2>/dev/null
+ls -la gpurun_out/prof_kernels.ncu-rep gpurun_out/prof_kernels_raw.csv

@@ -15,7 +15,12 @@ COLS = [("time", "gpu__time_duration.sum"), ("grid", "launch__grid_size"), ("blo
         ("alu_pct", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"),
         ("xu_pct", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active"),
         ("issue_pct", "sm__inst_issued.avg.pct_of_peak_sustained_active"), ("inst", "smsp__inst_executed.sum"),
-        ("l2_hit", "lts__t_sector_hit_rate.pct")]
+        ("l2_hit", "lts__t_sector_hit_rate.pct"),
+        ("tensor_pct", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active"),
+        ("tensor_subpipe_hmma_pct", "sm__inst_executed_pipe_tensor_subpipe_hmma.avg.pct_of_peak_sustained_active"),
+        ("tensor_mem_pct", "sm__mem_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed"),
+        ("smem_bytes", "launch__shared_mem_per_block_dynamic"),
+        ("nvlink_rx", "nvlrx__bytes.sum"), ("nvlink_tx", "nvltx__bytes.sum")]
 
 
 def main():

@@ -167,3 +167,43 @@ def test_param_shift_prefix_sharing_multi_pass():
         d = vqc.expvals(ang, tp.reshape(1, -1), 3) - vqc.expvals(ang, tm.reshape(1, -1), 3)
         assert float(grad[p]) == pytest.approx(0.5 * float((d * cot).sum()), abs=3e-4)
     assert float(grad[2 * n + 1]) == 0.0
+
+
+@pytest.mark.parametrize("n,L,S,n_out,tile,ent", [(10, 2, 4, 10, 12, "cnot"), (10, 3, 3, 2, 6, "cnot"), (14, 2, 2, 3, 12, "cnot"),
+                                                (13, 2, 2, 1, 12, "cz"), (20, 2, 2, 1, 12, "cnot")])
+def test_adjoint_on_the_pass_engine_matches_the_other_gradients(n, L, S, n_out, tile, ent):
+    """One forward + one backward sweep over the compiled passes gives the gradient of the shift rule (and, where a
+    register kernel exists, of K4a)."""
+    from qfedx_b200.ops.large import LargeVQC
+    g = torch.Generator().manual_seed(100 + n)
+    ang = (torch.rand(S, n, generator=g) * math.pi).cuda()
+    theta = torch.randn(L * n * 2, generator=g).cuda()
+    cot = torch.randn(S, n_out, generator=g).cuda()
+    vqc = LargeVQC(n, L, entangler=ent, tile_bits=tile)
+    gadj = vqc.adjoint_grad(ang, theta, cot)
+    gshift = vqc.param_shift_grad(ang, theta, cot, max_states=64)
+    np.testing.assert_allclose(gadj.cpu().numpy(), gshift.cpu().numpy(), atol=3e-4)
+    assert float(gadj.abs().max()) > 1e-3
+    if n <= 10:
+        full = torch.zeros(S, n, device="cuda")
+        full[:, :n_out] = cot
+        greg, _ = svop.sv_backward(ang, theta.reshape(1, L, n, 2), full, entangler=ent)
+        np.testing.assert_allclose(gadj.cpu().numpy(), greg.reshape(-1).cpu().numpy(), atol=3e-4)
+
+
+def test_large_vqc_trainer_with_adjoint_gradients_matches_param_shift_training():
+    from qfedx_b200.fl import FederatedDataset
+    from qfedx_b200.fl.trainers_large import LargeVQCTrainer, PassBackend
+    from qfedx_b200.models import VQC
+    n, L = 12, 2
+    g = torch.Generator().manual_seed(3)
+    clients = [((torch.rand(6, n, generator=g) * math.pi), torch.randint(0, 2, (6,), generator=g)) for _ in range(2)]
+    data = FederatedDataset.from_clients(clients, "cuda")
+    torch.manual_seed(0)
+    model = VQC(n, L, 2).cuda()
+    outs = {}
+    for method in ("param_shift", "adjoint"):
+        gen = torch.Generator(device="cuda").manual_seed(7)
+        tr = LargeVQCTrainer(model, data, PassBackend(n, L), epochs=1, batch_size=3, lr=0.05, grad_method=method, generator=gen)
+        outs[method], _ = tr.train(tr.global_flat(), [0, 1], 0)
+    np.testing.assert_allclose(outs["adjoint"].cpu().numpy(), outs["param_shift"].cpu().numpy(), atol=2e-3)
