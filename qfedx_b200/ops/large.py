@@ -351,7 +351,13 @@ class LargeVQC:
                       _lib.c_int(self.n), _lib.c_int(S), _lib.c_int(T), _lib.c_int(low), tq.ctypes.data_as(ctypes.c_void_p),
                       _lib.ptr(p.ops_dev), _lib.c_int(len(p.ops)), _lib.ptr(th), _lib.c_int(1), _lib.c_int(P), _lib.ptr(ang),
                       _lib.c_int(S), _lib.c_int(ang.shape[1]), _lib.ptr(grad), _lib.stream_ptr())
-        return grad.reshape(P)
+        grad = grad.reshape(P)
+        if self.L > 0:
+            # the last layer's RZ angles cannot move a Z-basis readout (see param_shift_grad): their gradient is exactly 0;
+            # the sweep returns rounding noise there, which Adam would normalise into full-size steps
+            last_rz = torch.tensor([(self.L - 1) * self.n * 2 + 2 * q + 1 for q in range(self.n)], device=dev)
+            grad[last_rz] = 0.0
+        return grad
 
     def _first_pass_of_param(self) -> dict:
         """parameter index -> index of the (only) readout pass whose gates use it."""
