@@ -154,8 +154,9 @@ int qfx_enable_peer(int dev, int peer);
 
 /* K7 across GPUs with an explicit exchange algorithm.  two_shot 0: every rank pushes its partial sum into every peer's
  * slot and reduces W slots locally (one cross-GPU barrier; recv_slots: world x dim 64-bit words per rank) - the choice for
- * latency-bound vectors.  two_shot 1: partials stay local, rank r pulls slice r of every peer's partial, reduces and
- * updates it, then every rank gathers the other slices by peer loads (two barriers; recv_slots: 2 x dim words per rank):
+ * latency-bound vectors.  two_shot 1: reduce-scatter by peer stores during the sweep over the client rows (slice o of the
+ * partial goes straight into rank o's buffer), local reduce + update of the own slice, then every rank gathers the other
+ * slices by peer loads (two barriers; recv_slots: (world + 1) * (ceil(dim / world) rounded up to 4) words per rank):
  * 2 (W-1)/W D instead of (W-1) D words over NVLink per rank.  pair_keys nullable; flags >= 32 words per rank. */
 int qfx_fedavg_fused_multi_ex(const float* client_params, const float* global_in, float* global_out,
                               const float* weights, const int* participate, const int* client_gids,

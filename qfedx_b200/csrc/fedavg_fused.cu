@@ -55,9 +55,11 @@ struct AggArgs {
     unsigned int* const* flags;    // [world] device pointers: flags[r] = rank r's flag array [world]
     unsigned int epoch;            // value written into flags this round (monotonic)
     int two_shot;                  // 0: every rank pushes its partial to every peer and reduces W slots locally (one
-                                   //    barrier; best for latency-bound sizes).  1: partials stay local, rank r pulls slice r
-                                   //    of every peer's partial, reduces and updates it, then every rank gathers the other
-                                   //    slices (two barriers, 2 (W-1)/W D words over NVLink per rank instead of (W-1) D)
+                                   //    barrier; best for latency-bound sizes).  1: reduce-scatter by peer stores during the
+                                   //    sweep over the client rows (slice o of the partial goes straight into rank o's
+                                   //    buffer), local reduce + update of the own slice, then every rank gathers the other
+                                   //    slices by peer loads (two barriers, 2 (W-1)/W D words over NVLink per rank
+                                   //    instead of (W-1) D; buffer: (W + 1) * ceil(D / W) words per rank)
 };
 
 __device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
@@ -319,9 +321,13 @@ __device__ __forceinline__ void fedavg_fused_body(const AggArgs& a, const int ma
                 IO::st(a.global_out + d, o);
             } else {
                 if (a.two_shot) {
-                    // keep the partial here (region 0 of this rank's symmetric buffer); peers pull their slice of it
-                    if constexpr (FIXED) IO::st(a.recv_slots[a.rank] + d, iacc[u]);
-                    else IO::st(reinterpret_cast<float*>(a.recv_slots[a.rank]) + d, facc[u]);
+                    // reduce-scatter by peer stores, overlapped with this sweep over the client rows: vector v belongs to
+                    // rank o = v / chunk, whose buffer holds one row per source rank: [W][chunk] vectors (region 0)
+                    const int chunk = (nvec + a.world - 1) / a.world;
+                    const int o = vi[u] / chunk;
+                    const size_t slot = ((size_t)a.rank * chunk + (size_t)(vi[u] - o * chunk)) * VEC;
+                    if constexpr (FIXED) IO::st(a.recv_slots[o] + slot, iacc[u]);
+                    else IO::st(reinterpret_cast<float*>(a.recv_slots[o]) + slot, facc[u]);
                 } else {
                     // push this rank's partial into slot [rank] of every rank (self included)
                     for (int r = 0; r < a.world; ++r) {
@@ -344,12 +350,13 @@ __device__ __forceinline__ void fedavg_fused_body(const AggArgs& a, const int ma
     }
     grid.sync();
     if (a.two_shot) {
-        // ---- reduce-scatter by peer loads: this rank owns vectors [lo, hi) ------------------------------
+        // ---- the W partial rows of this rank's slice [lo, hi) arrived by peer stores: reduce them locally --------
         const int chunk = (nvec + a.world - 1) / a.world;
         const int lo = min(nvec, a.rank * chunk), hi = min(nvec, lo + chunk);
-        float* result = reinterpret_cast<float*>(a.recv_slots[a.rank] + a.dim);    // region 1: the updated slice
+        const size_t row_words = (size_t)chunk * VEC;
+        float* result = reinterpret_cast<float*>(a.recv_slots[a.rank] + (size_t)a.world * row_words);   // region 1
         for (int v = lo + g0; v < hi; v += gstride) {
-            const size_t d = (size_t)v * VEC;
+            const size_t d = (size_t)v * VEC, loc = (size_t)(v - lo) * VEC;
             float upd[VEC];
             if constexpr (FIXED) {
                 unsigned long long sacc[VEC];
@@ -357,7 +364,7 @@ __device__ __forceinline__ void fedavg_fused_body(const AggArgs& a, const int ma
                 for (int e = 0; e < VEC; ++e) sacc[e] = 0ull;
                 for (int r = 0; r < a.world; ++r) {
                     long long t[VEC];
-                    IO::ldcv(a.recv_slots[r] + d, t);
+                    IO::ldcv(a.recv_slots[a.rank] + (size_t)r * row_words + loc, t);
 #pragma unroll
                     for (int e = 0; e < VEC; ++e) sacc[e] += (unsigned long long)t[e];
                 }
@@ -368,7 +375,7 @@ __device__ __forceinline__ void fedavg_fused_body(const AggArgs& a, const int ma
                 for (int e = 0; e < VEC; ++e) upd[e] = 0.f;
                 for (int r = 0; r < a.world; ++r) {           // fixed rank order: the sum is the same on every run
                     float t[VEC];
-                    IO::ldcv(reinterpret_cast<const float*>(a.recv_slots[r]) + d, t);
+                    IO::ldcv(reinterpret_cast<const float*>(a.recv_slots[a.rank]) + (size_t)r * row_words + loc, t);
 #pragma unroll
                     for (int e = 0; e < VEC; ++e) upd[e] += t[e];
                 }
@@ -378,7 +385,7 @@ __device__ __forceinline__ void fedavg_fused_body(const AggArgs& a, const int ma
 #pragma unroll
             for (int e = 0; e < VEC; ++e) o[e] = (a.mode == 1) ? g[e] + a.server_lr * upd[e] : upd[e];
             IO::st(a.global_out + d, o);
-            IO::st(result + d, o);
+            IO::st(result + loc, o);
         }
         // ---- second barrier (its own flag words), then gather the other ranks' slices ---------------------
         __threadfence_system();
@@ -392,10 +399,10 @@ __device__ __forceinline__ void fedavg_fused_body(const AggArgs& a, const int ma
         for (int q = 1; q < a.world; ++q) {
             const int r = (a.rank + q) % a.world;             // start with the next rank: W ranks, W different targets
             const int rlo = min(nvec, r * chunk), rhi = min(nvec, rlo + chunk);
-            const float* src = reinterpret_cast<const float*>(a.recv_slots[r] + a.dim);
+            const float* src = reinterpret_cast<const float*>(a.recv_slots[r] + (size_t)a.world * row_words);
             for (int v = rlo + g0; v < rhi; v += gstride) {
                 float t[VEC];
-                IO::ldcv(src + (size_t)v * VEC, t);
+                IO::ldcv(src + (size_t)(v - rlo) * VEC, t);
                 IO::st(a.global_out + (size_t)v * VEC, t);
             }
         }
@@ -595,8 +602,9 @@ extern "C" int qfx_fedavg_fused_loopback(int world, const float* const* client_p
 }
 
 // qfx_fedavg_fused_multi with an explicit exchange algorithm: two_shot = 0 is the one-barrier all-gather of partials
-// (recv_slots: world x dim words per rank), two_shot = 1 the reduce-scatter + all-gather by peer loads (recv_slots: 2 x dim
-// words per rank: partial, updated slice) - (W-1) D versus 2 (W-1)/W D words over NVLink per rank.
+// (recv_slots: world x dim words per rank), two_shot = 1 the reduce-scatter by peer stores + all-gather by peer loads
+// (recv_slots: (world + 1) * (ceil(dim / world) rounded up to 4) words per rank) - (W-1) D versus 2 (W-1)/W D words over
+// NVLink per rank, the first half overlapped with the sweep over the client rows.
 // pair_keys may be null (masks from the job seed).  flags: at least 2 * 16 words per rank.
 extern "C" int qfx_fedavg_fused_multi_ex(const float* client_params, const float* global_in, float* global_out,
                                          const float* weights, const int* participate, const int* client_gids,

@@ -40,7 +40,8 @@ class MultiGpuAggregator:
         from .symm import SymmetricBuffer
         self.rank, self.world, self.dim, self.device = rank, world, dim, device
         self.two_shot = (dim >= two_shot_min_dim) if two_shot is None else bool(two_shot)
-        slot_bytes = (2 if self.two_shot else world) * dim * 8
+        chunk = ((dim + world - 1) // world + 3) // 4 * 4          # words per rank slice (covers the 4-wide vector path)
+        slot_bytes = ((world + 1) * chunk if self.two_shot else world * dim) * 8
         # two receive-slot sets (alternated by epoch parity) + flags
         self.slots = [SymmetricBuffer(slot_bytes, rank, world, device) for _ in range(2)]
         self.flags = SymmetricBuffer(256, rank, world, device)

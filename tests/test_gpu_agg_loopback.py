@@ -27,8 +27,9 @@ def loopback_aggregate(world, cp_all, glob, w, part, two_shot, epochs=2, pair_ke
     gids = [torch.tensor(rw, dtype=torch.int32, device=dev) for rw in rows]
     outs = [torch.empty(D, device=dev) for _ in range(world)]
     scratch = [torch.zeros(max(1, len(rw)), device=dev) for rw in rows]
-    n_slots = 2 if two_shot else world
-    slot_sets = [[torch.zeros(n_slots * D, dtype=torch.int64, device=dev) for _ in range(world)] for _ in range(2)]
+    chunk = ((D + world - 1) // world + 3) // 4 * 4
+    words = (world + 1) * chunk if two_shot else world * D
+    slot_sets = [[torch.zeros(words, dtype=torch.int64, device=dev) for _ in range(world)] for _ in range(2)]
     tables = [torch.tensor([s.data_ptr() for s in ss], dtype=torch.int64, device=dev) for ss in slot_sets]
     flags = [torch.zeros(64, dtype=torch.int32, device=dev) for _ in range(world)]
     ftab = torch.tensor([f.data_ptr() for f in flags], dtype=torch.int64, device=dev)

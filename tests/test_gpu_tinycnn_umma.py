@@ -1,4 +1,5 @@
-"""tcgen05 implicit-GEMM conv2 kernels vs torch fp32 on the same bf16-rounded operands."""
+"""tcgen05 implicit-GEMM conv2 kernels (single-bf16-operand variants of the graph engine) vs float64 torch ON THE CPU on
+the same bf16-rounded operands - not vs cuDNN, whose fp32 convolutions may run in TF32."""
 import ctypes
 
 import pytest
@@ -26,9 +27,10 @@ def test_conv2_forward_umma_matches_torch():
     _lib.call("qfx_tinycnn_conv2_fwd_umma", _lib.ptr(a1), _lib.ptr(w), _lib.ptr(b), _lib.c_int(n), _lib.ptr(a2),
               _lib.ptr(i2), _lib.ptr(scratch), _lib.stream_ptr())
     torch.cuda.synchronize()
-    conv = F.conv2d(_bf16(a1), _bf16(w), None, padding=2)
+    conv = F.conv2d(_bf16(a1).cpu().double(), _bf16(w).cpu().double(), None, padding=2)
     ref, idx = F.max_pool2d(conv, 2, return_indices=True)
-    ref = torch.relu(ref + b[None, :, None, None])
+    ref = torch.relu(ref + b.cpu().double()[None, :, None, None])
+    a2, i2 = a2.cpu().double(), i2.cpu()
     err = (a2 - ref).abs().max()
     assert float(err) < 2e-3, float(err)
     # argmax within the 2x2 window (0..3 = dy*2+dx); near-ties may legitimately differ
@@ -52,15 +54,17 @@ def test_conv2_backward_umma_matches_torch():
               _lib.stream_ptr())
     _lib.call("qfx_tinycnn_conv2_wgrad_umma", _lib.ptr(g2), _lib.ptr(a1), _lib.c_int(n), _lib.ptr(part), _lib.stream_ptr())
     torch.cuda.synchronize()
-    a1b = _bf16(a1).requires_grad_(True)
-    wb = _bf16(w).requires_grad_(True)
+    a1b = _bf16(a1).cpu().double().requires_grad_(True)        # float64 on the CPU: the reference has no TF32 in it
+    wb = _bf16(w).cpu().double().requires_grad_(True)
+    g2b = _bf16(g2).cpu().double()
+    da1, part, g2c = da1.cpu().double(), part.cpu().double(), g2.cpu().double()
     out = F.conv2d(a1b, wb, None, padding=2)
     # data gradient uses bf16(g2) x bf16(w); weight gradient bf16(g2) x bf16(a1)
-    (da_ref,) = torch.autograd.grad(out, a1b, _bf16(g2), retain_graph=True)
+    (da_ref,) = torch.autograd.grad(out, a1b, g2b, retain_graph=True)
     assert float((da1 - da_ref).abs().max()) < 5e-3 * float(da_ref.abs().max())
     for i in range(n):
         oi = F.conv2d(a1b[i:i + 1], wb, None, padding=2)
-        (dw_ref,) = torch.autograd.grad(oi, wb, _bf16(g2[i:i + 1]))
+        (dw_ref,) = torch.autograd.grad(oi, wb, g2b[i:i + 1])
         got = part[i, 416:416 + 12800].reshape(32, 16, 5, 5)
         assert float((got - dw_ref).abs().max()) < 5e-3 * float(dw_ref.abs().max()), i
-        assert torch.allclose(part[i, 13216:13248], g2[i].sum(dim=(1, 2)), atol=1e-4)
+        assert torch.allclose(part[i, 13216:13248], g2c[i].sum(dim=(1, 2)), atol=1e-4)
