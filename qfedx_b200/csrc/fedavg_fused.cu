@@ -237,6 +237,9 @@ __device__ __forceinline__ void fedavg_fused_body(const AggArgs& a, const int ma
     __syncthreads();
 
     // ---- phase 2: weighted, noised, masked sum per element -----------------------------------
+    // two-shot exchange: every rank starts its sweep at the slice of the NEXT rank, so that at any moment the W ranks
+    // push to W different owners instead of all hammering rank 0's links first
+    const int rot = (a.world > 1 && a.two_shot) ? min(nvec - 1, ((a.rank + 1) % a.world) * ((nvec + a.world - 1) / a.world)) : 0;
     for (int v0 = g0; v0 < nvec; v0 += UNR * gstride) {
         float g[UNR][VEC], facc[UNR][VEC];
         unsigned long long iacc[UNR][VEC];
@@ -244,6 +247,7 @@ __device__ __forceinline__ void fedavg_fused_body(const AggArgs& a, const int ma
 #pragma unroll
         for (int u = 0; u < UNR; ++u) {
             vi[u] = min(v0 + u * gstride, nvec - 1);
+            if (rot) { vi[u] += rot; if (vi[u] >= nvec) vi[u] -= nvec; }
             IO::ld(a.global_in + (size_t)vi[u] * VEC, g[u]);
 #pragma unroll
             for (int e = 0; e < VEC; ++e) {

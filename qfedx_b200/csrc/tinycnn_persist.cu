@@ -36,8 +36,10 @@ constexpr int PNT_ALL = PNT + 32;             // + one warp whose lane 0 only is
 #define WSYNC() asm volatile("bar.sync 1, 512;" ::: "memory")
 constexpr int PPLANE = 352 * 16;              // bytes per half plane: 18 rows x 16 pixels x 16 B + zero slack
 constexpr int WOP = 25600;                    // bytes of one bf16 operand copy of the conv2 weights
-constexpr int OFF_A1 = 128;                   // [hi0 hi1 lo0 lo1] activation planes (behind 128 B of zeros)
-constexpr int OFF_G2 = OFF_A1 + 4 * PPLANE;   // [hi0..3 lo0..3] conv2-output-gradient planes
+constexpr int OFF_A1 = 128;                   // [hi0 hi1 lo0 lo1] activation planes (behind 128 B of zeros), set 0
+constexpr int OFF_A1B = OFF_A1 + 4 * PPLANE;  // set 1: PA double-buffers the planes so conv1 of the next image runs
+                                              // on the CUDA cores while the tensor core works on the previous one
+constexpr int OFF_G2 = OFF_A1B + 4 * PPLANE;  // [hi0..3 lo0..3] conv2-output-gradient planes
 constexpr int OFF_WF = OFF_G2 + 8 * PPLANE;   // forward operand hi | lo; scratch of PB / PC / PD once consumed
 constexpr int OFF_WB = OFF_WF + 2 * WOP;      // data-gradient operand hi | lo
 constexpr int OFF_X32 = OFF_WB + 2 * WOP;     // input image, 32 x 32 with a 2-pixel zero border (conv1 forward)
@@ -51,8 +53,8 @@ static_assert(PSMEM <= 227 * 1024, "shared memory");
 constexpr int FCX = 116;                      // row stride of the fc1 forward tiles (16-byte aligned rows)
 static_assert((32 + 64) * FCX * 4 <= 2 * WOP, "PB tiles");
 // TMEM columns.  Forward (PA) and backward (PD) accumulators are never live together and share columns:
-// forward 2 blocks x 64 (hi | lo weight halves); data gradient 2 x 32; weight gradient 10 x 40 behind it.
-constexpr int TM_FWD = 0, TM_DG = 0, TM_WG = 64, WG_N = 40;
+// forward 2 image buffers x 2 blocks x 64 (hi | lo weight halves); data gradient 2 x 32; weight gradient 10 x 40 behind it.
+constexpr int TM_FWD = 0, TM_FWD_SET = 128, TM_DG = 0, TM_WG = 64, WG_N = 40;
 static_assert(TM_WG + 10 * WG_N <= 512, "TMEM columns");
 constexpr int XS1P = 37;
 
@@ -143,7 +145,8 @@ __device__ __forceinline__ void store_wop(__nv_bfloat16* wo, int o, int c, int t
 // PA, first half: conv1 (5x5, 1 -> 16, pad 2) + bias + ReLU + 2x2 max-pool of the image in xs32.  Thread
 // (half, position) computes 8 channels of one pooled position and writes them straight into the bf16 hi/lo planes
 // (16 bytes per pixel and half plane); the fp32 activation and the arg-max / sign byte go to global memory for PD.
-__device__ __forceinline__ void conv1_to_planes(uint8_t* smem, float* __restrict__ a1g, unsigned char* __restrict__ i1g) {
+__device__ __forceinline__ void conv1_to_planes(uint8_t* smem, float* __restrict__ a1g, unsigned char* __restrict__ i1g,
+                                                int planes_off = OFF_A1) {
     const int tid = threadIdx.x;
     if (tid >= 392) return;
     const float* xs = reinterpret_cast<const float*>(smem + OFF_X32);
@@ -180,8 +183,8 @@ __device__ __forceinline__ void conv1_to_planes(uint8_t* smem, float* __restrict
     uint4 hi, lo;
     pack8_hi_lo(v8, hi, lo);
     const int slot = (py + 2) * 16 + px;
-    *reinterpret_cast<uint4*>(smem + OFF_A1 + half * PPLANE + slot * 16) = hi;
-    *reinterpret_cast<uint4*>(smem + OFF_A1 + (2 + half) * PPLANE + slot * 16) = lo;
+    *reinterpret_cast<uint4*>(smem + planes_off + half * PPLANE + slot * 16) = hi;
+    *reinterpret_cast<uint4*>(smem + planes_off + (2 + half) * PPLANE + slot * 16) = lo;
 }
 
 // activation planes of an image from its fp32 copy in global memory (PD, when the CTA owns several images)
@@ -201,20 +204,26 @@ __device__ __forceinline__ void rebuild_a1_planes(uint8_t* smem, const float* a1
 
 // one thread: conv2 forward, D[pixel slot, (hi|lo, oc)] += sum over taps A_tap[pixel slot, c] [W_hi | W_lo]_tap[oc, c]^T,
 // once for the hi and once for the lo activation planes (all four partial products; the epilogue adds the halves)
-__device__ __forceinline__ void issue_conv2_fwd(uint32_t sbase, uint32_t tmem) {
+template <bool ELECT = false>
+__device__ __forceinline__ void issue_conv2_fwd(uint32_t sbase, uint32_t tmem, int planes_off = OFF_A1) {
     constexpr uint32_t idesc = idesc_bf16(128, 64, 0, 0);
 #pragma unroll 1
     for (int blk = 0; blk < 2; ++blk) {
-#pragma unroll 1
+#pragma unroll 5
         for (int tap = 0; tap < 25; ++tap) {
             const int ky = tap / 5, kx = tap - ky * 5;
             // rows = 128 consecutive pixel slots; output slot p reads input slot p + ky*16 + kx - 2 (the two slots in front
             // of the first plane are zeros); 8-row groups 128 B apart, the second k-chunk (channels 8..15) one plane on
-            const uint32_t a_hi = sbase + OFF_A1 + (uint32_t)((128 * blk + ky * 16 + kx - 2) * 16);
+            const uint32_t a_hi = sbase + (uint32_t)planes_off + (uint32_t)((128 * blk + ky * 16 + kx - 2) * 16);
             const uint64_t ah = desc_noswz(a_hi, PPLANE, 128), al = desc_noswz(a_hi + 2 * PPLANE, PPLANE, 128);
             const uint64_t b = desc_noswz(sbase + OFF_WF + (uint32_t)tap * 2048, 1024, 128);
-            umma_bf16(tmem + TM_FWD + 64 * blk, al, b, idesc, tap > 0 ? 1u : 0u);
-            umma_bf16(tmem + TM_FWD + 64 * blk, ah, b, idesc, 1u);
+            if constexpr (ELECT) {
+                umma_bf16_elect(tmem + TM_FWD + 64 * blk, al, b, idesc, tap > 0 ? 1u : 0u);
+                umma_bf16_elect(tmem + TM_FWD + 64 * blk, ah, b, idesc, 1u);
+            } else {
+                umma_bf16(tmem + TM_FWD + 64 * blk, al, b, idesc, tap > 0 ? 1u : 0u);
+                umma_bf16(tmem + TM_FWD + 64 * blk, ah, b, idesc, 1u);
+            }
         }
     }
 }
@@ -278,11 +287,11 @@ __device__ __forceinline__ void build_g2_planes(uint8_t* smem, const float* __re
 
 // one thread: data gradient D[pixel slot, (hi|lo, c)] += sum_tap G_tap[pixel slot, oc] [Wflip_hi | Wflip_lo]_tap[c, oc]^T
 // (K = 32 oc = 2 MMAs), for the hi and the lo planes of g2
-__device__ __forceinline__ void issue_conv2_dgrad(uint32_t sbase, uint32_t tmem) {
+__device__ __forceinline__ void issue_conv2_dgrad(uint32_t sbase, uint32_t tmem) {   // convergent warp, one lane issues
     constexpr uint32_t idesc = idesc_bf16(128, 32, 0, 0);
 #pragma unroll 1
     for (int blk = 0; blk < 2; ++blk) {
-#pragma unroll 1
+#pragma unroll 5
         for (int tap = 0; tap < 25; ++tap) {
             const int ky = tap / 5, kx = tap - ky * 5;
 #pragma unroll
@@ -290,8 +299,8 @@ __device__ __forceinline__ void issue_conv2_dgrad(uint32_t sbase, uint32_t tmem)
                 const uint32_t a_hi = sbase + OFF_G2 + (uint32_t)(2 * j) * PPLANE + (uint32_t)((128 * blk + ky * 16 + kx - 2) * 16);
                 const uint64_t ah = desc_noswz(a_hi, PPLANE, 128), al = desc_noswz(a_hi + 4 * PPLANE, PPLANE, 128);
                 const uint64_t b = desc_noswz(sbase + OFF_WB + (uint32_t)tap * 2048 + (uint32_t)(2 * j) * 512, 512, 128);
-                umma_bf16(tmem + TM_DG + 32 * blk, al, b, idesc, (tap | j) ? 1u : 0u);
-                umma_bf16(tmem + TM_DG + 32 * blk, ah, b, idesc, 1u);
+                umma_bf16_elect(tmem + TM_DG + 32 * blk, al, b, idesc, (tap | j) ? 1u : 0u);
+                umma_bf16_elect(tmem + TM_DG + 32 * blk, ah, b, idesc, 1u);
             }
         }
     }
@@ -315,8 +324,8 @@ __device__ __forceinline__ void issue_conv2_wgrad(uint32_t sbase, uint32_t tmem,
         uint32_t b_l = (((sbase + OFF_A1 + (uint32_t)(2 + h) * PPLANE + (uint32_t)((16 * ky - 2) * 16)) >> 4) & 0x3FFF) | lbo_lo;
 #pragma unroll 2
         for (int kk = 0; kk < 14; ++kk) {
-            umma_bf16(acc, (a_hi_bits << 32) | a, (b_hi_bits << 32) | b_l, idesc, (accumulate || kk) ? 1u : 0u);
-            umma_bf16(acc, (a_hi_bits << 32) | a, (b_hi_bits << 32) | b_h, idesc, 1u);
+            umma_bf16_elect(acc, (a_hi_bits << 32) | a, (b_hi_bits << 32) | b_l, idesc, (accumulate || kk) ? 1u : 0u);
+            umma_bf16_elect(acc, (a_hi_bits << 32) | a, (b_hi_bits << 32) | b_h, idesc, 1u);
             a += 16; b_h += 16; b_l += 16;    // 16 pixel slots = 256 B
         }
     }
@@ -436,7 +445,7 @@ __device__ __forceinline__ void head_phase(const Step& s, int sel, int nb, int l
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(PNT_ALL, 1) tinycnn_round_kernel(const Round R) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ __align__(8) uint64_t bar_f, bar_d, bar_w, rdy_f, rdy_b;
+    __shared__ __align__(8) uint64_t bar_f[2], bar_d, bar_w, rdy_f[2], rdy_b;   // forward: one pair per image buffer
     __shared__ uint32_t tmem_slot;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int sel = blockIdx.y, cta = blockIdx.x, G = gridDim.x;
@@ -447,14 +456,15 @@ __global__ void __launch_bounds__(PNT_ALL, 1) tinycnn_round_kernel(const Round R
     const __nv_bfloat16* wop = R.wop + (size_t)sel * 4 * 12800;
     unsigned* bar = R.bar + sel;
     unsigned bar_target = 0;
-    uint32_t pf = 0, pd = 0, pw = 0;          // mbarrier phase parities
+    uint32_t pf[2] = {0, 0}, pd = 0, pw = 0;  // mbarrier phase parities
     long long t_mark = clock64();
 
     // ---- one-time set-up: zero planes and image borders, TMEM, mbarriers
     for (int i = tid * 16; i < OFF_WF; i += PNT_ALL * 16) *reinterpret_cast<uint4*>(smem + i) = make_uint4(0, 0, 0, 0);
     for (int i = OFF_X32 + tid * 16; i < OFF_W1C; i += PNT_ALL * 16) *reinterpret_cast<uint4*>(smem + i) = make_uint4(0, 0, 0, 0);
     if (warp == 1 && lane == 0) {
-        mbar_init1(&bar_f); mbar_init1(&bar_d); mbar_init1(&bar_w); mbar_init1(&rdy_f); mbar_init1(&rdy_b);
+        mbar_init1(&bar_f[0]); mbar_init1(&bar_f[1]); mbar_init1(&bar_d); mbar_init1(&bar_w);
+        mbar_init1(&rdy_f[0]); mbar_init1(&rdy_f[1]); mbar_init1(&rdy_b);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
@@ -474,8 +484,13 @@ __global__ void __launch_bounds__(PNT_ALL, 1) tinycnn_round_kernel(const Round R
     if (warp == PNT / 32) {
         // ---- MMA issuer: lane 0 walks the same steps as the workers and issues each image's tensor-core work as soon as
         // the workers have published its operands; completion goes back through bar_f / bar_d / bar_w
-        if (lane == 0) {
-            uint32_t prf = 0, prb = 0;
+        // all 32 lanes walk the loops together (uniform control flow, descriptors in uniform registers); one elected lane
+        // issues each MMA / commit.  A full 512-column allocation starts at TMEM address 0: using the constant keeps the
+        // accumulator addresses out of vector registers (checked once below).
+        {
+            if (tmem != 0u && lane == 0) atomicExch(R.err, 2);
+            constexpr uint32_t tm0 = 0u;
+            uint32_t prf[2] = {0, 0}, prb = 0;
 #pragma unroll 1
             for (int epoch = 0; epoch < R.epochs; ++epoch) {
                 s.epoch = epoch;
@@ -488,17 +503,23 @@ __global__ void __launch_bounds__(PNT_ALL, 1) tinycnn_round_kernel(const Round R
                     const int my_imgs = cta < nb ? (nb - cta + G - 1) / G : 0;
 #pragma unroll 1
                     for (int i = 0; i < my_imgs; ++i) {
-                        mbar_wait_all(&rdy_f, prf);
-                        issue_conv2_fwd(sbase, tmem);
-                        umma_commit1(&bar_f);
+                        if (i & 1) {
+                            mbar_wait_all(&rdy_f[1], prf[1]);
+                            issue_conv2_fwd<true>(sbase, tm0 + TM_FWD_SET, OFF_A1B);
+                            umma_commit1_elect(&bar_f[1]);
+                        } else {
+                            mbar_wait_all(&rdy_f[0], prf[0]);
+                            issue_conv2_fwd<true>(sbase, tm0, OFF_A1);
+                            umma_commit1_elect(&bar_f[0]);
+                        }
                     }
 #pragma unroll 1
                     for (int i = 0; i < my_imgs; ++i) {
                         mbar_wait_all(&rdy_b, prb);
-                        issue_conv2_dgrad(sbase, tmem);
-                        umma_commit1(&bar_d);
-                        issue_conv2_wgrad(sbase, tmem, i > 0);
-                        umma_commit1(&bar_w);
+                        issue_conv2_dgrad(sbase, tm0);
+                        umma_commit1_elect(&bar_d);
+                        issue_conv2_wgrad(sbase, tm0, i > 0);
+                        umma_commit1_elect(&bar_w);
                     }
                 }
             }
@@ -526,25 +547,41 @@ __global__ void __launch_bounds__(PNT_ALL, 1) tinycnn_round_kernel(const Round R
             }
             if (tid < 32) b2g[tid] = 0.f;
             QFX_MARK(15);
+            // software pipeline over this CTA's images: conv1 of image i (CUDA cores) runs while the tensor core still
+            // works on image i-1; the epilogue of image i-1 runs while the tensor core works on image i
+            {
+                int n_img = 0;
+                size_t prev_row = 0;
 #pragma unroll 1
-            for (int img = cta; img < nb; img += G) {
-                const size_t row = (size_t)sel * BS + img;
-                const float* src = s.X + (size_t)sample_index(s, sel, lo, img) * 784;
-                for (int i = tid; i < 28 * 14; i += PNT) {
-                    const int y = i / 14, x2 = i - y * 14;
-                    cp_async8(xs32 + (y + 2) * 32 + 2 + 2 * x2, src + y * 28 + 2 * x2);
+                for (int img = cta; img < nb; img += G, ++n_img) {
+                    const int buf = n_img & 1;
+                    const size_t row = (size_t)sel * BS + img;
+                    const float* src = s.X + (size_t)sample_index(s, sel, lo, img) * 784;
+                    for (int i = tid; i < 28 * 14; i += PNT) {
+                        const int y = i / 14, x2 = i - y * 14;
+                        cp_async8(xs32 + (y + 2) * 32 + 2 + 2 * x2, src + y * 28 + 2 * x2);
+                    }
+                    cp_async_wait_all();
+                    WSYNC();
+                    QFX_MARK(0);
+                    conv1_to_planes(smem, s.a1 + row * 3136, s.i1 + row * 3136, buf ? OFF_A1B : OFF_A1);
+                    hand_to_issuer(&rdy_f[buf]);
+                    QFX_MARK(1);
+                    if (n_img > 0) {
+                        mbar_wait_all(&bar_f[buf ^ 1], pf[buf ^ 1]);
+                        QFX_MARK(2);
+                        conv2_fwd_epilogue(tmem + (buf ^ 1) * TM_FWD_SET, b2s, s.a2 + prev_row * 1568, s.i2 + prev_row * 1568);
+                        QFX_MARK(3);
+                    }
+                    prev_row = row;
                 }
-                cp_async_wait_all();
-                WSYNC();
-                QFX_MARK(0);
-                conv1_to_planes(smem, s.a1 + row * 3136, s.i1 + row * 3136);
-                hand_to_issuer(&rdy_f);
-                QFX_MARK(1);
-                mbar_wait_all(&bar_f, pf);
-                QFX_MARK(2);
-                conv2_fwd_epilogue(tmem, b2s, s.a2 + row * 1568, s.i2 + row * 1568);
-                WSYNC();
-                QFX_MARK(3);
+                if (n_img > 0) {
+                    const int buf = (n_img - 1) & 1;
+                    mbar_wait_all(&bar_f[buf], pf[buf]);
+                    QFX_MARK(2);
+                    conv2_fwd_epilogue(tmem + buf * TM_FWD_SET, b2s, s.a2 + prev_row * 1568, s.i2 + prev_row * 1568);
+                    QFX_MARK(3);
+                }
             }
             cp_async_wait_all();
             group_barrier(bar, bar_target, G, R.err);

@@ -57,6 +57,26 @@ __device__ __forceinline__ void mbar_wait_parity(uint64_t* bar, uint32_t parity)
 __device__ __forceinline__ void umma_commit1(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_addr(bar)) : "memory");
 }
+// The same two operations for a CONVERGENT warp: all 32 lanes execute the call with identical operands, one elected
+// lane issues.  Keeping the issuing warp's control flow uniform lets the compiler hold descriptors in uniform registers;
+// under `if (lane == 0)` every MMA is wrapped in an elect / R2UR.BROADCAST / branch loop that costs more than the MMA.
+__device__ __forceinline__ void umma_bf16_elect(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p, e;\n"
+        "elect.sync _|e, 0xFFFFFFFF;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void umma_commit1_elect(uint64_t* bar) {
+    asm volatile(
+        "{\n"
+        ".reg .pred e;\n"
+        "elect.sync _|e, 0xFFFFFFFF;\n"
+        "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n"
+        "}\n" ::"r"(smem_addr(bar)) : "memory");
+}
 template <int N>
 __device__ __forceinline__ void tmem_ld(uint32_t taddr, uint32_t (&r)[N]);
 template <>
