@@ -65,14 +65,14 @@ struct Round {
     __nv_bfloat16* wop;      // [K,4,12800] conv2 operand copies: forward hi, forward lo, dgrad hi, dgrad lo
     unsigned* bar;           // [K] group barrier counters (zeroed by the host before the launch)
     int* err;                // set when a barrier gave up waiting (a bug elsewhere must not hang the GPU)
-    long long* prof;         // optional [K, G, 20] per-CTA cycle counters per phase (null: no timing)
+    long long* prof;         // optional [K, G, 24] per-CTA cycle counters per phase (null: no timing)
 };
 // phase timer: thread 0 adds the cycles since the previous mark to slot `id`
 #define QFX_MARK(id)                                                              \
     do {                                                                          \
         if (R.prof && tid == 0) {                                                 \
             const long long _t = clock64();                                       \
-            R.prof[((size_t)sel * gridDim.x + cta) * 20 + (id)] += _t - t_mark;   \
+            R.prof[((size_t)sel * gridDim.x + cta) * 24 + (id)] += _t - t_mark;   \
             t_mark = _t;                                                          \
         }                                                                         \
     } while (0)
@@ -339,10 +339,11 @@ struct HeadSm {
     float dz[BS][MAX_CLASSES];
     float red[2];
 };
+constexpr int PCX = 36;      // row stride of the fc1-backward tiles: 16-byte aligned rows for cp.async; lanes walk along k
 struct PcSm {
     float dh[BS][64];
-    float xs[BS][33];
-    float wsm[64][33];
+    float xs[2][BS][PCX];    // double-buffered: the next chunk's tiles land while this chunk is computed
+    float wsm[2][64][PCX];
     HeadSm hs;
 };
 static_assert(sizeof(PcSm) <= 2 * WOP, "PC scratch");
@@ -350,7 +351,16 @@ static_assert(sizeof(PcSm) <= 2 * WOP, "PC scratch");
 // Head for all rows of the minibatch (every CTA of the group computes it: the work is tiny and it saves a barrier):
 // h = dropout(relu(sum of split-K partials + b1)), logits, softmax-CE, d logits, dh.  The owner CTA also accumulates
 // the epoch statistics and leaves the fc2 / fc1-bias gradients for PE.
-__device__ __forceinline__ void head_phase(const Step& s, int sel, int nb, int lo, PcSm& sm, bool owner, int cta, int G) {
+__device__ __forceinline__ void head_phase(const Step& s, int sel, int nb, int lo, PcSm& sm, bool owner, int cta, int G,
+                                           long long* prof /*this CTA's counters or null*/, long long& t_mark) {
+#define HEAD_MARK(id)                                                      \
+    do {                                                                   \
+        if (prof && threadIdx.x == 0) {                                    \
+            const long long _t = clock64();                                \
+            prof[id] += _t - t_mark;                                       \
+            t_mark = _t;                                                   \
+        }                                                                  \
+    } while (0)
     HeadSm& hs = sm.hs;
     const int tid = threadIdx.x, NC = s.n_classes;
     const float* __restrict__ prm = s.params + (size_t)sel * s.nd;
@@ -361,33 +371,33 @@ __device__ __forceinline__ void head_phase(const Step& s, int sel, int nb, int l
     const unsigned long long dkey = key3(s.seed ^ 0x44524f50ull, (unsigned long long)rnd * 4096ull + s.client_ids[sel],
                                          (unsigned long long)s.epoch * 65536ull + s.batch_index);
     const float keep_scale = s.p_drop > 0.f ? 1.f / (1.f - s.p_drop) : 1.f;
-    {   // 2048 outputs, 4 per thread; the 56 split-K loads of a thread are issued before any is used
-        float pv[4][FC1_SLICES];
+    {   // 2048 outputs: thread = (row b, four consecutive features); its 14 split-K partials arrive as 14 independent
+        // 16-byte loads issued before any is used
+        const int b = tid >> 4, f4 = (tid & 15) * 4;
+        float4 pv[FC1_SLICES];
+        const float* part = s.fc1_part + ((size_t)sel * FC1_SLICES * BS + b) * 64 + f4;
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-            const int i = g * PNT + tid, b = i >> 6, f = i & 63;
-            const float* part = s.fc1_part + ((size_t)sel * FC1_SLICES * BS + b) * 64 + f;
+        for (int sl = 0; sl < FC1_SLICES; ++sl)
+            pv[sl] = b < nb ? __ldcg(reinterpret_cast<const float4*>(part + (size_t)sl * BS * 64)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 bias = __ldcg(reinterpret_cast<const float4*>(prm + F1B + f4));
+        float v[4] = {bias.x, bias.y, bias.z, bias.w};
 #pragma unroll
-            for (int sl = 0; sl < FC1_SLICES; ++sl) pv[g][sl] = b < nb ? __ldcg(part + (size_t)sl * BS * 64) : 0.f;
-        }
+        for (int sl = 0; sl < FC1_SLICES; ++sl) { v[0] += pv[sl].x; v[1] += pv[sl].y; v[2] += pv[sl].z; v[3] += pv[sl].w; }
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-            const int i = g * PNT + tid, b = i >> 6, f = i & 63;
-            float v = 0.f;
+        for (int j = 0; j < 4; ++j) {
+            float h = 0.f;
             if (b < nb) {
-                v = __ldcg(prm + F1B + f);
-#pragma unroll
-                for (int sl = 0; sl < FC1_SLICES; ++sl) v += pv[g][sl];
-                v = fmaxf(v, 0.f);
+                h = fmaxf(v[j], 0.f);
                 if (s.p_drop > 0.f) {
-                    const float u = uniform_from_bits(stream_at(dkey, (unsigned long long)i));
-                    v = u < s.p_drop ? 0.f : v * keep_scale;
+                    const float u = uniform_from_bits(stream_at(dkey, (unsigned long long)(b * 64 + f4 + j)));
+                    h = u < s.p_drop ? 0.f : h * keep_scale;
                 }
             }
-            hs.h[b][f] = v;
+            hs.h[b][f4 + j] = h;
         }
     }
     WSYNC();
+    HEAD_MARK(19);
     for (int i = tid; i < BS * NC; i += PNT) {
         const int b = i / NC, c = i % NC;
         float v = __ldcg(prm + f2b + c);
@@ -415,6 +425,7 @@ __device__ __forceinline__ void head_phase(const Step& s, int sel, int nb, int l
         }
     }
     WSYNC();
+    HEAD_MARK(20);
     for (int i = tid; i < BS * 64; i += PNT) {
         const int b = i >> 6, f = i & 63;
         float v = 0.f;
@@ -426,6 +437,7 @@ __device__ __forceinline__ void head_phase(const Step& s, int sel, int nb, int l
     }
     if (owner && tid == 0) { s.stats[sel * 2] += hs.red[0]; s.stats[sel * 2 + 1] += hs.red[1]; }
     WSYNC();
+    HEAD_MARK(21);
     {
         // gradients of fc2 weights, fc2 bias, fc1 bias (applied in PE): every CTA has the whole head, so the
         // NC*64 + NC + 64 sums over the minibatch are dealt round-robin to the warps of all G CTAs; lane = row
@@ -634,25 +646,31 @@ __global__ void __launch_bounds__(PNT_ALL, 1) tinycnn_round_kernel(const Round R
             // ================= PC: head, then fc1 backward per 32-column chunk =================
             {
                 PcSm& sm = *reinterpret_cast<PcSm*>(smem + OFF_WF);
-                head_phase(s, sel, nb, lo, sm, cta == 0, cta, G);
-                QFX_MARK(7);
-#pragma unroll 1
-                for (int chunk = cta; chunk < 49; chunk += G) {
+                // tiles of a 32-column chunk (a2 rows and W1 rows) straight from L2 into shared memory; rows beyond the
+                // minibatch were zeroed once below and are never overwritten
+                auto fetch_chunk = [&](int chunk, int buf) {
                     const int k0 = chunk * 32;
-                    WSYNC();
                     for (int i = tid; i < (BS + 64) * 8; i += PNT) {
                         const int r = i >> 3, c = i & 7;
-                        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                        float* d;
                         if (r < BS) {
-                            if (r < nb) v = __ldcg(reinterpret_cast<const float4*>(s.a2 + ((size_t)sel * BS + r) * 1568 + k0) + c);
-                            d = &sm.xs[r][4 * c];
+                            if (r < nb) cp_async16(&sm.xs[buf][r][4 * c], s.a2 + ((size_t)sel * BS + r) * 1568 + k0 + 4 * c);
                         } else {
-                            v = __ldcg(reinterpret_cast<const float4*>(prm + F1W + (size_t)(r - BS) * 1568 + k0) + c);
-                            d = &sm.wsm[r - BS][4 * c];
+                            cp_async16(&sm.wsm[buf][r - BS][4 * c], prm + F1W + (size_t)(r - BS) * 1568 + k0 + 4 * c);
                         }
-                        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
                     }
+                };
+                if (cta < 49) {
+                    for (int i = tid; i < 2 * BS * PCX; i += PNT) (&sm.xs[0][0][0])[i] = 0.f;
+                    WSYNC();
+                    fetch_chunk(cta, 0);      // in flight while the head is computed
+                }
+                head_phase(s, sel, nb, lo, sm, cta == 0, cta, G,
+                           R.prof ? R.prof + ((size_t)sel * gridDim.x + cta) * 24 : nullptr, t_mark);
+                QFX_MARK(7);
+                int buf = 0;
+#pragma unroll 1
+                for (int chunk = cta; chunk < 49; chunk += G, buf ^= 1) {
+                    const int k0 = chunk * 32;
                     float mprev[8];
                     const int t = tid & 255, k = t & 31;
                     if (tid >= 256) {
@@ -660,28 +678,30 @@ __global__ void __launch_bounds__(PNT_ALL, 1) tinycnn_round_kernel(const Round R
 #pragma unroll
                         for (int j = 0; j < 8; ++j) mprev[j] = __ldcg(mom + F1W + (size_t)(fg + j) * 1568 + k0 + k);
                     }
-                    WSYNC();
+                    cp_async_wait_all();
+                    WSYNC();                                  // this chunk's tiles are in; the other buffer is free again
+                    if (chunk + G < 49) fetch_chunk(chunk + G, buf ^ 1);
                     if (tid < 256) {
                         // dx[b][k] = sum_f dh[b][f] W1[f][k], masked by the ReLU of a2: rows bq, bq+8, bq+16, bq+24
                         const int bq = t >> 5;
                         float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll 8
                         for (int f = 0; f < 64; ++f) {
-                            const float w = sm.wsm[f][k];
+                            const float w = sm.wsm[buf][f][k];
 #pragma unroll
                             for (int r = 0; r < 4; ++r) acc[r] += sm.dh[bq + 8 * r][f] * w;
                         }
 #pragma unroll
                         for (int r = 0; r < 4; ++r) {
                             const int b = bq + 8 * r;
-                            if (b < nb) R.dxm[((size_t)sel * BS + b) * 1568 + k0 + k] = sm.xs[b][k] > 0.f ? acc[r] : 0.f;
+                            if (b < nb) R.dxm[((size_t)sel * BS + b) * 1568 + k0 + k] = sm.xs[buf][b][k] > 0.f ? acc[r] : 0.f;
                         }
                     } else {
                         // dW1[f][k] = sum_b dh[b][f] x[b][k]; SGD-momentum in place
                         const int fg = (t >> 5) * 8;
                         float acc[8] = {};
                         for (int b = 0; b < nb; ++b) {
-                            const float xv = sm.xs[b][k];
+                            const float xv = sm.xs[buf][b][k];
                             const float4 d0 = *reinterpret_cast<const float4*>(&sm.dh[b][fg]);
                             const float4 d1 = *reinterpret_cast<const float4*>(&sm.dh[b][fg + 4]);
                             acc[0] += d0.x * xv; acc[1] += d0.y * xv; acc[2] += d0.z * xv; acc[3] += d0.w * xv;
@@ -692,10 +712,11 @@ __global__ void __launch_bounds__(PNT_ALL, 1) tinycnn_round_kernel(const Round R
                             const size_t p = F1W + (size_t)(fg + j) * 1568 + k0 + k;
                             const float m = s.momentum * mprev[j] + acc[j];
                             mom[p] = m;
-                            prm[p] = sm.wsm[fg + j][k] - s.lr * m;
+                            prm[p] = sm.wsm[buf][fg + j][k] - s.lr * m;
                         }
                     }
                 }
+                cp_async_wait_all();
             }
             QFX_MARK(8);
             group_barrier(bar, bar_target, G, R.err);
@@ -1021,7 +1042,7 @@ extern "C" int qfx_tinycnn_train_round(const float* X, const int* labels, const 
         R.wop = w.wop + (size_t)k0 * 4 * 12800;
         R.bar = w.bar + k0;
         R.err = w.err;
-        R.prof = g_round_prof[current_device()] ? g_round_prof[current_device()] + (size_t)k0 * 32 * 20 : nullptr;
+        R.prof = g_round_prof[current_device()] ? g_round_prof[current_device()] + (size_t)k0 * 32 * 24 : nullptr;
         void* args[] = {(void*)&R};
         QFX_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)tinycnn_round_kernel, dim3((unsigned)G, (unsigned)kc), dim3(PNT_ALL),
                                                  args, (size_t)PSMEM, stream));
@@ -1029,7 +1050,7 @@ extern "C" int qfx_tinycnn_train_round(const float* X, const int* labels, const 
     return 0;
 }
 
-// Phase timing for tuning: cycles per phase and CTA are added into prof [K, G, 20] (int64, caller-zeroed; G = CTAs per
+// Phase timing for tuning: cycles per phase and CTA are added into prof [K, G, 24] (int64, caller-zeroed; G = CTAs per
 // client of the launch) by every following qfx_tinycnn_train_round on the current device; null switches it off.
 // Slots: 15 weight load issue, 0 image load, 1 conv1, 2 conv2 forward MMAs, 3 forward epilogue, 4 barrier 1, 5 fc1
 // forward, 6 barrier 2, 7 head, 8 fc1 backward, 9 barrier 3, 10 plane build, 11 data-gradient MMAs, 12 its epilogue +

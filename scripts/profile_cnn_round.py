@@ -15,7 +15,8 @@ from qfedx_b200.models import TinyCNN
 from qfedx_b200.ops import _lib
 
 NAMES = ["img load", "conv1", "fwd mma", "fwd epi", "bar1", "fc1 fwd", "bar2", "head", "fc1 bwd", "bar3", "planes",
-         "dgrad mma", "dg epi+c1wg", "wgrad wait", "wgrad epi", "wload", "bar4", "update", "bar5", "-"]
+         "dgrad mma", "dg epi+c1wg", "wgrad wait", "wgrad epi", "wload", "bar4", "update", "bar5", "head:load+h",
+         "head:logits+CE", "head:dh", "-", "-"]
 
 
 def main():
@@ -34,13 +35,13 @@ def main():
     steps = 5 * ((per + 31) // 32)
     print(f"clients {K}: round {s.elapsed_time(e):.2f} ms, {s.elapsed_time(e) * 1e3 / steps:.1f} us/step")
     geff = G if G else min(32, torch.cuda.get_device_properties(0).multi_processor_count // K)
-    prof = torch.zeros(K, geff, 20, dtype=torch.int64, device="cuda")
+    prof = torch.zeros(K, geff, 24, dtype=torch.int64, device="cuda")
     _lib.call("qfx_tinycnn_round_profile", ctypes.c_void_p(prof.data_ptr()), launches=0)
     tr.train(g0, list(range(K)), 2)
     torch.cuda.synchronize()
     _lib.call("qfx_tinycnn_round_profile", ctypes.c_void_p(0), launches=0)
     us = prof.double().cpu() / 1965.0 / steps          # cycles -> us per step at 1965 MHz
-    flat = us.view(-1, 20)
+    flat = us.view(-1, 24)
     print(f"{'phase':14s} {'mean':>8s} {'max':>8s}   (us per step, G = {geff} CTAs per client)")
     for i, n in enumerate(NAMES):
         if flat[:, i].max() > 0:
