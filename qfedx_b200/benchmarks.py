@@ -100,14 +100,18 @@ def unitary_gemm_throughput(n=8, L=6, B=1 << 15):
 
 
 def unitary_gemm_vs_engines():
-    """Where K2 earns its place in the product (models/vqc.py: inference_expvals picks it there): 12 qubits, where no
-    register kernel exists, against the pass engine K5; and a deep 10-qubit circuit over a large batch against the
-    register kernel K1, whose cost grows with the depth while the GEMM's does not.  Times include building and
+    """Where K2 earns its place in the product (models/vqc.py: inference_expvals picks it there): deep circuits over
+    large batches - at 12 qubits (no register kernel exists) against the pass engine K5, at 10 qubits against the register
+    kernel K1.  Both competitors grow with the depth, the GEMM does not; the shallow 12-qubit row shows the other side of
+    the break-even (the selection rule does not pick the GEMM there).  Times include building and
     packing the unitary (once per parameter set) separately from the per-batch pipeline."""
     from .models import VQC
     dev = torch.device("cuda")
     out = {}
-    for name, (n, L, B, other) in {"12q_4L_4096": (12, 4, 4096, "passes"), "10q_24L_16384": (10, 24, 16384, "registers")}.items():
+    shapes = {"12q_16L_4096": (12, 16, 4096, "passes"), "12q_4L_4096": (12, 4, 4096, "passes"),
+              "10q_24L_16384": (10, 24, 16384, "registers")}
+    from .ops.unitary_gemm import prefers_unitary_gemm
+    for name, (n, L, B, other) in shapes.items():
         torch.manual_seed(0)
         m = VQC(n, L, 2).to(dev)
         x = torch.rand(B, n, device=dev) * math.pi
@@ -118,7 +122,7 @@ def unitary_gemm_vs_engines():
         t_other = _time_ms(lambda: m.inference_expvals(x, other), iters=5)
         out[name] = {"n_qubits": n, "layers": L, "batch": B, "gemm_ms": t_gemm, "unitary_build_and_pack_ms": t_build,
                      "other_engine": other, "other_ms": t_other, "speedup": t_other / t_gemm,
-                     "max_abs_diff": float((a - b).abs().max()), "auto_picks_gemm": True}
+                     "max_abs_diff": float((a - b).abs().max()), "auto_picks_gemm": prefers_unitary_gemm(n, L, B)}
     return out
 
 

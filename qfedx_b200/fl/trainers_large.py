@@ -156,7 +156,7 @@ class LargeVQCTrainer:
         from ..ops.unitary_gemm import UnitaryGemm, prefers_unitary_gemm
         if X.is_cuda and isinstance(self.backend, PassBackend) and prefers_unitary_gemm(self.model.n_qubits,
                                                                                           self.model.n_layers, len(X)):
-            # 11-12 qubits, a test set of hundreds of samples: one tcgen05 GEMM with the round's unitary (K2)
+            # 11-12 qubits, a deep circuit and a test set of hundreds of samples: one tcgen05 GEMM with the round's unitary (K2)
             ug = UnitaryGemm(theta.reshape(1, self.model.n_layers, self.model.n_qubits, 2), self.model.entangler)
             z = a * ug.expvals(X.float())[:, :C] + b
             loss = F.binary_cross_entropy_with_logits(z[:, 0], y.float()) if C == 1 else F.cross_entropy(z, y)

@@ -75,7 +75,7 @@ class VQC(nn.Module):
     @torch.no_grad()
     def inference_expvals(self, x: torch.Tensor, engine: str = "auto") -> torch.Tensor:
         """<Z_q> [B, n] without autograd, on the fastest engine for the shape: the register kernel K1 (n <= 10), the
-        tcgen05 unitary GEMM K2 (11-12 qubits, or deep circuits over large batches: its cost does not grow with the
+        tcgen05 unitary GEMM K2 (deep circuits over large batches, also at 11-12 qubits where no register kernel exists: its cost does not grow with the
         depth) or the pass engine K5 (n > 12).  ``engine`` forces 'registers' | 'gemm' | 'passes'."""
         if not x.is_cuda or self.encoding != "angle":
             return self.expvals(x)

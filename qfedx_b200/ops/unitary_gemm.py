@@ -31,13 +31,13 @@ def ansatz_unitary_t(theta: torch.Tensor, entangler: str = "cnot") -> torch.Tens
 
 
 def prefers_unitary_gemm(n_qubits: int, n_layers: int, batch: int) -> bool:
-    """Where K2 is the faster inference engine (measured on B200, bench aux `unitary_gemm_*`): its cost does not depend
-    on the circuit depth, the register kernel's grows linearly with it, and for 11-12 qubits the alternative is the
-    pass engine, which streams every state through HBM once per pass."""
+    """Where K2 is the faster inference engine (measured on B200, bench aux `unitary_gemm_vs_engines`): its cost does not
+    depend on the circuit depth - one [2 x 2^n]^2 GEMM per batch - while the register kernel (n <= 10) and the pass engine
+    (n > 10) grow linearly with it.  Break-even depths: about 12 layers at 10 and 12 qubits, 8 at 11, 10 at 8-9 qubits."""
     if not (MIN_QUBITS <= n_qubits <= MAX_QUBITS):
         return False
     if n_qubits > MAX_REG_QUBITS:
-        return batch >= 256
+        return batch >= 256 and n_layers >= (12 if n_qubits >= 12 else 8)
     return batch >= 4096 and n_qubits >= 8 and n_layers >= (12 if n_qubits >= 10 else 10)
 
 

@@ -55,23 +55,23 @@ def test_model_api_uses_the_unitary_gemm_for_11_and_12_qubits(n, L, B):
     m = VQC(n, L, 3, init_scale=0.7).cuda()
     g = torch.Generator().manual_seed(1)
     x = (torch.rand(B, n, generator=g) * math.pi).cuda()
-    assert prefers_unitary_gemm(n, L, B)
-    E = m.inference_expvals(x)                       # auto -> gemm
+    assert prefers_unitary_gemm(n, 16, B) and not prefers_unitary_gemm(n, 2, B)     # deep: GEMM; shallow: pass engine
+    E = m.inference_expvals(x, "gemm")
     assert getattr(m, "_ug", None) is not None
     E_pass = m.inference_expvals(x, "passes")
     E_ref = ref.vqc_expvals_ref(x[:48].cpu().double(), m.theta.detach().cpu().double()[None]).numpy()
     np.testing.assert_allclose(E[:48].cpu().numpy(), E_ref, atol=5e-5)
     np.testing.assert_allclose(E.cpu().numpy(), E_pass.cpu().numpy(), atol=5e-5)
-    pred = m.predict(x)
+    pred = m.predict(x, "gemm")
     z_ref = (m.readout_scale.detach().cpu().double() * torch.from_numpy(E_ref)[:, :3] + m.readout_bias.detach().cpu().double())
     assert torch.equal(pred[:48].cpu(), z_ref.argmax(1))
     # the packed unitary is reused until theta changes, then rebuilt
     ug = m._ug
-    m.inference_expvals(x)
+    m.inference_expvals(x, "gemm")
     assert m._ug is ug
     with torch.no_grad():
         m.theta.add_(0.1)
-    E2 = m.inference_expvals(x)
+    E2 = m.inference_expvals(x, "gemm")
     assert m._ug is not ug and float((E2 - E).abs().max()) > 1e-3
 
 
