@@ -264,7 +264,8 @@ def run_large(cfg, name, args, rank, world, local):
     P = model.n_angle_params
     steps_per_client = cfg["epochs"] * ((per + cfg["batch"] - 1) // cfg["batch"])
     # parameter shift: the last layer's n RZ angles have an exactly zero gradient for a Z-basis readout and are skipped
-    per_step = cfg["batch"] * ((1 + 2 * (P - n)) if cfg["grad"] == "param_shift" else 3)
+    # adjoint: one forward and one backward sweep over two states - counted as 1 + 3 forward-equivalent simulations
+    per_step = cfg["batch"] * ((1 + 2 * (P - n)) if cfg["grad"] == "param_shift" else (4 if cfg["grad"] == "adjoint" else 3))
     sims = K * steps_per_client * per_step + cfg["test_n"]
     n_gates = len(ansatz_gates(n, L))                      # feature map + ansatz
     return dict(ms=ms, e2e_ms=e2e_ms, clocks=clocks, launches=launches,
@@ -408,6 +409,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="cfed", choices=["cfed", "vqc8", "vqc4", "vqc20", "vqc30"])
     ap.add_argument("--no-aux", action="store_true", help="skip the secondary measurements")
+    ap.add_argument("--grad", default=None, choices=["param_shift", "adjoint", "spsa"],
+                    help="vqc20 / vqc30: gradient method (default: the one BASELINE.json's config names; 'adjoint' is the pass "
+                         "engine's reverse sweep - a secondary line, the config is then labelled accordingly)")
     ap.add_argument("--allow-shrink", action="store_true",
                     help="honour QFX_BENCH_CLIENTS / QFX_BENCH_SCALE (smoke runs; the line then says so and is not a headline)")
     args = ap.parse_args()
@@ -415,6 +419,8 @@ def main():
     init_dist(world, local)
     cfgs = {"cfed": CFED, "vqc8": VQC8, "vqc4": VQC4, "vqc20": VQC20, "vqc30": VQC30}
     cfg = dict(cfgs[args.config])
+    if args.grad and args.config in ("vqc20", "vqc30"):
+        cfg["grad"] = args.grad
     # every QFX_* variable this process can see is echoed in the JSON line; the two that change the size of the timed
     # job are refused unless --allow-shrink is given (and then mark the line as shrunk)
     env_seen = {k: v for k, v in sorted(os.environ.items()) if k.startswith("QFX_")}
