@@ -210,17 +210,24 @@ def aux_measurements(args=None, rank=0, world=1, local=0, skip=None):
             out["multi_gpu_error"] = f"{type(exc).__name__}: {exc}"
     if rank != 0:
         return out
-    out["sv8_throughput"] = small_circuit_throughput(8, 6, 1 << 15)
-    out["sv4_throughput"] = small_circuit_throughput(4, 2, 1 << 18)
-    out["vs_torch_baseline_8q"] = torch_baseline_ratio(8, 6, 2048)
-    out["agg_vqc"] = aggregation_latency(64, 102)
-    out["agg_tinycnn_dp_secagg"] = aggregation_latency(8, 113859, True)
-    out["agg_1e8_dp"] = aggregation_latency(4, 25_000_000, iters=10)
-    out["agg_1e8_clip"] = aggregation_latency(4, 25_000_000, sigma=0.0, iters=10)
-    out["agg_1e8_weights"] = aggregation_latency(4, 25_000_000, mode="weights", clip=0.0, sigma=0.0, iters=10)
-    out["unitary_gemm_8q"] = unitary_gemm_throughput(8, 6, 1 << 15)
-    out["unitary_gemm_vs_engines"] = unitary_gemm_vs_engines()
-    out["sv20_pass_engine"] = large_state_throughput(20, 2, 16)
+
+    def safe(key, fn, *a, **kw):     # one failing secondary number must not take the others with it
+        try:
+            out[key] = fn(*a, **kw)
+        except Exception as exc:
+            out[key] = {"error": f"{type(exc).__name__}: {exc}"}
+
+    safe("sv8_throughput", small_circuit_throughput, 8, 6, 1 << 15)
+    safe("sv4_throughput", small_circuit_throughput, 4, 2, 1 << 18)
+    safe("vs_torch_baseline_8q", torch_baseline_ratio, 8, 6, 2048)
+    safe("agg_vqc", aggregation_latency, 64, 102)
+    safe("agg_tinycnn_dp_secagg", aggregation_latency, 8, 113859, True)
+    safe("agg_1e8_dp", aggregation_latency, 4, 25_000_000, iters=10)
+    safe("agg_1e8_clip", aggregation_latency, 4, 25_000_000, sigma=0.0, iters=10)
+    safe("agg_1e8_weights", aggregation_latency, 4, 25_000_000, mode="weights", clip=0.0, sigma=0.0, iters=10)
+    safe("unitary_gemm_8q", unitary_gemm_throughput, 8, 6, 1 << 15)
+    safe("unitary_gemm_vs_engines", unitary_gemm_vs_engines)
+    safe("sv20_pass_engine", large_state_throughput, 20, 2, 16)
     return out
 
 

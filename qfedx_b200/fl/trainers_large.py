@@ -141,7 +141,62 @@ class LargeVQCTrainer:
                 last = float(loss)
         return w, last
 
+    def _train_lockstep(self, flat, selected):
+        """All selected clients of this rank advance together (pass engine + adjoint gradients): at step j every client
+        that still has a minibatch contributes its samples to ONE batch of states - sample row s of client k sits at batch
+        index s * K + k, so the kernels pick client k's parameter row with `index % K` - and one forward sweep, one readout
+        and one backward sweep serve all of them; Adam runs vectorised over the clients.  Same arithmetic per client as the
+        one-client-at-a-time loop (sample orders are drawn in that loop's order)."""
+        P, C, dev = self.model.n_angle_params, self.model.n_logits, flat.device
+        sel = [int(k) for k in selected]
+        data = [self.data.client(k) for k in sel]
+        K, bs = len(sel), self.batch_size
+        orders = [[torch.randperm(len(X), device=X.device, generator=self.generator) for _ in range(self.epochs)] for X, _ in data]
+        W = flat.float()[None].repeat(K, 1).contiguous()
+        m, v = torch.zeros_like(W), torch.zeros_like(W)
+        t = torch.zeros(K, device=dev)
+        last = torch.zeros(K, device=dev)
+        n_k = torch.tensor([len(X) for X, _ in data], device=dev)
+        n_feat = data[0][0].shape[1]
+        for e in range(self.epochs):
+            for j in range(int(math.ceil(int(n_k.max()) / bs))):
+                act = [i for i in range(K) if j * bs < len(data[i][0])]
+                A = len(act)
+                xb = torch.zeros(bs, A, n_feat, device=dev)
+                yb = torch.zeros(bs, A, dtype=torch.long, device=dev)
+                valid = torch.zeros(bs, A, device=dev)
+                for c, i in enumerate(act):
+                    idx = orders[i][e][j * bs:(j + 1) * bs]
+                    s_ = len(idx)
+                    xb[:s_, c], yb[:s_, c], valid[:s_, c] = data[i][0][idx].float(), data[i][1][idx], 1.0
+                    if s_ < bs:                                 # pad with a real sample: zero cotangent, no contribution
+                        xb[s_:, c] = data[i][0][idx[0]].float()
+                rows = torch.as_tensor(act, device=dev)
+                Wa = W[rows]
+                theta, a, b = Wa[:, :P].contiguous(), Wa[:, P:P + C], Wa[:, P + C:]
+                E = self.backend.vqc.expvals(xb.reshape(bs * A, n_feat), theta, C).reshape(bs, A, C)
+                Ed = E.detach().requires_grad_(True)
+                a_, b_ = a.detach().requires_grad_(True), b.detach().requires_grad_(True)
+                z = a_[None] * Ed + b_[None]
+                if C == 1:
+                    per = F.binary_cross_entropy_with_logits(z[..., 0], yb.float(), reduction="none")
+                else:
+                    per = F.cross_entropy(z.reshape(bs * A, C), yb.reshape(-1), reduction="none").reshape(bs, A)
+                loss_k = (per * valid).sum(0) / valid.sum(0)                 # every client's own minibatch mean
+                gE, ga, gb = torch.autograd.grad(loss_k.sum(), [Ed, a_, b_])
+                gth = self.backend.vqc.adjoint_grad(xb.reshape(bs * A, n_feat), theta, gE.reshape(bs * A, C).contiguous())
+                g = torch.cat([gth, ga, gb], dim=1)
+                t[rows] += 1
+                m[rows] = 0.9 * m[rows] + 0.1 * g
+                v[rows] = 0.999 * v[rows] + 0.001 * g * g
+                tt = t[rows][:, None]
+                W[rows] = Wa - self.lr * (m[rows] / (1 - 0.9 ** tt)) / (torch.sqrt(v[rows] / (1 - 0.999 ** tt)) + 1e-8)
+                last[rows] = loss_k.detach()
+        return W, {"train_loss": float(last.mean())}
+
     def train(self, global_flat, selected, rnd):
+        if self.grad_method == "adjoint" and isinstance(self.backend, PassBackend) and global_flat.is_cuda and len(selected) > 1:
+            return self._train_lockstep(global_flat, selected)
         rows, losses = [], []
         for k in selected:
             w, l = self._train_one(global_flat, int(k))

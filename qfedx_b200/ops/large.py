@@ -56,6 +56,7 @@ class Pass:
 
 
 REG_TILE_BITS = 12
+MAX_OPS_PER_PASS = 160        # csrc/sv_large.cu: MAX_OPS_PER_PASS
 PLAN_KIND_RXRZ_STRIPPED = 7   # plan-private op kind (csrc/sv_large.cu: V2_KIND_RXRZ_STRIPPED)
 
 
@@ -175,7 +176,13 @@ def compile_passes(n_qubits: int, gates: Sequence[Tuple[int, int, int, int]], ti
                 _lib.c_int(max_passes), _lib.c_int(max_ops), ip(tq), ip(begin), ip(ops))
     if n_pass < 0:
         raise _lib.QfxError(f"qfx_circuit_compile failed ({n_pass}): {_lib.lib().qfx_last_error().decode()}")
-    passes = [Pass(tq[i].copy(), ops[begin[i]:begin[i + 1]].copy()) for i in range(n_pass)]
+    # a deep circuit on few qubits can put more gates into one tile than a launch takes (MAX_OPS_PER_PASS in
+    # csrc/sv_large.cu): such a pass is cut into consecutive passes over the same tile
+    passes = []
+    for i in range(n_pass):
+        po = ops[begin[i]:begin[i + 1]]
+        for lo in range(0, max(1, len(po)), MAX_OPS_PER_PASS):
+            passes.append(Pass(tq[i].copy(), po[lo:lo + MAX_OPS_PER_PASS].copy()))
     if tile_bits == REG_TILE_BITS:
         for p in passes:
             p.plan = plan_segments(p.ops)
@@ -258,7 +265,7 @@ class LargeVQC:
                 th = th.reshape(B, self.L, self.n, 2)
                 ang = angles.repeat(B // angles.shape[0], 1)
                 return ref.vqc_state_ref(ang, th, torch.arange(B), "ry", self.entangler)
-            return ref.vqc_state_ref(angles, th, None if th.shape[0] == 1 else torch.arange(B), "ry", self.entangler)
+            return ref.vqc_state_ref(angles, th, None if th.shape[0] == 1 else torch.arange(B) % th.shape[0], "ry", self.entangler)
         st = torch.empty(B, 1 << self.n, dtype=torch.complex64, device=angles.device)
         run_passes(st, self.n, self.readout_passes if before_final_ring else self.passes, theta, angles, shift_param,
                    shift_value, init_zero=True, low_bits=self.low_bits, use_register_engine=self.register_engine)
@@ -323,14 +330,23 @@ class LargeVQC:
     def adjoint_grad(self, angles: torch.Tensor, theta: torch.Tensor, cot: torch.Tensor) -> torch.Tensor:
         """Same gradient as ``param_shift_grad`` by adjoint differentiation: one forward sweep, lambda = O psi, one
         backward sweep over the compiled passes carrying psi and lambda (csrc/sv_large.cu: sv_large_adjoint_pass_kernel)
-        - a constant number of state sweeps instead of 2P shifted circuits.  theta [P] shared by the samples."""
+        - a constant number of state sweeps instead of 2P shifted circuits.
+
+        theta [P]: shared by all S samples, returns [P].  theta [R, P]: sample b runs with row b % R (several clients'
+        models in one batch, rows interleaved) and the result is [R, P], row r summed over the samples of row r."""
         n_out = cot.shape[1]
         S, P, dev = angles.shape[0], self.n_params, angles.device
-        th = theta.reshape(1, P).contiguous().float()
+        shared = theta.dim() == 1
+        th = theta.reshape(-1, P).contiguous().float()
+        R = th.shape[0]
         if not angles.is_cuda:
             t = th.detach().clone().requires_grad_(True)
-            E = ref.expval_z_all(ref.vqc_state_ref(angles, t.reshape(1, self.L, self.n, 2), None, "ry", self.entangler)).float()
-            return torch.autograd.grad((E[:, :n_out] * cot).sum(), t)[0].reshape(P)
+            gid = None if R == 1 else (torch.arange(S) % R)
+            E = ref.expval_z_all(ref.vqc_state_ref(angles, t.reshape(R, self.L, self.n, 2), gid, "ry", self.entangler)).float()
+            g = torch.autograd.grad((E[:, :n_out] * cot).sum(), t)[0]
+            if self.L > 0:   # exactly-zero gradients of the last layer's RZ angles (see below): no rounding noise for Adam
+                g[:, [(self.L - 1) * self.n * 2 + 2 * q + 1 for q in range(self.n)]] = 0.0
+            return g.reshape(P) if shared else g
         ang = angles.contiguous().float()
         psi = self.states(ang, th, before_final_ring=True)
         lam = torch.empty_like(psi)
@@ -338,7 +354,7 @@ class LargeVQC:
         _lib.call("qfx_sv_large_parity_obs", _lib.ptr(torch.view_as_real(psi)), _lib.ptr(torch.view_as_real(lam)),
                   _lib.c_int(self.n), _lib.c_int(n_out), masks, _lib.ptr(cot.contiguous().float()), _lib.c_int(S),
                   _lib.stream_ptr())
-        grad = torch.zeros(1, P, device=dev)
+        grad = torch.zeros(R, P, device=dev)
         for p in reversed(self.readout_passes):
             if p.ops_dev is None or p.ops_dev.device != dev:
                 p.ops_dev = torch.as_tensor(p.ops, device=dev).contiguous()
@@ -349,15 +365,14 @@ class LargeVQC:
                 low += 1
             _lib.call("qfx_sv_large_adjoint_pass", _lib.ptr(torch.view_as_real(psi)), _lib.ptr(torch.view_as_real(lam)),
                       _lib.c_int(self.n), _lib.c_int(S), _lib.c_int(T), _lib.c_int(low), tq.ctypes.data_as(ctypes.c_void_p),
-                      _lib.ptr(p.ops_dev), _lib.c_int(len(p.ops)), _lib.ptr(th), _lib.c_int(1), _lib.c_int(P), _lib.ptr(ang),
+                      _lib.ptr(p.ops_dev), _lib.c_int(len(p.ops)), _lib.ptr(th), _lib.c_int(R), _lib.c_int(P), _lib.ptr(ang),
                       _lib.c_int(S), _lib.c_int(ang.shape[1]), _lib.ptr(grad), _lib.stream_ptr())
-        grad = grad.reshape(P)
         if self.L > 0:
             # the last layer's RZ angles cannot move a Z-basis readout (see param_shift_grad): their gradient is exactly 0;
             # the sweep returns rounding noise there, which Adam would normalise into full-size steps
             last_rz = torch.tensor([(self.L - 1) * self.n * 2 + 2 * q + 1 for q in range(self.n)], device=dev)
-            grad[last_rz] = 0.0
-        return grad
+            grad[:, last_rz] = 0.0
+        return grad.reshape(P) if shared else grad
 
     def _first_pass_of_param(self) -> dict:
         """parameter index -> index of the (only) readout pass whose gates use it."""

@@ -212,3 +212,25 @@ def test_large_vqc_trainer_with_adjoint_gradients_matches_param_shift_training()
     # differ by ~lr between two correct gradient methods; everything else must agree closely
     diff = (outs["adjoint"] - outs["param_shift"]).abs().flatten()
     assert float((diff < 2e-3).float().mean()) >= 0.95 and float(diff.median()) < 1e-4, diff
+
+
+def test_lockstep_adjoint_trainer_on_the_gpu_matches_per_client_training():
+    from qfedx_b200.fl import FederatedDataset
+    from qfedx_b200.fl.trainers_large import LargeVQCTrainer, PassBackend
+    from qfedx_b200.models import VQC
+    n, L = 13, 2
+    g = torch.Generator().manual_seed(4)
+    clients = [((torch.rand(5 + k, n, generator=g) * 0.8), torch.randint(0, 2, (5 + k,), generator=g)) for k in range(3)]
+    data = FederatedDataset.from_clients(clients, "cuda")
+    torch.manual_seed(0)
+    model = VQC(n, L, 2).cuda()
+    outs = []
+    for mode in ("seq", "lock"):
+        gen = torch.Generator(device="cuda").manual_seed(7)
+        tr = LargeVQCTrainer(model, data, PassBackend(n, L), epochs=2, batch_size=2, lr=0.05, grad_method="adjoint", generator=gen)
+        if mode == "seq":
+            outs.append(torch.stack([tr._train_one(tr.global_flat(), k)[0] for k in range(3)]))
+        else:
+            outs.append(tr.train(tr.global_flat(), [0, 1, 2], 0)[0])
+    d = (outs[0] - outs[1]).abs().flatten()
+    assert float(d.median()) < 1e-4 and float((d < 2e-3).float().mean()) > 0.85, d

@@ -249,3 +249,36 @@ def test_pass_counts_of_the_benchmark_circuits_do_not_regress():
     assert readout(30, 2) <= 4                      # config 5 on one GPU
     plan = plan_sharded(30, 3, ansatz_gates(30, 2, final_ring=False))
     assert plan.n_swaps == 1 and sum(len(p) for k, p in plan.steps if k == "local") <= 4   # config 5 on 8 GPUs
+
+
+def test_lockstep_adjoint_training_equals_the_one_client_at_a_time_loop():
+    """All clients in one batch of states (row s * K + k -> parameter row k) follow the per-client loop; coordinates
+    whose gradient is zero up to rounding may differ by Adam-sized steps, everything else agrees."""
+    import math
+    from qfedx_b200.fl import FederatedDataset
+    from qfedx_b200.fl.trainers_large import LargeVQCTrainer, PassBackend
+    from qfedx_b200.models import VQC
+    n, L = 5, 2
+    g = torch.Generator().manual_seed(3)
+    clients = [((torch.rand(7 + k, n, generator=g) * math.pi), torch.randint(0, 2, (7 + k,), generator=g)) for k in range(3)]
+    data = FederatedDataset.from_clients(clients, "cpu")
+    torch.manual_seed(0)
+    model = VQC(n, L, 2)
+    outs = []
+    for mode in ("seq", "lock"):
+        gen = torch.Generator().manual_seed(7)
+        tr = LargeVQCTrainer(model, data, PassBackend(n, L), epochs=2, batch_size=3, lr=0.05, grad_method="adjoint", generator=gen)
+        if mode == "seq":
+            outs.append(torch.stack([tr._train_one(tr.global_flat(), k)[0] for k in range(3)]))
+        else:
+            outs.append(tr._train_lockstep(tr.global_flat(), [0, 1, 2])[0])
+    d = (outs[0] - outs[1]).abs().flatten()
+    assert float(d.median()) < 1e-5 and float((d < 1e-3).float().mean()) > 0.85, d
+    # the batched gradient itself is exact: row r of the result is the gradient of the samples that used row r
+    vq = PassBackend(n, L).vqc
+    th = 0.3 * torch.randn(2, vq.n_params, generator=g)
+    ang = torch.rand(6, n, generator=g) * math.pi
+    cot = torch.randn(6, 1, generator=g)
+    gb = vq.adjoint_grad(ang, th, cot)
+    assert torch.allclose(gb[0], vq.adjoint_grad(ang[0::2], th[0], cot[0::2]), atol=1e-6)
+    assert torch.allclose(gb[1], vq.adjoint_grad(ang[1::2], th[1], cot[1::2]), atol=1e-6)
