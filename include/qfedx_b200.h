@@ -166,6 +166,19 @@ int qfx_fedavg_fused_multi_ex(const float* client_params, const float* global_in
                               int rank, int world, long long* const* recv_slots,
                               unsigned int* const* flags, unsigned int epoch, int two_shot, cudaStream_t stream);
 
+/* K7 across GPUs through the NVSwitch reduction (NVLS): every rank's partial stays in its own row `partial` of a buffer
+ * bound to a multicast object over the job's GPUs; the owner of a slice reads the sum of all W rows with
+ * multimem.ld_reduce on `partial_mc` (the multicast address of the same row), applies the server update and broadcasts
+ * the slice with multimem.st on `out_mc`.  partial: dim words of 4 bytes (8 with secagg); out: dim floats; global_out
+ * may be `out` itself (no copy).  flags as for qfx_fedavg_fused_multi_ex. */
+int qfx_fedavg_fused_multi_nvls(const float* client_params, const float* global_in, float* global_out,
+                                const float* weights, const int* participate, const int* client_gids,
+                                int k_local, int k_global, int dim, int mode, int n_wrap, float clip,
+                                float sigma, float server_lr, unsigned long long seed, int round, int secagg,
+                                const unsigned long long* pair_keys, float* norms_out, float* scratch,
+                                int rank, int world, void* partial, const void* partial_mc, float* out,
+                                float* out_mc, unsigned int* const* flags, unsigned int epoch, cudaStream_t stream);
+
 /* Loopback world for tests on a single GPU: `world` logical ranks of K7's multi-GPU path in ONE cooperative launch
  * (blockIdx.y = rank; every "rank's" receive slots and flag words live in this GPU's memory).  client_params, client_gids,
  * k_local, global_out and scratch are HOST arrays with one entry per rank; args_dev is world * 512 bytes of device scratch. */

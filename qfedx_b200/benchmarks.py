@@ -147,27 +147,37 @@ def large_state_throughput(n=20, L=2, batch=16, tile_bits=12, low_bits=3, regist
 
 
 def multi_gpu_aggregation(rank, world, dev, D=100_000_000 // 8 * 8, iters=5):
-    """K7 across GPUs (peer stores + flags inside the cooperative launch) against NCCL all_reduce on a 1e8-float
-    vector: every rank holds ONE client row, plain FedAvg of weights (one sweep), max time over ranks."""
+    """K7 across GPUs inside one cooperative launch (in-switch reduction where the job has a multicast object, else
+    peer stores + loads) against NCCL all_reduce on a 1e8-float vector: every rank holds ONE client row, plain FedAvg
+    of weights (one sweep), max time over ranks.  The peer-store exchange is timed as well when NVLS was picked."""
     import torch.distributed as dist
     from .parallel.runtime import MultiGpuAggregator
     from .utils.timing import max_over_ranks
     fused = MultiGpuAggregator(rank, world, D, dev)
+    peer = MultiGpuAggregator(rank, world, D, dev, exchange="two_shot") if fused.exchange == "nvls" else None
     row = torch.randn(1, D, device=dev)
     glob = torch.zeros(D, device=dev)
     out = torch.empty(D, device=dev)
+    fout = fused.result_row if fused.exchange == "nvls" else out      # NVLS: the broadcast row is the result (no copy)
     w = torch.ones(world)
 
     def run_fused():
-        fused(row, glob, w, None, mode="weights", gids=[rank], out=out)
+        fused(row, glob, w, None, mode="weights", gids=[rank], out=fout)
+
+    def run_peer():
+        peer(row, glob, w, None, mode="weights", gids=[rank], out=out)
 
     def run_nccl():
         out.copy_(row[0])
         out.mul_(1.0 / world)
         dist.all_reduce(out)
 
-    res = {}
-    for name, fn in (("fused_ms", run_fused), ("nccl_all_reduce_ms", run_nccl)):
+    def run_nccl_only():
+        dist.all_reduce(out)
+
+    res = {"exchange": fused.exchange}
+    cases = [("fused_ms", run_fused), ("nccl_all_reduce_ms", run_nccl), ("nccl_all_reduce_alone_ms", run_nccl_only)] + ([("fused_peer_two_shot_ms", run_peer)] if peer else [])
+    for name, fn in cases:
         for _ in range(2):
             fn()
         torch.cuda.synchronize(); dist.barrier()
@@ -177,12 +187,12 @@ def multi_gpu_aggregation(rank, world, dev, D=100_000_000 // 8 * 8, iters=5):
             fn()
         e.record(); torch.cuda.synchronize()
         res[name] = max_over_ranks(s.elapsed_time(e) / iters)
-    run_fused(); a = out.clone(); run_nccl()
+    run_fused(); a = fout.clone(); run_nccl()
     res["max_abs_diff_vs_nccl"] = float((a - out).abs().max())
     res.update({"floats": D, "world": world,
                 "fused_algbw_gbs": D * 4 / res["fused_ms"] / 1e6, "nccl_algbw_gbs": D * 4 / res["nccl_all_reduce_ms"] / 1e6,
                 "fused_vs_nccl": res["nccl_all_reduce_ms"] / res["fused_ms"]})
-    del fused
+    del fused, peer
     torch.cuda.empty_cache()
     return res
 

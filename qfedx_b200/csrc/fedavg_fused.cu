@@ -59,8 +59,40 @@ struct AggArgs {
                                    //    sweep over the client rows (slice o of the partial goes straight into rank o's
                                    //    buffer), local reduce + update of the own slice, then every rank gathers the other
                                    //    slices by peer loads (two barriers, 2 (W-1)/W D words over NVLink per rank
-                                   //    instead of (W-1) D; buffer: (W + 1) * ceil(D / W) words per rank)
+                                   //    instead of (W-1) D; buffer: (W + 1) * ceil(D / W) words per rank).  2: NVLS -
+                                   //    the partial stays in this rank's own multicast-bound buffer, the owner of a slice
+                                   //    gets the sum of all W partials from the switch (multimem.ld_reduce) and broadcasts
+                                   //    the updated slice with one multimem.st: (W-1)/W D + D/W words per direction and
+                                   //    rank, half of the peer-store exchange, and no reduction work on the SMs
+    void* nvls_partial;            // this rank's partial row [dim] (float, or int64 with secagg): unicast address
+    const void* nvls_partial_mc;   // multicast address of the same buffer (every rank's copy behind one address)
+    float* nvls_out;               // [dim] result row in the multicast-bound buffer: unicast address
+    float* nvls_out_mc;            // its multicast address
 };
+
+// Multicast (NVLS) accesses: the address names the same offset of every rank's buffer; the switch sums the W copies
+// on a load and replicates a store to all of them.
+__device__ __forceinline__ void mc_ld_reduce_f32x4(const float* mc, float (&x)[4]) {
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(x[0]), "=f"(x[1]), "=f"(x[2]), "=f"(x[3]) : "l"(mc) : "memory");
+}
+__device__ __forceinline__ float mc_ld_reduce_f32(const float* mc) {
+    float v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f32 %0, [%1];" : "=f"(v) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long mc_ld_reduce_u64(const long long* mc) {
+    unsigned long long v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u64 %0, [%1];" : "=l"(v) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void mc_st_f32x4(float* mc, const float (&x)[4]) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                 ::"l"(mc), "f"(x[0]), "f"(x[1]), "f"(x[2]), "f"(x[3]) : "memory");
+}
+__device__ __forceinline__ void mc_st_f32(float* mc, float v) {
+    asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(mc), "f"(v) : "memory");
+}
 
 __device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -239,7 +271,7 @@ __device__ __forceinline__ void fedavg_fused_body(const AggArgs& a, const int ma
     // ---- phase 2: weighted, noised, masked sum per element -----------------------------------
     // two-shot exchange: every rank starts its sweep at the slice of the NEXT rank, so that at any moment the W ranks
     // push to W different owners instead of all hammering rank 0's links first
-    const int rot = (a.world > 1 && a.two_shot) ? min(nvec - 1, ((a.rank + 1) % a.world) * ((nvec + a.world - 1) / a.world)) : 0;
+    const int rot = (a.world > 1 && a.two_shot == 1) ? min(nvec - 1, ((a.rank + 1) % a.world) * ((nvec + a.world - 1) / a.world)) : 0;
     for (int v0 = g0; v0 < nvec; v0 += UNR * gstride) {
         float g[UNR][VEC], facc[UNR][VEC];
         unsigned long long iacc[UNR][VEC];
@@ -324,7 +356,11 @@ __device__ __forceinline__ void fedavg_fused_body(const AggArgs& a, const int ma
                 }
                 IO::st(a.global_out + d, o);
             } else {
-                if (a.two_shot) {
+                if (a.two_shot == 2) {
+                    // NVLS: the partial stays at home; the switch reads it when the owner of the slice reduces
+                    if constexpr (FIXED) IO::st(reinterpret_cast<long long*>(a.nvls_partial) + d, iacc[u]);
+                    else IO::st(reinterpret_cast<float*>(a.nvls_partial) + d, facc[u]);
+                } else if (a.two_shot) {
                     // reduce-scatter by peer stores, overlapped with this sweep over the client rows: vector v belongs to
                     // rank o = v / chunk, whose buffer holds one row per source rank: [W][chunk] vectors (region 0)
                     const int chunk = (nvec + a.world - 1) / a.world;
@@ -353,6 +389,58 @@ __device__ __forceinline__ void fedavg_fused_body(const AggArgs& a, const int ma
         while ((int)(ld_acquire_sys(f) - a.epoch) < 0) { __nanosleep(64); }
     }
     grid.sync();
+    if (a.two_shot == 2) {
+        // ---- NVLS: in-switch sum of the W partials of this rank's slice, update, broadcast store -------------------
+        const int chunk = (nvec + a.world - 1) / a.world;
+        const int lo = min(nvec, a.rank * chunk), hi = min(nvec, lo + chunk);
+        constexpr int NU = 4;                                  // independent multicast loads in flight per thread
+        for (int v0 = lo + g0; v0 < hi; v0 += NU * gstride) {
+            float upd[NU][VEC], g[NU][VEC];
+#pragma unroll
+            for (int u = 0; u < NU; ++u) {
+                const int v = min(v0 + u * gstride, hi - 1);
+                const size_t d = (size_t)v * VEC;
+                if constexpr (FIXED) {
+#pragma unroll
+                    for (int e = 0; e < VEC; ++e) {
+                        const unsigned long long sacc = mc_ld_reduce_u64(reinterpret_cast<const long long*>(a.nvls_partial_mc) + d + e);
+                        upd[u][e] = (float)((double)(long long)sacc / FIXED_SCALE);
+                    }
+                } else if constexpr (VEC == 4) {
+                    mc_ld_reduce_f32x4(reinterpret_cast<const float*>(a.nvls_partial_mc) + d, upd[u]);
+                } else {
+                    upd[u][0] = mc_ld_reduce_f32(reinterpret_cast<const float*>(a.nvls_partial_mc) + d);
+                }
+                IO::ld(a.global_in + d, g[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < NU; ++u) {
+                const int v = v0 + u * gstride;
+                if (v >= hi) continue;
+                float o[VEC];
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) o[e] = (a.mode == 1) ? g[u][e] + a.server_lr * upd[u][e] : upd[u][e];
+                if constexpr (VEC == 4) mc_st_f32x4(a.nvls_out_mc + (size_t)v * VEC, o);
+                else mc_st_f32(a.nvls_out_mc + (size_t)v * VEC, o[0]);
+            }
+        }
+        __threadfence_system();
+        grid.sync();
+        if (blockIdx.x == 0 && tid < a.world) st_release_sys(a.flags[tid] + AGG_MAX_WORLD + a.rank, a.epoch);
+        if (blockIdx.x == 0 && tid < a.world) {
+            const unsigned int* f = a.flags[a.rank] + AGG_MAX_WORLD + tid;
+            while ((int)(ld_acquire_sys(f) - a.epoch) < 0) { __nanosleep(64); }
+        }
+        grid.sync();
+        if (a.global_out != a.nvls_out) {                      // callers that read the result row in place skip the copy
+            for (int v = g0; v < nvec; v += gstride) {
+                float t[VEC];
+                IO::ldcv(a.nvls_out + (size_t)v * VEC, t);
+                IO::st(a.global_out + (size_t)v * VEC, t);
+            }
+        }
+        return;
+    }
     if (a.two_shot) {
         // ---- the W partial rows of this rank's slice [lo, hi) arrived by peer stores: reduce them locally --------
         const int chunk = (nvec + a.world - 1) / a.world;
@@ -475,7 +563,11 @@ static int launch_fedavg(AggArgs& a, cudaStream_t stream) {
                   "clip/noise need delta mode");
     QFX_ARG_CHECK(a.world >= 1 && a.world <= AGG_MAX_WORLD && a.rank >= 0 && a.rank < a.world, QFX_ERR_BAD_ARG,
                   "bad rank/world");
-    QFX_ARG_CHECK(a.world == 1 || (a.recv_slots && a.flags), QFX_ERR_BAD_ARG, "multi-GPU needs slots and flags");
+    if (a.world > 1 && a.two_shot == 2)
+        QFX_ARG_CHECK(a.flags && a.nvls_partial && a.nvls_partial_mc && a.nvls_out && a.nvls_out_mc, QFX_ERR_BAD_ARG,
+                      "the NVLS exchange needs flags and the unicast + multicast addresses of the partial and result rows");
+    else
+        QFX_ARG_CHECK(a.world == 1 || (a.recv_slots && a.flags), QFX_ERR_BAD_ARG, "multi-GPU needs slots and flags");
     QFX_ARG_CHECK(a.scratch != nullptr, QFX_ERR_BAD_ARG, "scratch is required");
     const int num_sms = device_sm_count();
     QFX_ARG_CHECK(num_sms > 0, QFX_ERR_UNSUPPORTED, "cannot query the SM count of the current device");
@@ -487,7 +579,9 @@ static int launch_fedavg(AggArgs& a, cudaStream_t stream) {
     if (a.k_local > 0) QFX_CUDA_TRY(cudaMemsetAsync(a.scratch, 0, sizeof(float) * a.k_local, stream));
     // 16-byte accesses when every row starts on a 16-byte boundary
     auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
-    const bool vec4 = a.dim % 4 == 0 && al16(a.client_params) && al16(a.global_in) && al16(a.global_out);
+    const bool nvls = a.world > 1 && a.two_shot == 2;
+    const bool vec4 = a.dim % 4 == 0 && al16(a.client_params) && al16(a.global_in) && al16(a.global_out) &&
+                      (!nvls || (al16(a.nvls_partial) && al16(a.nvls_partial_mc) && al16(a.nvls_out) && al16(a.nvls_out_mc)));
     const bool fixed = a.secagg != 0;
     AggKernel kern = vec4 ? (fixed ? (AggKernel)fedavg_fused_kernel<4, 2, true> : (AggKernel)fedavg_fused_kernel<4, 2, false>)
                           : (fixed ? (AggKernel)fedavg_fused_kernel<1, 4, true> : (AggKernel)fedavg_fused_kernel<1, 4, false>);
@@ -626,6 +720,31 @@ extern "C" int qfx_fedavg_fused_multi_ex(const float* client_params, const float
     a.norms_out = norms_out; a.scratch = scratch; a.masked_out = nullptr; a.pair_keys = pair_keys;
     a.rank = rank; a.world = world; a.recv_slots = recv_slots; a.flags = flags; a.epoch = epoch;
     a.two_shot = two_shot ? 1 : 0;
+    return launch_fedavg(a, stream);
+}
+
+// K7 across GPUs through the NVSwitch reduction (NVLS).  partial / out are rows of dim words (partial: 8 bytes per word
+// with secagg, else 4) in buffers bound to a multicast object that spans the job's GPUs; *_mc is the multicast address
+// of the same row (parallel/runtime.py takes both from torch's symmetric memory rendezvous).  The result lands in
+// out on every rank; global_out may be out itself (no copy) or any other row (copied at the end of the launch).
+extern "C" int qfx_fedavg_fused_multi_nvls(const float* client_params, const float* global_in, float* global_out,
+                                           const float* weights, const int* participate, const int* client_gids,
+                                           int k_local, int k_global, int dim, int mode, int n_wrap, float clip,
+                                           float sigma, float server_lr, unsigned long long seed, int round, int secagg,
+                                           const unsigned long long* pair_keys, float* norms_out, float* scratch,
+                                           int rank, int world, void* partial, const void* partial_mc, float* out,
+                                           float* out_mc, unsigned int* const* flags, unsigned int epoch,
+                                           cudaStream_t stream) {
+    AggArgs a = {};
+    a.client_params = client_params; a.global_in = global_in; a.global_out = global_out;
+    a.weights = weights; a.participate = participate; a.client_gids = client_gids;
+    a.k_local = k_local; a.k_global = k_global; a.dim = dim; a.mode = mode; a.n_wrap = n_wrap;
+    a.clip = clip; a.sigma = sigma; a.server_lr = server_lr; a.seed = seed; a.round = round; a.secagg = secagg;
+    a.norms_out = norms_out; a.scratch = scratch; a.masked_out = nullptr; a.pair_keys = pair_keys;
+    a.rank = rank; a.world = world; a.recv_slots = nullptr; a.flags = flags; a.epoch = epoch;
+    a.two_shot = 2;
+    a.nvls_partial = partial; a.nvls_partial_mc = partial_mc; a.nvls_out = out; a.nvls_out_mc = out_mc;
+    QFX_ARG_CHECK(world >= 2, QFX_ERR_BAD_ARG, "the NVLS exchange is a multi-GPU path");
     return launch_fedavg(a, stream);
 }
 

@@ -60,3 +60,32 @@ class SymmetricBuffer:
 
     def peer_table(self, offset_bytes: int = 0) -> torch.Tensor:
         return (self.ptr_table + offset_bytes).contiguous()
+
+
+class MulticastBuffer:
+    """A buffer of ``nbytes`` on every rank bound to ONE multicast object over the job's GPUs (NVLS): ``mc_ptr`` names
+    the same offset of all copies at once - ``multimem.ld_reduce`` on it returns the sum over the ranks computed in the
+    NVSwitch, ``multimem.st`` writes all copies.  Allocation, handle exchange and the multicast binding are torch's
+    symmetric-memory rendezvous (plumbing only); the kernels that use the addresses are ours (csrc/fedavg_fused.cu).
+    ``available`` is False where the driver or fabric has no multicast support - callers fall back to peer stores."""
+
+    def __init__(self, nbytes: int, device: torch.device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.nbytes, self.device = nbytes, device
+        group = group if group is not None else dist.group.WORLD
+        self.local = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
+        self.handle = symm_mem.rendezvous(self.local, group)
+        self.local_ptr = self.local.data_ptr()
+        self.mc_ptr = int(getattr(self.handle, "multicast_ptr", 0) or 0)
+        ok = torch.tensor([1 if self.mc_ptr else 0], device=device, dtype=torch.int32)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+        self.available = bool(int(ok))
+
+    @staticmethod
+    def supported(device: torch.device) -> bool:
+        try:
+            from torch._C._distributed_c10d import _SymmetricMemory
+            from torch._C._autograd import DeviceType
+            return bool(_SymmetricMemory.has_multicast_support(DeviceType.CUDA, device.index or 0))
+        except Exception:
+            return False

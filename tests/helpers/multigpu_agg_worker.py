@@ -9,7 +9,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspa
 from qfedx_b200.parallel.runtime import MultiGpuAggregator, NcclAggregator, local_clients  # noqa: E402
 
 
-def check(rank, world, dev, K, D, secagg, clip, two_shot):
+def check(rank, world, dev, K, D, secagg, clip, exchange):
     ok = True
     g = torch.Generator().manual_seed(1234 + K + D)                  # same stream on every rank
     glob = torch.randn(D, generator=g)
@@ -20,7 +20,7 @@ def check(rank, world, dev, K, D, secagg, clip, two_shot):
     mine = local_clients(rank, K, world)
     rows = [k for k in mine if part[k]]
     cp = cp_all[rows].to(dev) if rows else None
-    fused = MultiGpuAggregator(rank, world, D, dev, two_shot=two_shot)
+    fused = MultiGpuAggregator(rank, world, D, dev, exchange=exchange)
     base = NcclAggregator(rank, world, D, dev)
     b = None
     for rnd in range(3):                                                 # several epochs: flags, slot parity
@@ -35,7 +35,7 @@ def check(rank, world, dev, K, D, secagg, clip, two_shot):
         same = all(torch.equal(gathered[0], t) for t in gathered)
         if err > 3e-5 or not same:
             ok = False
-            print(f"rank {rank}: K={K} D={D} secagg={secagg} two_shot={two_shot} round {rnd}: err={err:.3e} identical={same}", flush=True)
+            print(f"rank {rank}: K={K} D={D} secagg={secagg} exchange={exchange} round {rnd}: err={err:.3e} identical={same}", flush=True)
     # back-to-back rounds with every rank delayed by a different random amount before each launch: a fast
     # rank runs ahead into the next epoch while a slow one is still reducing the previous slots
     skew = torch.Generator().manual_seed(99 + rank)
@@ -49,7 +49,7 @@ def check(rank, world, dev, K, D, secagg, clip, two_shot):
         err = float((a - b).abs().max())
         if err > 3e-5:
             ok = False
-            print(f"rank {rank}: K={K} D={D} secagg={secagg} two_shot={two_shot} skewed round {i}: err={err:.3e}", flush=True)
+            print(f"rank {rank}: K={K} D={D} secagg={secagg} exchange={exchange} skewed round {i}: err={err:.3e}", flush=True)
     del fused
     return ok
 
@@ -60,9 +60,15 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
     ok = True
+    from qfedx_b200.parallel.symm import MulticastBuffer
+    sup = torch.tensor([1 if MulticastBuffer.supported(dev) else 0], device=dev, dtype=torch.int32)
+    dist.all_reduce(sup, op=dist.ReduceOp.MIN)
+    exchanges = ("one_shot", "two_shot") + (("nvls",) if int(sup) else ())
+    if rank == 0:
+        print("exchanges under test:", exchanges, flush=True)
     for K, D, secagg, clip in [(16, 102, False, 0.0), (16, 4096, False, 0.7), (16, 113859, False, 0.7), (8, 5000, True, 0.7), (5, 300, True, 0.0)]:
-        for two_shot in (False, True):                                   # both exchange algorithms
-            ok = check(rank, world, dev, K, D, secagg, clip, two_shot) and ok
+        for exchange in exchanges:                                       # every exchange algorithm the box supports
+            ok = check(rank, world, dev, K, D, secagg, clip, exchange) and ok
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:
