@@ -314,17 +314,41 @@ struct PassArgsV2 {
 constexpr int V2_PLAN_MAX = 1 + 4 * (13 + 4 * MAX_OPS_PER_PASS / 2) + MAX_OPS_PER_PASS + 1;
 constexpr int V2_KIND_RXRZ_STRIPPED = 7;   // plan-private op kind: RXRZ on a register bit without its scalar phase
 
+// The kernel is persistent over the tiles of one state: a CTA sets up its gate matrices and op stream once, then walks
+// tiles blockIdx.x, blockIdx.x + gridDim.x, ...; the NEXT tile is fetched with cp.async into the other half of a
+// double-buffered shared-memory tile while the current one is worked on in registers, so global loads, gate math and
+// the stores of the previous tile overlap inside one CTA instead of only across the three CTAs of an SM.
+__device__ __forceinline__ void cp_async_8(void* smem_dst, const void* gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit_wait_all() {
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
 __global__ void __launch_bounds__(PASS_THREADS, 3)
 sv_large_pass_v2_kernel(const PassArgsV2 pa) {
     const PassArgs& a = pa.base;
-    __shared__ __align__(16) float2 tile[1 << V2_T];
+    extern __shared__ __align__(16) float2 tiles2[];            // two tiles of 2^V2_T amplitudes
     __shared__ float2 mats[MAX_OPS_PER_PASS][4];
-    __shared__ int splan[V2_PLAN_MAX];
+    __shared__ short splan[V2_PLAN_MAX];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, batch = blockIdx.y;
     float2* st = a.states + ((size_t)batch << a.n_qubits);
-    for (int i = tid; i < pa.plan_len; i += PASS_THREADS) splan[i] = pa.plan[i];   // op stream out of global memory
+    const unsigned n_tiles = 1u << (a.n_qubits - V2_T);
+    __shared__ unsigned long long koff[16];
+    if (tid < 16) koff[tid] = deposit_bits((unsigned)tid, 8, V2_T - 8, a.tile_q);
+    const unsigned long long tlow = deposit_bits((unsigned)tid, 0, 8, a.tile_q);
+    __syncthreads();
+    // first tile on its way before the set-up below touches global memory
+    if (!a.init_zero_state && blockIdx.x < n_tiles) {
+        const unsigned long long toff = tile_base(a, blockIdx.x) | tlow;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) cp_async_8(&tiles2[v2_swz(tid + 256 * k)], st + (toff | koff[k]));
+    }
+    for (int i = tid; i < pa.plan_len; i += PASS_THREADS) splan[i] = (short)pa.plan[i];   // op stream out of global memory
     // plan[0] = n_seg | has_trailer << 16; trailer = n_ops op modes (0 general, 1 stripped RXRZ, 2 carrier) + carrier
-    const bool has_modes = (pa.plan[0] >> 16) & 1;
+    const int plan0 = pa.plan[0];
+    const bool has_modes = (plan0 >> 16) & 1;
     const int* gmodes = pa.plan + pa.plan_len - a.n_ops - 1;
     for (int i = tid; i < a.n_ops; i += PASS_THREADS) {
         if (has_modes && gmodes[i] == 1) {
@@ -356,28 +380,33 @@ sv_large_pass_v2_kernel(const PassArgsV2 pa) {
             mats[carrier][tid] = make_float2(cg * v.x - sg * v.y, cg * v.y + sg * v.x);
         }
     }
-    const unsigned long long base = tile_base(a, blockIdx.x);
-    __shared__ unsigned long long koff[16];
-    if (tid < 16) koff[tid] = deposit_bits((unsigned)tid, 8, V2_T - 8, a.tile_q);
-    const unsigned long long toff = base | deposit_bits((unsigned)tid, 0, 8, a.tile_q);
-    __syncthreads();
     // tile element j lives at v2_swz(j): low nibble XOR-ed with the two higher nibbles (linear over GF(2), so the
     // address of a union of disjoint bit sets is the XOR of their addresses).  Any segment whose lane bits cover
     // the four classes mod 4 then reads and writes its layout without bank conflicts.
+    int parity = 0;
+    for (unsigned t = blockIdx.x; t < n_tiles; t += gridDim.x, parity ^= 1) {
+    float2* tile = tiles2 + (parity << V2_T);
+    const unsigned long long toff = tile_base(a, t) | tlow;
+    cp_async_commit_wait_all();      // this thread's pieces of tile t have landed
+    __syncthreads();                 // ... everybody's; and every thread is done reading the other buffer (stores of t - 1)
+    if (a.init_zero_state) {
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        const unsigned long long off = toff | koff[k];
-        tile[v2_swz(tid + 256 * k)] = a.init_zero_state ? make_float2((off == 0ull) ? 1.f : 0.f, 0.f) : st[off];
+        for (int k = 0; k < 16; ++k) tile[v2_swz(tid + 256 * k)] = make_float2(((toff | koff[k]) == 0ull) ? 1.f : 0.f, 0.f);
+        __syncthreads();
+    } else if (t + gridDim.x < n_tiles) {
+        float2* nxt = tiles2 + ((parity ^ 1) << V2_T);
+        const unsigned long long noff = tile_base(a, t + gridDim.x) | tlow;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) cp_async_8(&nxt[v2_swz(tid + 256 * k)], st + (noff | koff[k]));
     }
-    __syncthreads();
 
-    const int* plan = splan;
-    const int n_seg = plan[0] & 0xFFFF;
+    const short* plan = splan;
+    const int n_seg = plan0 & 0xFFFF;
     int cur = 1;
     for (int sg = 0; sg < n_seg; ++sg) {
-        const int* p2b = plan + cur;          // position -> tile bit
+        const short* p2b = plan + cur;          // position -> tile bit
         const int n_ops = plan[cur + 12];
-        const int* ops = plan + cur + 13;
+        const short* ops = plan + cur + 13;
         cur += 13 + 4 * n_ops;
         // tile index of (warp, lane, register r)
         int bwl = 0;
@@ -464,6 +493,7 @@ sv_large_pass_v2_kernel(const PassArgsV2 pa) {
     }
 #pragma unroll
     for (int k = 0; k < 16; ++k) st[toff | koff[k]] = tile[v2_swz(tid + 256 * k)];
+    }   // tiles of this CTA
 }
 
 // <Z_q> for q < n_local taken from the index bits, for q >= n_local from `high_bits` (the rank)
@@ -866,7 +896,23 @@ extern "C" int qfx_sv_large_pass(float* states, int n_qubits, int batch, int til
         pa.base = a;
         pa.plan = plan_dev;
         pa.plan_len = plan_len;
-        sv_large_pass_v2_kernel<<<grid, PASS_THREADS, 0, stream>>>(pa);
+        // persistent over tiles: as many CTAs as are resident at once (3 per SM), each walking its share of one
+        // state's tiles with the next tile prefetched into the second half of the dynamic shared memory
+        constexpr int kTilesSmem = 2 * (int)(sizeof(float2) << V2_T);
+        static PerDeviceFlag attr_set;
+        if (!attr_set.here()) {
+            QFX_CUDA_TRY(cudaFuncSetAttribute((const void*)sv_large_pass_v2_kernel,
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize, kTilesSmem));
+            attr_set.here() = true;
+        }
+        // CTAs per state: at least 16 tiles each (the set-up is paid once per CTA), at least one resident wave in
+        // total, and - when one state's share of the GPU is more than one CTA - a whole number of waves
+        const unsigned resident = (unsigned)num_sms() * 3u;
+        const unsigned per = resident / (unsigned)batch > 0u ? resident / (unsigned)batch : 1u;
+        unsigned gx = grid.x / 16u > per ? grid.x / 16u : per;
+        if ((unsigned)batch <= resident) gx = (gx + per - 1u) / per * per;
+        if (gx > grid.x) gx = grid.x;
+        sv_large_pass_v2_kernel<<<dim3(gx, batch), PASS_THREADS, kTilesSmem, stream>>>(pa);
         return check_launch("sv_large_pass_v2_kernel");
     }
     sv_large_pass_kernel<<<grid, PASS_THREADS, smem, stream>>>(a);
