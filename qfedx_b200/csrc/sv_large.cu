@@ -6,7 +6,7 @@
 //     independent states (clients, or the 2P shifted circuits of the parameter-shift rule, each
 //     with its own angle shift), so a 20-qubit state (8 MiB, L2-resident on B200) is re-read from
 //     L2 rather than HBM between passes.
-// K3' sv_large_expz_kernel   <Z_q> for every qubit, with the shard's rank bits as high index bits.
+// K3' sv_large_expz_masks_kernel   <Z-string> readouts (<Z_q> = one-bit masks), the shard's rank bits as high index bits.
 // K6  sv_global_swap_fused_kernel   sharded statevector: the top g "global" qubits are the rank
 //     index.  Exchanging them with the top g local qubits is an all-to-all of contiguous slices;
 //     each thread PULLS its 2^g amplitudes from the 2^g peers with plain loads over NVLink (peer
@@ -496,66 +496,74 @@ sv_large_pass_v2_kernel(const PassArgsV2 pa) {
     }   // tiles of this CTA
 }
 
-// <Z_q> for q < n_local taken from the index bits, for q >= n_local from `high_bits` (the rank)
-__global__ void __launch_bounds__(256)
-sv_large_expz_kernel(const float2* __restrict__ states, int n_local, int n_total, unsigned int high_bits,
-                     float* __restrict__ out /*[batch][n_total]*/) {
-    __shared__ float red[32];
-    const int batch = blockIdx.y, tid = threadIdx.x;
-    const float2* st = states + ((size_t)batch << n_local);
-    const size_t N = (size_t)1 << n_local;
-    float acc[32];
-#pragma unroll
-    for (int q = 0; q < 32; ++q) acc[q] = 0.f;
-    float tot = 0.f;
-    for (size_t i = (size_t)blockIdx.x * 256 + tid; i < N; i += (size_t)gridDim.x * 256) {
-        const float2 v = st[i];
-        const float p = v.x * v.x + v.y * v.y;
-        tot += p;
-#pragma unroll
-        for (int q = 0; q < 32; ++q)
-            if (q < n_local) acc[q] += ((i >> q) & 1) ? -p : p;
-    }
-    if (tid < 32) red[tid] = 0.f;
-    __syncthreads();
-#pragma unroll
-    for (int q = 0; q < 32; ++q) {
-        if (q < n_total) {
-            float v = q < n_local ? acc[q] : (((high_bits >> (q - n_local)) & 1u) ? -tot : tot);
-            v = warp_sum(v);
-            if ((tid & 31) == 0) atomicAdd(&red[q], v);
-        }
-    }
-    __syncthreads();
-    if (tid < n_total) atomicAdd(out + (size_t)batch * n_total + tid, red[tid]);
-}
-
 // <Z-string> readout: out[q] = sum_i |psi_i|^2 (-1)^{parity(idx & masks[q])} with idx = high_bits << n_local | i.
 // A trailing CNOT ring only permutes basis states, so <Z_q> after it equals a parity readout before it
 // (Z_t -> Z_c Z_t under CNOT(c,t)): the ring's passes - and for a sharded state its swaps - are never run.
 struct MaskArgs { unsigned long long m[32]; };
-__global__ void __launch_bounds__(256)
+// The n_out parities of one basis index form a GF(2)-linear map of its bits: signs(idx) = XOR over the bytes of idx of
+// a 256-entry table (bit q of an entry = parity(byte & byte of mask q)).  A thread's low index byte never changes,
+// so per amplitude the sign word costs one shared-memory lookup per remaining byte instead of n_out 64-bit
+// popcounts (which made the kernel XU-bound at 75 % before it was anywhere near the memory system).
+__global__ void __launch_bounds__(256, 4)
 sv_large_expz_masks_kernel(const float2* __restrict__ states, int n_local, int n_out, unsigned int high_bits,
                            const MaskArgs masks, float* __restrict__ out /*[batch][n_out]*/) {
     __shared__ float red[32];
+    __shared__ unsigned int tab[4][256];                       // index bits 9..16, 17..24, 25..32, 33..40
     const int batch = blockIdx.y, tid = threadIdx.x;
-    const float2* st = states + ((size_t)batch << n_local);
-    const size_t N = (size_t)1 << n_local;
+    const float4* st = reinterpret_cast<const float4*>(states + ((size_t)batch << n_local));   // two amplitudes per load
+    const size_t N2 = (size_t)1 << (n_local - 1);
     const unsigned long long hi = (unsigned long long)high_bits << n_local;
+    __shared__ unsigned int col[64];                           // col[b]: bit q set iff mask q contains index bit b
+    if (tid < 64) {
+        unsigned int w = 0u;
+        for (int q = 0; q < n_out; ++q) w |= (unsigned)((masks.m[q] >> tid) & 1ull) << q;
+        col[tid] = w;
+    }
+    __syncthreads();
+    for (int e = tid; e < 4 * 256; e += 256) {
+        const int b0 = 9 + 8 * (e >> 8);
+        unsigned int w = 0u;
+#pragma unroll
+        for (int b = 0; b < 8; ++b)
+            if ((e >> b) & 1) w ^= col[b0 + b];
+        tab[e >> 8][e & 255] = w;
+    }
+    // the thread's own nine low index bits (2 * tid: the pair index strides by multiples of 256), the bits of `hi`
+    // below bit 9 and above bit 40; c0 = the sign change from the even to the odd amplitude of a pair
+    unsigned int s_fixed = 0u;
+    const unsigned int c0 = col[0];
+    for (unsigned long long fixed = (unsigned long long)(2 * tid) | (hi & 511ull) | (hi & ~((1ull << 41) - 1ull)); fixed;
+         fixed &= fixed - 1ull)
+        s_fixed ^= col[__ffsll((long long)fixed) - 1];
+    if (tid < 32) red[tid] = 0.f;
+    __syncthreads();
     float acc[32];
 #pragma unroll
     for (int q = 0; q < 32; ++q) acc[q] = 0.f;
-    for (size_t i = (size_t)blockIdx.x * 256 + tid; i < N; i += (size_t)gridDim.x * 256) {
-        const float2 v = st[i];
-        const float p = v.x * v.x + v.y * v.y;
-        const unsigned long long idx = hi | i;
+    constexpr int UN = 4;                                      // independent 16-byte loads in flight per thread
+    const size_t stride = (size_t)gridDim.x * 256;
+    for (size_t i0 = (size_t)blockIdx.x * 256 + tid; i0 < N2; i0 += UN * stride) {
+        float4 v[UN];
 #pragma unroll
-        for (int q = 0; q < 32; ++q)
-            if (q < n_out)                                       // uniform; sign bit of p flipped by the parity
-                acc[q] += __uint_as_float(__float_as_uint(p) ^ ((unsigned)(__popcll(idx & masks.m[q]) & 1) << 31));
+        for (int u = 0; u < UN; ++u) {
+            const size_t i = i0 + u * stride;
+            v[u] = i < N2 ? __ldcs(st + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < UN; ++u) {
+            const unsigned long long up = (hi | ((i0 + u * stride) << 1)) >> 9;
+            const unsigned int sg = s_fixed ^ tab[0][up & 255] ^ tab[1][(up >> 8) & 255] ^ tab[2][(up >> 16) & 255] ^
+                                    tab[3][(up >> 24) & 255];
+            const unsigned int sg1 = sg ^ c0;
+            const unsigned int pa = __float_as_uint(v[u].x * v[u].x + v[u].y * v[u].y);
+            const unsigned int pb = __float_as_uint(v[u].z * v[u].z + v[u].w * v[u].w);
+#pragma unroll
+            for (int q = 0; q < 32; ++q)
+                if (q < n_out)                                   // uniform; sign bit of p flipped by the parity
+                    acc[q] += __uint_as_float(pa ^ ((sg << (31 - q)) & 0x80000000u)) +
+                              __uint_as_float(pb ^ ((sg1 << (31 - q)) & 0x80000000u));
+        }
     }
-    if (tid < 32) red[tid] = 0.f;
-    __syncthreads();
 #pragma unroll
     for (int q = 0; q < 32; ++q) {
         if (q < n_out) {
@@ -919,16 +927,29 @@ extern "C" int qfx_sv_large_pass(float* states, int n_qubits, int batch, int til
     return check_launch("sv_large_pass_kernel");
 }
 
+static int launch_expz_masks(const float* states, int n_local, int n_out, unsigned int high_bits, const MaskArgs& m,
+                             int batch, float* out, cudaStream_t stream) {
+    QFX_CUDA_TRY(cudaMemsetAsync(out, 0, sizeof(float) * (size_t)batch * n_out, stream));
+    // one resident wave: the per-CTA tables are paid once and no tail wave trails the others
+    int occ = 0;
+    QFX_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)sv_large_expz_masks_kernel, 256, 0));
+    size_t blocks = (((size_t)1 << n_local) + 256 * 8 - 1) / (256 * 8);     // a thread takes 4 pairs per trip
+    size_t cap = (size_t)num_sms() * (size_t)(occ > 0 ? occ : 1) / (size_t)batch;
+    if (cap < 1) cap = 1;
+    if (blocks > cap) blocks = cap;
+    sv_large_expz_masks_kernel<<<dim3((unsigned)blocks, batch), 256, 0, stream>>>(
+        reinterpret_cast<const float2*>(states), n_local, n_out, high_bits, m, out);
+    return check_launch("sv_large_expz_masks_kernel");
+}
+
+// <Z_q> of every qubit = the Z-string readout with one-bit masks (q >= n_local: the bit comes from `high_bits`)
 extern "C" int qfx_sv_large_expz(const float* states, int n_local, int n_total, unsigned int high_bits, int batch,
                                  float* out, cudaStream_t stream) {
     QFX_ARG_CHECK(n_local >= 1 && n_total >= n_local && n_total <= 32, QFX_ERR_BAD_ARG, "bad qubit counts");
-    QFX_CUDA_TRY(cudaMemsetAsync(out, 0, sizeof(float) * (size_t)batch * n_total, stream));
-    size_t blocks = (((size_t)1 << n_local) + 256 * 8 - 1) / (256 * 8);
-    const size_t cap = (size_t)num_sms() * 8 / (batch > 8 ? 8 : batch) + 1;
-    if (blocks > cap) blocks = cap;
-    sv_large_expz_kernel<<<dim3((unsigned)blocks, batch), 256, 0, stream>>>(reinterpret_cast<const float2*>(states),
-                                                                          n_local, n_total, high_bits, out);
-    return check_launch("sv_large_expz_kernel");
+    QFX_ARG_CHECK(batch >= 1 && batch <= 65535, QFX_ERR_BAD_ARG, "bad batch");
+    MaskArgs m = {};
+    for (int q = 0; q < n_total; ++q) m.m[q] = 1ull << q;
+    return launch_expz_masks(states, n_local, n_total, high_bits, m, batch, out, stream);
 }
 
 extern "C" int qfx_sv_large_expz_masks(const float* states, int n_local, int n_out, unsigned int high_bits,
@@ -938,13 +959,7 @@ extern "C" int qfx_sv_large_expz_masks(const float* states, int n_local, int n_o
     QFX_ARG_CHECK(masks_host != nullptr && batch >= 1 && batch <= 65535, QFX_ERR_BAD_ARG, "bad masks / batch");
     MaskArgs m = {};
     for (int q = 0; q < n_out; ++q) m.m[q] = masks_host[q];
-    QFX_CUDA_TRY(cudaMemsetAsync(out, 0, sizeof(float) * (size_t)batch * n_out, stream));
-    size_t blocks = (((size_t)1 << n_local) + 256 * 8 - 1) / (256 * 8);
-    const size_t cap = (size_t)num_sms() * 8 / (batch > 8 ? 8 : batch) + 1;
-    if (blocks > cap) blocks = cap;
-    sv_large_expz_masks_kernel<<<dim3((unsigned)blocks, batch), 256, 0, stream>>>(
-        reinterpret_cast<const float2*>(states), n_local, n_out, high_bits, m, out);
-    return check_launch("sv_large_expz_masks_kernel");
+    return launch_expz_masks(states, n_local, n_out, high_bits, m, batch, out, stream);
 }
 
 // CTAs per SM of the fused swap's grid (tuning knob, per device; results do not depend on it).  More CTAs keep more
