@@ -508,31 +508,37 @@ __global__ void __launch_bounds__(256, 4)
 sv_large_expz_masks_kernel(const float2* __restrict__ states, int n_local, int n_out, unsigned int high_bits,
                            const MaskArgs masks, float* __restrict__ out /*[batch][n_out]*/) {
     __shared__ float red[32];
-    __shared__ unsigned int tab[4][256];                       // index bits 9..16, 17..24, 25..32, 33..40
+    __shared__ unsigned int tab[4][256];                       // index bits 11..18, 19..26, 27..34, 35..42
+    __shared__ unsigned int col[64];                           // col[b]: bit q set iff mask q contains index bit b
+    __shared__ float sig[3][32];                               // +-1 per output for index bits 0, 9 and 10
     const int batch = blockIdx.y, tid = threadIdx.x;
     const float4* st = reinterpret_cast<const float4*>(states + ((size_t)batch << n_local));   // two amplitudes per load
     const size_t N2 = (size_t)1 << (n_local - 1);
     const unsigned long long hi = (unsigned long long)high_bits << n_local;
-    __shared__ unsigned int col[64];                           // col[b]: bit q set iff mask q contains index bit b
     if (tid < 64) {
         unsigned int w = 0u;
         for (int q = 0; q < n_out; ++q) w |= (unsigned)((masks.m[q] >> tid) & 1ull) << q;
         col[tid] = w;
     }
+    if (tid < 96) {
+        const int which = tid >> 5, q = tid & 31, bit = which == 0 ? 0 : 8 + which;
+        sig[which][q] = (q < n_out && ((masks.m[q] >> bit) & 1ull)) ? -1.f : 1.f;
+    }
     __syncthreads();
     for (int e = tid; e < 4 * 256; e += 256) {
-        const int b0 = 9 + 8 * (e >> 8);
+        const int b0 = 11 + 8 * (e >> 8);
         unsigned int w = 0u;
 #pragma unroll
         for (int b = 0; b < 8; ++b)
             if ((e >> b) & 1) w ^= col[b0 + b];
         tab[e >> 8][e & 255] = w;
     }
-    // the thread's own nine low index bits (2 * tid: the pair index strides by multiples of 256), the bits of `hi`
-    // below bit 9 and above bit 40; c0 = the sign change from the even to the odd amplitude of a pair
+    // A thread's trip covers the eight amplitudes that differ in index bits 0 (the two halves of a 16-byte load), 9
+    // and 10 (four loads 256 pairs apart): their |psi|^2 are folded with the outputs' +-1 for those three bits (seven
+    // FMAs per output instead of eight sign flips and adds), and the sign of everything else - the thread's own bits
+    // 1..8, the table bytes of the bits above 10, and the bits of `hi` the tables do not reach - is applied once.
     unsigned int s_fixed = 0u;
-    const unsigned int c0 = col[0];
-    for (unsigned long long fixed = (unsigned long long)(2 * tid) | (hi & 511ull) | (hi & ~((1ull << 41) - 1ull)); fixed;
+    for (unsigned long long fixed = (unsigned long long)(2 * tid) | (hi & 0x7ffull) | (hi & ~((1ull << 43) - 1ull)); fixed;
          fixed &= fixed - 1ull)
         s_fixed ^= col[__ffsll((long long)fixed) - 1];
     if (tid < 32) red[tid] = 0.f;
@@ -540,28 +546,28 @@ sv_large_expz_masks_kernel(const float2* __restrict__ states, int n_local, int n
     float acc[32];
 #pragma unroll
     for (int q = 0; q < 32; ++q) acc[q] = 0.f;
-    constexpr int UN = 4;                                      // independent 16-byte loads in flight per thread
-    const size_t stride = (size_t)gridDim.x * 256;
-    for (size_t i0 = (size_t)blockIdx.x * 256 + tid; i0 < N2; i0 += UN * stride) {
-        float4 v[UN];
+    const size_t n_groups = (N2 + 1023) >> 10;                  // groups of 4 x 256 pairs (index bits 0..10)
+    for (size_t grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
+        float pa[4], pb[4];
 #pragma unroll
-        for (int u = 0; u < UN; ++u) {
-            const size_t i = i0 + u * stride;
-            v[u] = i < N2 ? __ldcs(st + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int u = 0; u < 4; ++u) {
+            const size_t i = (grp << 10) + (size_t)u * 256 + tid;
+            const float4 v = i < N2 ? __ldcs(st + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+            pa[u] = v.x * v.x + v.y * v.y;
+            pb[u] = v.z * v.z + v.w * v.w;
         }
+        const unsigned long long up = (hi | (grp << 11)) >> 11;
+        const unsigned int sg = s_fixed ^ tab[0][up & 255] ^ tab[1][(up >> 8) & 255] ^ tab[2][(up >> 16) & 255] ^
+                                tab[3][(up >> 24) & 255];
 #pragma unroll
-        for (int u = 0; u < UN; ++u) {
-            const unsigned long long up = (hi | ((i0 + u * stride) << 1)) >> 9;
-            const unsigned int sg = s_fixed ^ tab[0][up & 255] ^ tab[1][(up >> 8) & 255] ^ tab[2][(up >> 16) & 255] ^
-                                    tab[3][(up >> 24) & 255];
-            const unsigned int sg1 = sg ^ c0;
-            const unsigned int pa = __float_as_uint(v[u].x * v[u].x + v[u].y * v[u].y);
-            const unsigned int pb = __float_as_uint(v[u].z * v[u].z + v[u].w * v[u].w);
-#pragma unroll
-            for (int q = 0; q < 32; ++q)
-                if (q < n_out)                                   // uniform; sign bit of p flipped by the parity
-                    acc[q] += __uint_as_float(pa ^ ((sg << (31 - q)) & 0x80000000u)) +
-                              __uint_as_float(pb ^ ((sg1 << (31 - q)) & 0x80000000u));
+        for (int q = 0; q < 32; ++q) {
+            if (q < n_out) {                                     // uniform
+                const float s0 = sig[0][q], s9 = sig[1][q], s10 = sig[2][q];
+                const float a0 = fmaf(s0, pb[0], pa[0]), a1 = fmaf(s0, pb[1], pa[1]);
+                const float a2 = fmaf(s0, pb[2], pa[2]), a3 = fmaf(s0, pb[3], pa[3]);
+                const float r = fmaf(s10, fmaf(s9, a3, a2), fmaf(s9, a1, a0));
+                acc[q] += __uint_as_float(__float_as_uint(r) ^ ((sg << (31 - q)) & 0x80000000u));
+            }
         }
     }
 #pragma unroll
@@ -933,7 +939,7 @@ static int launch_expz_masks(const float* states, int n_local, int n_out, unsign
     // one resident wave: the per-CTA tables are paid once and no tail wave trails the others
     int occ = 0;
     QFX_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)sv_large_expz_masks_kernel, 256, 0));
-    size_t blocks = (((size_t)1 << n_local) + 256 * 8 - 1) / (256 * 8);     // a thread takes 4 pairs per trip
+    size_t blocks = (((size_t)1 << n_local) + 256 * 8 - 1) / (256 * 8);     // groups: a thread takes 4 pairs per trip
     size_t cap = (size_t)num_sms() * (size_t)(occ > 0 ? occ : 1) / (size_t)batch;
     if (cap < 1) cap = 1;
     if (blocks > cap) blocks = cap;
