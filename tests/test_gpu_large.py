@@ -100,23 +100,38 @@ def test_sharded_backend_loopback_trainer_runs():
     np.testing.assert_allclose(a.cpu().numpy(), b.cpu().numpy(), atol=3e-5)
 
 
-def test_parity_readout_kernel_matches_torch():
-    """qfx_sv_large_expz_masks on random states, arbitrary masks, with rank bits above the shard."""
-    from qfedx_b200.ops.large import expvals_parity
-    n_local, B, high = 14, 3, 5
-    g = torch.Generator().manual_seed(7)
-    st = torch.complex(torch.randn(B, 1 << n_local, generator=g), torch.randn(B, 1 << n_local, generator=g)).cuda()
-    masks = [int(m) for m in torch.randint(1, 1 << 17, (9,), generator=g)]
-    got = expvals_parity(st.to(torch.complex64), n_local, masks, high_bits=high).cpu().double().numpy()
+def _parity_reference(st, n_local, masks, high):
     idx = (high << n_local) | np.arange(1 << n_local, dtype=np.int64)
     p = (st.abs() ** 2).cpu().double().numpy()
+    out = np.zeros((st.shape[0], len(masks)))
     for j, m in enumerate(masks):
         par = np.zeros_like(idx)
         v = idx & m
         while v.any():
             par ^= v & 1
             v >>= 1
-        np.testing.assert_allclose(got[:, j], (p * (1 - 2 * par)).sum(1), rtol=2e-5)
+        out[:, j] = (p * (1 - 2 * par)).sum(1)
+    return out
+
+
+@pytest.mark.parametrize("n_local,high", [(1, 3), (2, 0), (5, 6), (8, 1), (9, 2), (10, 7), (11, 5), (12, 0), (14, 5), (17, 3)])
+def test_parity_readout_kernel_matches_torch(n_local, high):
+    """qfx_sv_large_expz_masks on random states, arbitrary masks, with rank bits above the shard.  The shard sizes walk
+    through every index-bit class of the kernel: the pair bit, the thread's bits, the folded bits 9 and 10, the table
+    bytes, and rank bits landing in each of them."""
+    from qfedx_b200.ops.large import expvals_parity, expvals_z
+    B = 3
+    g = torch.Generator().manual_seed(7 + n_local)
+    st = torch.complex(torch.randn(B, 1 << n_local, generator=g), torch.randn(B, 1 << n_local, generator=g)).cuda()
+    masks = [int(m) for m in torch.randint(1, 1 << (n_local + 3), (9,), generator=g)] + [1, 1 << (n_local - 1), (1 << (n_local + 3)) - 1]
+    got = expvals_parity(st.to(torch.complex64), n_local, masks, high_bits=high).cpu().double().numpy()
+    want = _parity_reference(st, n_local, masks, high)
+    scale = float((st.abs() ** 2).sum(1).max())
+    np.testing.assert_allclose(got, want, atol=2e-5 * scale)
+    # <Z_q> of every qubit, rank bits included, is the same kernel with one-bit masks
+    n_total = n_local + 3
+    gz = expvals_z(st.to(torch.complex64), n_local, n_total, high_bits=high).cpu().double().numpy()
+    np.testing.assert_allclose(gz, _parity_reference(st, n_local, [1 << q for q in range(n_total)], high), atol=2e-5 * scale)
 
 
 @pytest.mark.parametrize("world", [2, 8])
