@@ -79,6 +79,10 @@ int qfx_vqc_local_train(int n_qubits, int n_layers, int basis, int entangler, in
                         float lr, float beta1, float beta2, float eps, int grad_mode, int cluster_size,
                         int lane_mode, unsigned long long shuffle_key, cudaStream_t stream);
 
+/* Phase timers of the VQC training kernel: n_selected x 12 int64 cycle counters (thread 0 of each cluster's first
+ * CTA; caller-zeroed) accumulated by the following launches on this device; null switches them off (default). */
+int qfx_vqc_train_profile(long long* prof);
+
 /* Evaluation in one launch: out2[0] = sum of losses, out2[1] = number correct.
  * Counterpart of evaluate_model, /root/reference/src/CFed/Classical_FL.py:83-102. */
 int qfx_vqc_eval(int n_qubits, int n_layers, int basis, int entangler, int n_classes, const float* angles,

@@ -41,7 +41,10 @@ struct TrainArgs {
     int ring_offset_floats;   // where the CNOT-ring scratch starts in dynamic shared memory (set by the launcher)
     unsigned long long shuffle_key;   // non-zero and perm == null: samples are visited in a keyed Feistel order
     ReadoutNoise rn;          // readout-level noise applied to <Z> before the logits (alpha 1, beta 0, shots 0 = exact)
+    long long* prof;          // [n_selected][12] cycle counters per phase (thread 0 of each cluster's CTA 0), or null
 };
+
+static long long* g_train_prof[QFX_MAX_DEVICES] = {};
 
 // Gradient sink: reduce over the whole warp (dead circuits contribute zero) and add into the warp's private
 // row of the shared-memory gradient matrix - no atomics, no contention.  `first` marks the first pass of a
@@ -55,6 +58,10 @@ struct WarpRowSink {
     __device__ __forceinline__ void operator()(int p, float v) {   // single value (readout / statistics)
         v = warp_sum(live ? v : 0.f);
         if (lane == 0) { if (first) row[p] = v; else row[p] += v; }
+    }
+    // the same when the warp is ONE circuit and `live` is set on its lane 0 only: nothing to reduce
+    __device__ __forceinline__ void single(int p, float v) {
+        if (live) { if (first) row[p] = v; else row[p] += v; }
     }
     // one layer's 2 NQ gradient shares: slot q -> parameter (l NQ + q) 2, slot NQ + q -> (l NQ + q) 2 + 1
     template <int NQ, int NG>
@@ -129,6 +136,19 @@ vqc_local_train_kernel(const TrainArgs a) {
     float2* ring_buf = ring_all + (size_t)(threadIdx.x >> C::LB) * C::DIM;
 
     const int tid = threadIdx.x;
+    // phase timers (scripts/profile_vqc_train.py): 0 minibatch set-up, 1 forward + readout, 2 loss + readout sinks,
+    // 3 backward, 4 wait for the cluster, 5 gradient reduction (DSMEM), 6 second cluster barrier, 7 optimizer,
+    // 8 diagonal tables
+    long long* prof = (a.prof && tid == 0 && crank == 0) ? a.prof + (size_t)sel * 12 : nullptr;
+    long long t_mark = prof ? clock64() : 0;
+#define VQC_MARK(id)                                   \
+    do {                                               \
+        if (prof) {                                    \
+            const long long _t = clock64();            \
+            prof[id] += _t - t_mark;                   \
+            t_mark = _t;                               \
+        }                                              \
+    } while (0)
     for (int p = tid; p < D; p += TR_THREADS) {
         const float v = a.params_in[p];
         prm[p] = v; m1[p] = 0.f; m2[p] = 0.f;
@@ -141,7 +161,10 @@ vqc_local_train_kernel(const TrainArgs a) {
     const int lg = tid & (C::LANES - 1);
     const int slots_cta = TR_THREADS >> C::LB;
     const int slots_all = slots_cta * cs;
-    const int slot = crank * slots_cta + (tid >> C::LB);
+    // circuit slots are dealt round-robin over the cluster's CTAs, so a minibatch smaller than the cluster's slot count
+    // leaves every CTA the same number of idle warps instead of leaving whole CTAs idle: a cluster wider than one
+    // pass needs then shortens the step (fewer circuits share an SM's issue slots)
+    const int slot = (tid >> C::LB) * cs + crank;
 
     const int seg_lo = a.offsets[client];
     const int n_k = a.offsets[client + 1] - seg_lo;
@@ -160,11 +183,15 @@ vqc_local_train_kernel(const TrainArgs a) {
             __syncthreads();
             float* my_row = sgrad + (tid >> 5) * DS;
             const int lane = tid & 31;
+            VQC_MARK(0);
 
             const int n_pass = (nb + slots_all - 1) / slots_all;
             for (int ps = 0; ps < n_pass; ++ps) {
                 const int j = ps * slots_all + slot;
                 const bool live = j < nb;
+                // a warp that IS one circuit and has no sample left skips the simulation altogether: its gradient row
+                // keeps the zeros written above (nothing below is a block-wide barrier)
+                if (C::LANES == 32 && !live && a.grad_mode == 0) continue;
                 const int jj = live ? j : nb - 1;
                 const int sidx = perm_e ? perm_e[b_lo + jj]
                                         : seg_lo + (fkey ? (int)feistel_perm((uint32_t)(b_lo + jj), (uint32_t)n_k, fkey) : b_lo + jj);
@@ -175,6 +202,7 @@ vqc_local_train_kernel(const TrainArgs a) {
                 ansatz_forward_merged(psi, tab, dt, a.n_layers, a.ent, lg, ring_buf);
                 float ez[NQ];
                 psi.expval_z_all(ez, lg);
+                VQC_MARK(1);
                 if (a.rn.alpha != 1.f || a.rn.beta != 0.f || a.rn.shots > 0) {
                     // noisy readout of the logit qubits; shot noise is keyed by (epoch, sample) so that every lane of the
                     // circuit draws the same outcome
@@ -195,20 +223,33 @@ vqc_local_train_kernel(const TrainArgs a) {
                 {
                     // readout and statistics: one contribution per circuit (its lane 0)
                     WarpRowSink once{my_row, live && lg == 0, lane, ps == 0};
+                    if (C::LANES == 32) {
 #pragma unroll
-                    for (int q = 0; q < NQ; ++q)
-                        if (q < NC) {
-                            once(P + q, dz[q] * ez[q]);
-                            once(P + NC + q, dz[q]);
-                        }
-                    once(D, loss);
-                    once(D + 1, correct ? 1.f : 0.f);
+                        for (int q = 0; q < NQ; ++q)
+                            if (q < NC) {
+                                once.single(P + q, dz[q] * ez[q]);
+                                once.single(P + NC + q, dz[q]);
+                            }
+                        once.single(D, loss);
+                        once.single(D + 1, correct ? 1.f : 0.f);
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < NQ; ++q)
+                            if (q < NC) {
+                                once(P + q, dz[q] * ez[q]);
+                                once(P + NC + q, dz[q]);
+                            }
+                        once(D, loss);
+                        once(D + 1, correct ? 1.f : 0.f);
+                    }
                 }
+                VQC_MARK(2);
                 if (a.grad_mode == 0) {
                     Sv<NQ, LB_> lam;
                     lam.set_obs_times(psi, cot, lg);
                     WarpRowSink sink{my_row, live, lane, ps == 0};
                     ansatz_backward_merged(psi, lam, tab, dt, a.n_layers, a.ent, lg, sink, ring_buf);
+                    VQC_MARK(3);
                 } else if (live && lg == 0) {
 #pragma unroll
                     for (int q = 0; q < NQ; ++q) scot[j * NQ + q] = cot[q];
@@ -230,7 +271,7 @@ vqc_local_train_kernel(const TrainArgs a) {
                     const int j = (it >> 1) / P;
                     const int sidx = perm_e ? perm_e[b_lo + j]
                                             : seg_lo + (fkey ? (int)feistel_perm((uint32_t)(b_lo + j), (uint32_t)n_k, fkey) : b_lo + j);
-                    const int owner = (j % slots_all) / slots_cta;
+                    const int owner = (j % slots_all) % cs;
                     const float* cot_src = cluster.map_shared_rank(scot, owner);
                     Sv<NQ, LB_> psi;
                     psi.set_product(a.angles + (size_t)sidx * NQ, a.basis, lg);
@@ -247,22 +288,33 @@ vqc_local_train_kernel(const TrainArgs a) {
             }
 
             // ---- reduce over the cluster and update -------------------------------------
+            // the CTA's warp rows are summed into row 0 locally first, so that only one row per CTA crosses the cluster
+            __syncthreads();
+            for (int p = tid; p < D + 2; p += TR_THREADS) {
+                float acc = 0.f;
+#pragma unroll
+                for (int w = 0; w < NW; ++w) acc += sgrad[w * DS + p];
+                sgrad[p] = acc;
+            }
             if (cs > 1) cluster.sync(); else __syncthreads();
+            VQC_MARK(4);
             float gsum[(TR_MAX_D + 2 + TR_THREADS - 1) / TR_THREADS];
 #pragma unroll
             for (int r = 0; r < (TR_MAX_D + 2 + TR_THREADS - 1) / TR_THREADS; ++r) {
                 const int p = tid + r * TR_THREADS;
                 float acc = 0.f;
                 if (p < D + 2) {
-                    for (int c = 0; c < cs; ++c) {
-                        const float* src = cs > 1 ? cluster.map_shared_rank(sgrad, c) : sgrad;
-#pragma unroll
-                        for (int w = 0; w < NW; ++w) acc += src[w * DS + p];
+                    if (cs > 1) {
+                        for (int c = 0; c < cs; ++c) acc += cluster.map_shared_rank(sgrad, c)[p];
+                    } else {
+                        acc = sgrad[p];
                     }
                 }
                 gsum[r] = acc;
             }
+            VQC_MARK(5);
             if (cs > 1) cluster.sync(); else __syncthreads();
+            VQC_MARK(6);
             b1t *= a.beta1; b2t *= a.beta2;
             const float inv_nb = 1.f / (float)nb;
 #pragma unroll
@@ -289,11 +341,14 @@ vqc_local_train_kernel(const TrainArgs a) {
                     epoch_correct += gsum[r];
                 }
             }
+            VQC_MARK(7);
             __syncthreads();
             build_diag_tables<NQ, LB_>(dloc, dlane, tab, a.n_layers, tid, TR_THREADS);
             __syncthreads();
+            VQC_MARK(8);
         }
     }
+#undef VQC_MARK
     if (crank == 0) {
         for (int p = tid; p < D; p += TR_THREADS) a.params_out[(size_t)sel * D + p] = prm[p];
         // the threads that own slots D and D+1 hold the epoch statistics
@@ -457,7 +512,15 @@ extern "C" int qfx_vqc_local_train_noisy(int n_qubits, int n_layers, int basis, 
     a.eps = eps; a.grad_mode = grad_mode; a.shuffle_key = shuffle_key;
     QFX_ARG_CHECK(shots >= 0, QFX_ERR_BAD_ARG, "shots must be >= 0");
     a.rn = ReadoutNoise{noise_alpha, noise_beta, shots, noise_key};
+    a.prof = g_train_prof[current_device()];
     return dispatch_nq2<TrainLaunch>(n_qubits, a, n_selected, cluster_size, lane_mode, stream);
+}
+
+// Phase timers of the training kernel: prof = device buffer of n_selected x 12 int64 (zeroed by the caller) that the next
+// launches on this device accumulate cycle counts into, or null to switch the timers off (the default).
+extern "C" int qfx_vqc_train_profile(long long* prof) {
+    g_train_prof[current_device()] = prof;
+    return 0;
 }
 
 extern "C" int qfx_vqc_local_train(int n_qubits, int n_layers, int basis, int entangler, int n_classes,

@@ -158,11 +158,16 @@ class VQCFusedTrainer:
             else:
                 lane_bits = 0 if n <= 4 else (n - 4 if n <= 9 else 5)
             slots = 256 >> lane_bits
+            # cluster_size 0: per-client cluster sizes, chosen every round from the selected clients' step counts
+            # (``_plan_tiers``); ``self.cluster_size`` is then the single-pass size used when all clients get the same
+            self.tiered = cluster_size <= 0
             if cluster_size <= 0:  # enough CTAs to cover one minibatch in a single pass, at most 8
                 cluster_size = 1
                 while cluster_size < 8 and slots * cluster_size < batch_size:
                     cluster_size *= 2
             self.cluster_size = cluster_size
+            self._slots = slots
+            self._tier_streams = {}
             self._out = None
         else:
             self._fallback = TorchLocalTrainer(model, data, None, epochs, batch_size, lr, optimizer, momentum,
@@ -182,14 +187,37 @@ class VQCFusedTrainer:
     def load_flat(self, flat):
         self.model.load_flat_params(flat)
 
+    def _plan_tiers(self, selected):
+        """Cluster size per selected client.  A round lasts as long as its slowest client, and a client's optimizer
+        steps are sequential, so the client with the most steps gets the widest cluster (8 CTAs: the fewest circuits
+        per SM and step) and every other client the NARROWEST cluster that still finishes within that client's time -
+        small clients then take one or two SMs instead of four, and the job stays within one wave of CTAs.  Cost model
+        of a step, measured with the kernel's phase timers (scripts/profile_vqc_train.py, 8 qubits x 6 layers): a fixed
+        part worth about 2.7 circuits plus one unit per circuit a CTA simulates."""
+        bs = self.batch_size
+        steps = [self.epochs * ((int(self.data.sizes[int(k)]) + bs - 1) // bs) for k in selected]
+        # widest useful cluster: one pass over the minibatch; twice that when a circuit is a whole warp (n >= 6 qubits:
+        # halving the warps per SM still shortens the step, measured 24.1 -> 20.6 us) - narrower circuits share warps
+        # and gain nothing from more CTAs
+        top = min(8, self.cluster_size * (2 if self._slots == 8 else 1))
+        sizes = [c for c in (1, 2, 4, 8) if c <= top]
+        cost = {c: 2.7 + (bs + c - 1) // c for c in sizes}
+        target = max(steps) * cost[sizes[-1]] if steps else 0.0
+        return [next(c for c in sizes if st * cost[c] <= target or c == sizes[-1]) for st in steps]
+
     def train(self, global_flat: torch.Tensor, selected, rnd: int):
         if not self.cuda:
             return self._fallback.train(global_flat, selected, rnd)
         m = self.model
-        sel = torch.as_tensor(np.asarray(selected), dtype=torch.int32, device=self.angles.device)
-        K = sel.numel()
-        out = torch.empty(K, self.dim, device=self.angles.device, dtype=torch.float32)
-        stats = torch.empty(K, 2, device=self.angles.device, dtype=torch.float32)
+        selected = [int(k) for k in np.asarray(selected).reshape(-1)]
+        K = len(selected)
+        dev = self.angles.device
+        cs_of = self._plan_tiers(selected) if self.tiered else [self.cluster_size] * K
+        # clients ordered by tier (widest clusters first): each tier is one launch writing its slice of the outputs
+        order = sorted(range(K), key=lambda i: -cs_of[i])
+        sel = torch.as_tensor(np.asarray([selected[i] for i in order]), dtype=torch.int32, device=dev)
+        out = torch.empty(K, self.dim, device=dev, dtype=torch.float32)
+        stats = torch.empty(K, 2, device=dev, dtype=torch.float32)
         from .prng import shuffle_key
         use_array = self.shuffle and self.shuffle_mode == "array"
         perm = self.data.epoch_permutations(self.epochs, self.generator) if use_array else None
@@ -197,18 +225,49 @@ class VQCFusedTrainer:
         beta1 = self.momentum if self.optimizer == "sgd" else self.betas[0]
         g = global_flat.contiguous().float()
         from .prng import shuffle_key as _key
-        _lib.call("qfx_vqc_local_train_noisy", _lib.c_int(m.n_qubits), _lib.c_int(m.n_layers), _lib.c_int(BASIS[m.basis]),
-                  _lib.c_int(ENTANGLER[m.entangler]), _lib.c_int(m.n_logits), _lib.ptr(self.angles),
-                  _lib.ptr(self.labels), _lib.ptr(self.data.offsets), _lib.ptr(perm),
-                  _lib.c_int(self.angles.shape[0]), _lib.ptr(g), _lib.ptr(sel), _lib.c_int(K), _lib.ptr(out),
-                  _lib.ptr(stats), _lib.c_int(self.epochs), _lib.c_int(self.batch_size),
-                  _lib.c_int(OPTIMIZERS[self.optimizer]), _lib.c_float(self.lr), _lib.c_float(beta1),
-                  _lib.c_float(self.betas[1]), _lib.c_float(self.eps),
-                  _lib.c_int(0 if self.grad_method == "adjoint" else 1), _lib.c_int(self.cluster_size),
-                  _lib.c_int(self.lane_mode), _lib.c_u64(skey), _lib.c_float(self._noise_ab[0]),
-                  _lib.c_float(self._noise_ab[1]), _lib.c_int(self._shots), _lib.c_u64(_key(self.seed ^ 0x5EED, rnd)),
-                  _lib.stream_ptr())
-        self.launches += 1
+        tiers, lo = [], 0
+        while lo < K:
+            hi = lo
+            while hi < K and cs_of[order[hi]] == cs_of[order[lo]]:
+                hi += 1
+            tiers.append((cs_of[order[lo]], lo, hi))
+            lo = hi
+
+        def launch(cs, lo, hi):
+            _lib.call("qfx_vqc_local_train_noisy", _lib.c_int(m.n_qubits), _lib.c_int(m.n_layers), _lib.c_int(BASIS[m.basis]),
+                      _lib.c_int(ENTANGLER[m.entangler]), _lib.c_int(m.n_logits), _lib.ptr(self.angles),
+                      _lib.ptr(self.labels), _lib.ptr(self.data.offsets), _lib.ptr(perm),
+                      _lib.c_int(self.angles.shape[0]), _lib.ptr(g), _lib.ptr(sel[lo:hi]), _lib.c_int(hi - lo),
+                      _lib.ptr(out[lo:hi]), _lib.ptr(stats[lo:hi]), _lib.c_int(self.epochs), _lib.c_int(self.batch_size),
+                      _lib.c_int(OPTIMIZERS[self.optimizer]), _lib.c_float(self.lr), _lib.c_float(beta1),
+                      _lib.c_float(self.betas[1]), _lib.c_float(self.eps),
+                      _lib.c_int(0 if self.grad_method == "adjoint" else 1), _lib.c_int(cs),
+                      _lib.c_int(self.lane_mode), _lib.c_u64(skey), _lib.c_float(self._noise_ab[0]),
+                      _lib.c_float(self._noise_ab[1]), _lib.c_int(self._shots), _lib.c_u64(_key(self.seed ^ 0x5EED, rnd)),
+                      _lib.stream_ptr())
+            self.launches += 1
+
+        if len(tiers) == 1:
+            launch(*tiers[0])
+        else:
+            # one launch per tier, side by side on their own streams (the tiers are independent; together they fill the GPU)
+            main = torch.cuda.current_stream()
+            fork = torch.cuda.Event()
+            fork.record(main)
+            for cs, lo, hi in tiers:
+                st = self._tier_streams.get(cs)
+                if st is None:
+                    st = self._tier_streams[cs] = torch.cuda.Stream(device=dev)
+                st.wait_event(fork)
+                with torch.cuda.stream(st):
+                    launch(cs, lo, hi)
+                    done = torch.cuda.Event()
+                    done.record(st)
+                main.wait_event(done)
+        if order != list(range(K)):        # back to the caller's client order
+            inv = torch.as_tensor(np.argsort(np.asarray(order)), dtype=torch.long, device=dev)
+            out, stats = out.index_select(0, inv), stats.index_select(0, inv)
+        self.last_cluster_sizes = cs_of
         self._last_stats = stats
         return out, {"train_stats": stats}
 
