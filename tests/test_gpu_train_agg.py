@@ -58,6 +58,33 @@ def test_fused_local_training_matches_torch_loop(nq, classes, opt, cluster, lane
     np.testing.assert_allclose(out.cpu().numpy(), exp.numpy(), atol=3e-4)
 
 
+def test_tiered_cluster_sizes_match_the_sequential_reference():
+    """Clients of very different sizes: the auto mode gives the longest client the widest cluster and the small ones
+    narrower clusters (one launch per tier, side by side); every client's result still equals the float64 loop, in
+    the caller's client order, and a wide cluster on a minibatch smaller than its slot count (idle warps) is exact."""
+    torch.manual_seed(0)
+    g = torch.Generator().manual_seed(5)
+    nq, classes = 8, 3
+    clients = [(torch.rand(n, nq, generator=g) * math.pi, torch.randint(0, classes, (n,), generator=g))
+               for n in (7, 150, 33, 64, 12)]
+    model = VQC(nq, 2, classes)
+    g0 = model.flat_params()
+    data = FederatedDataset.from_clients(clients, "cuda")
+    fused = VQCFusedTrainer(VQC(nq, 2, classes).cuda(), data, epochs=2, batch_size=16, lr=0.05, optimizer="adam",
+                            shuffle=False, eps=ADAM_EPS)                # cluster_size=0: tiers
+    order = [3, 0, 1, 4, 2]
+    out, info = fused.train(g0.cuda(), order, 0)
+    sizes = fused.last_cluster_sizes
+    assert sizes[order.index(1)] == max(sizes) and min(sizes) < max(sizes), sizes
+    exp = _torch_sequential_reference(model.double(), g0, clients, 2, 16, 0.05, "adam")
+    np.testing.assert_allclose(out.cpu().numpy(), exp[order].numpy(), atol=3e-4)
+    assert info["train_stats"].shape == (5, 2)
+    wide = VQCFusedTrainer(VQC(nq, 2, classes).cuda(), data, epochs=2, batch_size=16, lr=0.05, optimizer="adam",
+                           shuffle=False, eps=ADAM_EPS, cluster_size=8)   # 64 slots for 16 samples
+    out8, _ = wide.train(g0.cuda(), order, 0)
+    np.testing.assert_allclose(out8.cpu().numpy(), exp[order].numpy(), atol=3e-4)
+
+
 def test_param_shift_training_equals_adjoint_training():
     clients = _clients(2, 24, 4, 2, seed=3)
     data = FederatedDataset.from_clients(clients, "cuda")
