@@ -535,10 +535,11 @@ __device__ __forceinline__ void fedavg_fused_body(const AggArgs& a, const int ma
     }
 }
 
-// four CTAs per SM (64 registers): the sweep over the client rows is bandwidth-bound and lives on loads in flight - with
-// the cross-GPU branches in the body the compiler otherwise takes 78 registers and the 1e8-float sweep loses 15 %
-template <int VEC, int UNR, bool FIXED>
-__global__ void __launch_bounds__(AGG_THREADS, 4)
+// One GPU: four CTAs per SM (64 registers) - the sweep over the client rows is bandwidth-bound and lives on loads in
+// flight; left alone, the compiler takes 78 registers for the body with its cross-GPU branches and the 1e8-float sweep
+// loses 15 %.  Across GPUs (MULTI) the exchange loops want the registers instead (NVLS at 1e8 floats: 1.17 vs 1.21 ms).
+template <int VEC, int UNR, bool FIXED, bool MULTI>
+__global__ void __launch_bounds__(AGG_THREADS, MULTI ? 3 : 4)
 fedavg_fused_kernel(const AggArgs a, const int mask_keys_in_smem) {
     fedavg_fused_body<VEC, UNR, FIXED>(a, mask_keys_in_smem);
 }
@@ -585,10 +586,16 @@ static int launch_fedavg(AggArgs& a, cudaStream_t stream) {
     const bool vec4 = a.dim % 4 == 0 && al16(a.client_params) && al16(a.global_in) && al16(a.global_out) &&
                       (!nvls || (al16(a.nvls_partial) && al16(a.nvls_partial_mc) && al16(a.nvls_out) && al16(a.nvls_out_mc)));
     const bool fixed = a.secagg != 0;
-    AggKernel kern = vec4 ? (fixed ? (AggKernel)fedavg_fused_kernel<4, 2, true> : (AggKernel)fedavg_fused_kernel<4, 2, false>)
-                          : (fixed ? (AggKernel)fedavg_fused_kernel<1, 4, true> : (AggKernel)fedavg_fused_kernel<1, 4, false>);
-    static PerDeviceFlag attr_set[4];
-    const int which = (vec4 ? 2 : 0) + (fixed ? 1 : 0);
+    const bool multi = a.world > 1;
+    AggKernel kern;
+    if (multi)
+        kern = vec4 ? (fixed ? (AggKernel)fedavg_fused_kernel<4, 2, true, true> : (AggKernel)fedavg_fused_kernel<4, 2, false, true>)
+                    : (fixed ? (AggKernel)fedavg_fused_kernel<1, 4, true, true> : (AggKernel)fedavg_fused_kernel<1, 4, false, true>);
+    else
+        kern = vec4 ? (fixed ? (AggKernel)fedavg_fused_kernel<4, 2, true, false> : (AggKernel)fedavg_fused_kernel<4, 2, false, false>)
+                    : (fixed ? (AggKernel)fedavg_fused_kernel<1, 4, true, false> : (AggKernel)fedavg_fused_kernel<1, 4, false, false>);
+    static PerDeviceFlag attr_set[8];
+    const int which = (multi ? 4 : 0) + (vec4 ? 2 : 0) + (fixed ? 1 : 0);
     if (!attr_set[which].here()) {
         QFX_CUDA_TRY(cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemCap));
         attr_set[which].here() = true;

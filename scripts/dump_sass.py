@@ -12,13 +12,13 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent.parent
 LIB = ROOT / "qfedx_b200" / "lib" / "libqfedx_b200.so"
 OUT = ROOT / "profiles" / "sass"
-INTEREST = ["UTCHMMA", "UTCQMMA", "UTCBAR", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UBLKCP", "SYNCS", "LDGSTS", "HMMA",
+INTEREST = ["LDGMC", "UTCHMMA", "UTCQMMA", "UTCBAR", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UBLKCP", "SYNCS", "LDGSTS", "HMMA",
             "FFMA", "SHFL", "ATOMS", "ATOMG", "ATOM", "REDG", "RED", "MEMBAR", "CCTL", "BAR", "LDS", "STS", "LDG", "STG"]
 # kernels whose raw listing is kept (regex on the demangled name)
 KEEP = [r"tinycnn_round_kernel", r"tinycnn_eval_conv_kernel", r"conv2_(fwd|dgrad|wgrad)_umma_train", r"unitary_gemm_kernel<128>",
         r"sv_forward_kernel<8>", r"sv_adjoint_kernel<8>", r"vqc_local_train_kernel<8, 5>",
         r"sv_large_pass_v2_kernel", r"sv_large_adjoint_pass_kernel",
-        r"sv_large_expz_masks_kernel", r"sv_global_swap_fused_kernel<3>", r"fedavg_fused_kernel<4, 2, (true|false)>",
+        r"sv_large_expz_masks_kernel", r"sv_global_swap_fused_kernel<3>", r"fedavg_fused_kernel<4, 2, (true|false), (true|false)>",
         r"p2p_probe_kernel<4>", r"readout_noise_kernel"]
 
 
