@@ -118,6 +118,26 @@ class TorchLocalTrainer:
         return tot_loss / len(X), correct / len(X)
 
 
+def plan_cluster_tiers(steps, batch_size: int, one_pass_size: int, slots_per_cta: int):
+    """Cluster size (CTAs) per client of a round of the fused VQC trainer, from the clients' optimizer-step counts.
+
+    A round lasts as long as its slowest client, and a client's steps are sequential, so the client with the most steps
+    gets the widest cluster (the fewest circuits per SM and step) and every other client the NARROWEST cluster that still
+    finishes within that client's time - small clients then take one or two SMs instead of four, and the job stays within
+    one wave of CTAs.  Cost model of a step, measured with the kernel's phase timers (scripts/profile_vqc_train.py,
+    8 qubits x 6 layers): a fixed part worth about 2.7 circuits plus one unit per circuit a CTA simulates.
+
+    ``one_pass_size``: the cluster that covers a minibatch in one pass; ``slots_per_cta``: circuits a CTA simulates at
+    once (8 when a circuit is a whole warp, n >= 6 qubits - only then is a cluster of twice the one-pass size useful:
+    halving the warps per SM still shortens the step, measured 24.1 -> 20.6 us; narrower circuits share warps and gain
+    nothing from more CTAs)."""
+    top = min(8, one_pass_size * (2 if slots_per_cta == 8 else 1))
+    sizes = [c for c in (1, 2, 4, 8) if c <= top]
+    cost = {c: 2.7 + (batch_size + c - 1) // c for c in sizes}
+    target = max(steps) * cost[sizes[-1]] if len(steps) else 0.0
+    return [next(c for c in sizes if st * cost[c] <= target or c == sizes[-1]) for st in steps]
+
+
 class VQCFusedTrainer:
     """All selected clients train in one kernel launch (CUDA); see csrc/vqc_train.cu."""
 
@@ -188,22 +208,9 @@ class VQCFusedTrainer:
         self.model.load_flat_params(flat)
 
     def _plan_tiers(self, selected):
-        """Cluster size per selected client.  A round lasts as long as its slowest client, and a client's optimizer
-        steps are sequential, so the client with the most steps gets the widest cluster (8 CTAs: the fewest circuits
-        per SM and step) and every other client the NARROWEST cluster that still finishes within that client's time -
-        small clients then take one or two SMs instead of four, and the job stays within one wave of CTAs.  Cost model
-        of a step, measured with the kernel's phase timers (scripts/profile_vqc_train.py, 8 qubits x 6 layers): a fixed
-        part worth about 2.7 circuits plus one unit per circuit a CTA simulates."""
         bs = self.batch_size
         steps = [self.epochs * ((int(self.data.sizes[int(k)]) + bs - 1) // bs) for k in selected]
-        # widest useful cluster: one pass over the minibatch; twice that when a circuit is a whole warp (n >= 6 qubits:
-        # halving the warps per SM still shortens the step, measured 24.1 -> 20.6 us) - narrower circuits share warps
-        # and gain nothing from more CTAs
-        top = min(8, self.cluster_size * (2 if self._slots == 8 else 1))
-        sizes = [c for c in (1, 2, 4, 8) if c <= top]
-        cost = {c: 2.7 + (bs + c - 1) // c for c in sizes}
-        target = max(steps) * cost[sizes[-1]] if steps else 0.0
-        return [next(c for c in sizes if st * cost[c] <= target or c == sizes[-1]) for st in steps]
+        return plan_cluster_tiers(steps, bs, self.cluster_size, self._slots)
 
     def train(self, global_flat: torch.Tensor, selected, rnd: int):
         if not self.cuda:

@@ -181,3 +181,21 @@ def test_cli_train_under_torchrun_matches_single_process(tmp_path, world):
     b = json.loads([l for l in multi.stdout.splitlines() if l.startswith("{")][-1])
     assert b["world"] == world and a["world"] == 1
     assert a["accuracies"] == pytest.approx(b["accuracies"], abs=1e-6)
+
+
+def test_cluster_tiers_follow_the_step_counts():
+    """Per-client cluster sizes of the fused VQC trainer (pure planning, no GPU): the longest client gets the widest
+    cluster, nobody gets a wider one than it needs to keep up, equal clients share one tier, and circuits narrower than a
+    warp never go beyond the one-pass size."""
+    from qfedx_b200.fl.trainers import plan_cluster_tiers
+    steps = [175, 140, 100, 60, 40, 10, 5]
+    tiers = plan_cluster_tiers(steps, 32, 4, 8)
+    assert tiers[0] == 8 and tiers == sorted(tiers, reverse=True) and tiers[-1] == 1
+    cost = lambda c: 2.7 + (32 + c - 1) // c
+    for st, c in zip(steps, tiers):
+        assert st * cost(c) <= steps[0] * cost(8) or c == 8
+        if c > 1:
+            assert st * cost(c // 2) > steps[0] * cost(8)            # the next narrower cluster would be too slow
+    assert plan_cluster_tiers([50, 50, 50, 50], 32, 1, 32) == [1, 1, 1, 1]        # 4-qubit circuits: one CTA covers the batch
+    assert set(plan_cluster_tiers([90, 90], 32, 4, 8)) == {8}
+    assert plan_cluster_tiers([], 32, 4, 8) == []
