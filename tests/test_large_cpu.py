@@ -282,3 +282,17 @@ def test_lockstep_adjoint_training_equals_the_one_client_at_a_time_loop():
     gb = vq.adjoint_grad(ang, th, cot)
     assert torch.allclose(gb[0], vq.adjoint_grad(ang[0::2], th[0], cot[0::2]), atol=1e-6)
     assert torch.allclose(gb[1], vq.adjoint_grad(ang[1::2], th[1], cot[1::2]), atol=1e-6)
+
+
+def test_deep_circuits_on_few_qubits_are_cut_into_launchable_passes():
+    """12 qubits x 16 layers fits ONE tile, so the scheduler returns a single pass of 396 gates - more than a launch of
+    the pass kernel takes (160).  compile_passes cuts it into consecutive passes over the same tile; order and content of
+    the gates are unchanged and every piece gets its own segment plan."""
+    from qfedx_b200.ops.large import MAX_OPS_PER_PASS, ansatz_gates, compile_passes
+    gates = ansatz_gates(12, 16)
+    passes = compile_passes(12, gates, 12, 3)
+    _check_schedule(12, gates, passes, 12, 3)
+    assert len(passes) >= 3 and all(1 <= len(p.ops) <= MAX_OPS_PER_PASS for p in passes)
+    assert all((p.tile_qubits == passes[0].tile_qubits).all() for p in passes)
+    assert all(p.plan is not None for p in passes)
+    assert sum(len(p.ops) for p in passes) == 12 + 16 * (12 + 12)
