@@ -73,6 +73,8 @@ def run_experiment(cfg: ExperimentConfig) -> dict:
     from .parallel.runtime import local_clients, make_aggregator
     from .utils.metrics import auc_from_logits
     rank, world, local = _dist_context()
+    if rank != 0:      # one narrator per job: the other ranks neither print per-round lines nor write the round log
+        cfg.fl.quiet, cfg.fl.log_path, cfg.fl.tensorboard_dir = True, None, None
     set_seeds(cfg.seed)
     dev = _device(cfg.device)
     if dev.type == "cuda" and world > 1:
