@@ -366,6 +366,10 @@ __device__ __forceinline__ void head_phase(const Step& s, int sel, int nb, int l
     const float* __restrict__ prm = s.params + (size_t)sel * s.nd;
     const int f2b = F2W + 64 * NC;
     if (tid < 2) hs.red[tid] = 0.f;
+    // the row's label (two dependent global loads: sample order, then label) is fetched now, under the partial sums, and
+    // not when the softmax needs it
+    int y_row = 0;
+    if (tid < BS && tid < nb) y_row = s.labels[sample_index(s, sel, lo, tid)];
     for (int i = tid; i < NC * 64; i += PNT) hs.w2[i / 64][i % 64] = __ldcg(prm + F2W + i);
     const int rnd = s.round_dev ? *s.round_dev : s.round;
     const unsigned long long dkey = key3(s.seed ^ 0x44524f50ull, (unsigned long long)rnd * 4096ull + s.client_ids[sel],
@@ -409,7 +413,7 @@ __device__ __forceinline__ void head_phase(const Step& s, int sel, int nb, int l
     if (tid < BS) {
         const int b = tid;
         if (b < nb) {
-            const int y = s.labels[sample_index(s, sel, lo, b)];
+            const int y = y_row;
             float m = hs.z[b][0]; int arg = 0;
             for (int c = 1; c < NC; ++c) if (hs.z[b][c] > m) { m = hs.z[b][c]; arg = c; }
             float sum = 0.f;
