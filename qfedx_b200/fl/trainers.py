@@ -188,6 +188,7 @@ class VQCFusedTrainer:
             self.cluster_size = cluster_size
             self._slots = slots
             self._tier_streams = {}
+            self._plans = {}
             self._out = None
         else:
             self._fallback = TorchLocalTrainer(model, data, None, epochs, batch_size, lr, optimizer, momentum,
@@ -219,10 +220,20 @@ class VQCFusedTrainer:
         selected = [int(k) for k in np.asarray(selected).reshape(-1)]
         K = len(selected)
         dev = self.angles.device
-        cs_of = self._plan_tiers(selected) if self.tiered else [self.cluster_size] * K
-        # clients ordered by tier (widest clusters first): each tier is one launch writing its slice of the outputs
-        order = sorted(range(K), key=lambda i: -cs_of[i])
-        sel = torch.as_tensor(np.asarray([selected[i] for i in order]), dtype=torch.int32, device=dev)
+        # plan of a selection (cluster sizes, launch order, device index tensors): kept for the selections seen last - with
+        # full participation every round reuses one entry and starts without host-to-device copies
+        key = tuple(selected)
+        plan = self._plans.get(key)
+        if plan is None:
+            cs_of = self._plan_tiers(selected) if self.tiered else [self.cluster_size] * K
+            # clients ordered by tier (widest clusters first): each tier is one launch writing its slice of the outputs
+            order = sorted(range(K), key=lambda i: -cs_of[i])
+            sel = torch.as_tensor(np.asarray([selected[i] for i in order]), dtype=torch.int32, device=dev)
+            inv = None if order == list(range(K)) else torch.as_tensor(np.argsort(np.asarray(order)), dtype=torch.long, device=dev)
+            if len(self._plans) >= 16:
+                self._plans.pop(next(iter(self._plans)))
+            plan = self._plans[key] = (cs_of, order, sel, inv)
+        cs_of, order, sel, inv = plan
         out = torch.empty(K, self.dim, device=dev, dtype=torch.float32)
         stats = torch.empty(K, 2, device=dev, dtype=torch.float32)
         from .prng import shuffle_key
@@ -271,8 +282,7 @@ class VQCFusedTrainer:
                     done = torch.cuda.Event()
                     done.record(st)
                 main.wait_event(done)
-        if order != list(range(K)):        # back to the caller's client order
-            inv = torch.as_tensor(np.argsort(np.asarray(order)), dtype=torch.long, device=dev)
+        if inv is not None:                # back to the caller's client order
             out, stats = out.index_select(0, inv), stats.index_select(0, inv)
         self.last_cluster_sizes = cs_of
         self._last_stats = stats
